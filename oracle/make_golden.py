@@ -1,0 +1,345 @@
+"""Generate ``tests/golden/*.npz`` by running the UNMODIFIED reference
+(TEST INFRASTRUCTURE; runs only in the build container, see ``ref_shim.py``).
+
+    python -m oracle.make_golden
+
+Every fixture stores the full inputs next to the reference's outputs so that the
+tests never need ``/root/reference`` (the GPU box does not have it).
+
+Fixtures
+--------
+kat_propagators.npz  reference propagators / priors on the TIP prior
+                     (kf_tools.py:99-116,174-353) + the numbers quoted in the
+                     reference's own tests/test_kf.py:19-54
+kat_time_grid.npz    iterate_time_grid on tests/test_utils.py:18-38's case
+barrax_mask.npz      Barrax_pivots.tif as packed bits + compaction index digest
+solve_s2.npz         variational_kalman_multiband (solvers.py:100-145) on
+                     operators built by create_prosail_observation_operator
+run_s2.npz           LinearKalman.run, S2/PROSAIL style (kafka_test_S2.py:174-194)
+run_tip.npz          LinearKalman.run, 2-band TIP with state_mapper operators and
+                     propagate_information_filter_LAI (kafka_test.py:156-217)
+run_linear.npz       LinearKalman.run, 1 linear band in (H0,H) tuple form
+"""
+import datetime as dt
+import hashlib
+import logging
+import os
+import re
+
+import numpy as np
+import scipy.sparse as sp
+
+from oracle import ref_shim
+from oracle.gp import GaussianProcess
+from kafka_inferenceengine_b200 import synthetic as syn
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                   "tests", "golden")
+
+
+class _IterLog(logging.Handler):
+    """Collect 'Iteration # n, convergence norm: g' lines (linear_kf.py:294-296)."""
+    rx = re.compile(r"Iteration # (\d+), convergence norm: (\S+)")
+
+    def __init__(self):
+        super().__init__()
+        self.rows = []
+
+    def emit(self, record):
+        m = self.rx.search(record.getMessage())
+        if m:
+            self.rows.append((int(m.group(1)), float(m.group(2))))
+
+
+def _predict(gp, X):
+    return gp.predict(X, do_unc=False)[0]
+
+
+def _gp_arrays(prefix, gps):
+    out = {}
+    for b, gp in enumerate(gps):
+        out["%s_inputs_%d" % (prefix, b)] = gp.inputs
+        out["%s_targets_%d" % (prefix, b)] = gp.targets
+        out["%s_theta_%d" % (prefix, b)] = gp.theta
+    return out
+
+
+def _obs_arrays(obs):
+    out = {}
+    for di, d in enumerate(obs.dates):
+        for b in range(obs.bands_per_observation[d]):
+            bd = obs.get_band_data(d, b)
+            out["obs_y_%d_%d" % (di, b)] = bd.observations
+            out["obs_invvar_%d_%d" % (di, b)] = bd.uncertainty.diagonal().reshape(bd.mask.shape)
+            out["obs_mask_%d_%d" % (di, b)] = bd.mask
+    out["obs_dates"] = np.array([d.toordinal() for d in obs.dates])
+    return out
+
+
+def _small_mask(rng, ny, nx, frac=0.55):
+    m = rng.random((ny, nx)) < frac
+    m[0, :] = False           # ragged edges: an empty row and a full row
+    m[1, :] = True
+    return m
+
+
+class _RefOutput(object):
+    def __init__(self):
+        self.rows = []
+
+    def dump_data(self, timestep, x, P, P_inv, state_mask, n_params):
+        self.rows.append((timestep.toordinal(), np.array(x, dtype=np.float64),
+                          np.array(P_inv.diagonal(), dtype=np.float64)))
+
+
+def _run_arrays(out, itlog):
+    res = {"out_steps": np.array([r[0] for r in out.rows]),
+           "out_x": np.array([r[1] for r in out.rows]),
+           "out_diag": np.array([r[2] for r in out.rows]),
+           "iter_log": np.array(itlog.rows, dtype=np.float64).reshape(-1, 2)}
+    return res
+
+
+def kat_propagators(kafka):
+    kt = kafka.inference.kf_tools
+    x0, cov, inv = kt.tip_prior()
+    n_pix = 3
+    x_a = np.tile(x0, n_pix) + 0.01 * np.arange(7 * n_pix)
+    Pi = sp.block_diag([inv.astype(np.float64) * (1 + 0.1 * i) for i in range(n_pix)]).tocsr()
+    M = sp.eye(7 * n_pix, format="csr")
+    q = np.tile(np.linspace(0.05, 0.15, 7), n_pix)
+    Q = sp.diags(q).tocsr()
+    res = {"tip_mean": x0, "tip_cov": cov, "tip_inv": inv, "x_a": x_a,
+           "Pinv": Pi.toarray(), "q": q}
+    _, _, p = kt.propagate_information_filter_approx_SLOW(x_a, None, Pi, M, Q)
+    res["approx_Pinv"] = p.toarray()
+    _, _, p = kt.propagate_information_filter_SLOW(x_a, None, Pi, M, Q)
+    res["exact_Pinv"] = p.toarray()
+    xf, _, p = kt.propagate_information_filter_LAI(x_a, None, Pi, M, Q)
+    res["lai_x"] = xf
+    res["lai_Pinv"] = p.toarray()
+    xf, _, p = kt.no_propagation(x_a, None, Pi, M, Q)
+    res["noprop_x"] = xf
+    res["noprop_Pinv"] = p.toarray()
+    P = sp.block_diag([cov.astype(np.float64)] * n_pix).tocsr()
+    xf, pf, _ = kt.propagate_standard_kalman(x_a, P, None, M * 2.0, Q)
+    res["std_x"] = xf
+    res["std_P"] = pf.toarray()
+    # blend_prior (kf_tools.py:75-96)
+    prior_mean = np.tile(x0, n_pix)
+    prior_inv = sp.block_diag([inv.astype(np.float64)] * n_pix).tocsr()
+    xc, C = kt.blend_prior(prior_mean, prior_inv, x_a, Pi)
+    res["blend_x"] = xc
+    res["blend_C"] = C.toarray()
+    # numbers quoted in the reference's own test (tests/test_kf.py:30-54): single pixel, Q=0.1 I
+    Pi1 = sp.csr_matrix(inv.astype(np.float64))
+    _, _, p = kt.propagate_information_filter_approx_SLOW(x0, None, Pi1, np.eye(7),
+                                                          sp.csr_matrix(np.eye(7) * 0.1))
+    res["test_kf_approx_diag"] = p.toarray().diagonal()
+    _, _, p = kt.propagate_information_filter_SLOW(x0, None, Pi1, sp.eye(7),
+                                                   sp.csr_matrix(np.eye(7) * 0.1))
+    res["test_kf_exact"] = np.asarray(p.todense())
+    np.savez_compressed(os.path.join(OUT, "kat_propagators.npz"), **res)
+
+
+def kat_time_grid(kafka):
+    base = dt.datetime(2007, 7, 1)
+    grid = [base + i * dt.timedelta(days=1) for i in range(0, 60, 16)]
+    base = dt.datetime(2007, 1, 1)
+    dates = [base + i * dt.timedelta(days=1) for i in range(1, 365 + 8, 8)]
+    steps, locs, firsts = [], [], []
+    for t, loc, first in kafka.inference.utils.iterate_time_grid(grid, dates):
+        steps.append(t.toordinal())
+        locs.append([d.toordinal() for d in loc])
+        firsts.append(first)
+    np.savez_compressed(os.path.join(OUT, "kat_time_grid.npz"),
+                        steps=np.array(steps), locs=np.array(locs), firsts=np.array(firsts))
+
+
+def barrax_mask():
+    import cv2
+    m = cv2.imread(os.path.join(ref_shim.REFERENCE_ROOT, "Barrax_pivots.tif"),
+                   cv2.IMREAD_UNCHANGED)
+    mask = m.astype(bool)
+    idx = np.flatnonzero(mask.ravel())
+    np.savez_compressed(os.path.join(OUT, "barrax_mask.npz"),
+                        shape=np.array(mask.shape), bits=np.packbits(mask.ravel()),
+                        n_true=np.array(idx.size),
+                        idx_sha256=np.array(hashlib.sha256(idx.astype(np.int64).tobytes()).hexdigest()))
+    return mask
+
+
+def solve_and_run_s2(kafka):
+    rng = np.random.default_rng(20240601)
+    P, B, T = 10, 10, 250
+    mask = _small_mask(rng, 18, 23)
+    N = int(mask.sum())
+    gps = [syn.make_emulator(rng, syn.SAIL_MEAN, syn.SAIL_SIGMA, n_train=T, cls=GaussianProcess)
+           for _ in range(B)]
+    x_true = syn.SAIL_MEAN + syn.SAIL_SIGMA * rng.standard_normal((N, P))
+    base = dt.datetime(2017, 7, 3)
+    dates = [base + dt.timedelta(days=d) for d in (0, 1, 4)]
+    obs = syn.SyntheticObservations(mask, dates, gps, x_true, _predict, rng)
+    inv_cov = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32)
+    ku = kafka.inference.utils
+
+    class Prior(object):
+        def process_prior(self, time, inv_cov=True):
+            x0 = np.tile(syn.SAIL_MEAN, N)
+            return x0, ku.block_diag([inv_cov_blk for _ in range(N)], dtype=np.float32)
+    inv_cov_blk = inv_cov
+    prior = Prior()
+    x0, Pinv0 = prior.process_prior(None)
+
+    # ---- single linearised solve around a perturbed state (solvers.py:100-145)
+    x_lin = x0 + np.tile(0.3 * syn.SAIL_SIGMA, N) * rng.standard_normal(N * P)
+    d0 = dates[0]
+    Hs = [ku.create_prosail_observation_operator(P, gps[b], None, obs.get_band_data(d0, b).mask,
+                                                 mask, x_lin, b) for b in range(B)]
+    bd = [obs.get_band_data(d0, b) for b in range(B)]
+    x, _, A, innov, fwd = kafka.inference.solvers.variational_kalman_multiband(
+        [b_.observations for b_ in bd], [b_.mask for b_ in bd], mask,
+        [b_.uncertainty for b_ in bd], Hs, P, x_lin, x0, None, Pinv0.tocsr(), None)
+    res = {"mask": mask, "x_true": x_true, "x0": x0, "x_lin": x_lin,
+           "prior_inv_block": inv_cov, "ref_x": x, "ref_A_diag": A.diagonal(),
+           "ref_A_blocks_first": A[:3 * P, :3 * P].toarray(),
+           "ref_innovations": innov, "ref_fwd": fwd,
+           "ref_H0": np.array([h[0] for h in Hs]),
+           "ref_J": np.array([np.asarray(h[1].tocsr().data) for h in Hs], dtype=object)}
+    # J rows are ragged (unobserved rows are empty): store dense (B, N, P)
+    Jd = np.zeros((B, N, P), dtype=np.float32)
+    for b, h in enumerate(Hs):
+        Hc = h[1].tocoo()
+        Jd[b, Hc.row, Hc.col - P * Hc.row] = Hc.data
+    res["ref_J"] = Jd
+    res.update(_gp_arrays("gp", gps))
+    res.update(_obs_arrays(obs))
+    np.savez_compressed(os.path.join(OUT, "solve_s2.npz"), **res)
+
+    # ---- full run (kafka_test_S2.py:174-194): prior-only advance, Q = 0
+    itlog = _IterLog()
+    logging.getLogger("kafka.linear_kf.linear_kf").addHandler(itlog)
+    logging.getLogger("kafka.linear_kf.linear_kf").setLevel(logging.INFO)
+    out = _RefOutput()
+    kf = kafka.LinearKalman(obs, out, mask, ku.create_prosail_observation_operator,
+                            syn.S2_PARAMETERS, state_propagation=None, prior=prior,
+                            linear=False)
+    kf.set_trajectory_model()
+    kf.set_trajectory_uncertainty(np.zeros_like(x0))
+    grid = [base + dt.timedelta(days=d) for d in (0, 2, 4, 6, 8)]
+    kf.run(grid, x0, None, Pinv0, iter_obs_op=True)
+    logging.getLogger("kafka.linear_kf.linear_kf").removeHandler(itlog)
+    res2 = {"mask": mask, "x_true": x_true, "x0": x0, "prior_inv_block": inv_cov,
+            "grid": np.array([g.toordinal() for g in grid])}
+    res2.update(_gp_arrays("gp", gps))
+    res2.update(_obs_arrays(obs))
+    res2.update(_run_arrays(out, itlog))
+    np.savez_compressed(os.path.join(OUT, "run_s2.npz"), **res2)
+
+
+def run_tip(kafka):
+    rng = np.random.default_rng(77)
+    P, B, T = 7, 2, 120
+    mask = _small_mask(rng, 14, 17)
+    N = int(mask.sum())
+    mappers = [np.array([0, 1, 6, 2]), np.array([3, 4, 6, 5])]
+    gps = [syn.make_emulator(rng, syn.TIP_MEAN[m], syn.TIP_SIGMA[m], n_train=T, w_scale=0.15,
+                             cls=GaussianProcess) for m in mappers]
+    x_true = syn.TIP_MEAN + 0.5 * syn.TIP_SIGMA * rng.standard_normal((N, P))
+    base = dt.datetime(2017, 1, 1)
+    dates = [base + dt.timedelta(days=d) for d in (1, 9, 17, 18, 33)]
+    obs = syn.SyntheticObservations(mask, dates, gps, x_true, _predict, rng,
+                                    state_mappers=mappers, min_sigma=2.5e-3)
+    kt = kafka.inference.kf_tools
+    ku = kafka.inference.utils
+    mean, prior_inv = kt.tip_prior_full({"n_pixels": N})
+    itlog = _IterLog()
+    lg = logging.getLogger("kafka.linear_kf.linear_kf")
+    lg.addHandler(itlog)
+    lg.setLevel(logging.INFO)
+    out = _RefOutput()
+    kf = kafka.LinearKalman(obs, out, mask, ku.create_nonlinear_observation_operator,
+                            syn.TIP_PARAMETERS,
+                            state_propagation=kt.propagate_information_filter_LAI,
+                            prior=None, linear=False)
+    q = np.zeros(N * P)
+    q[6::7] = 0.04                                           # kafka_test.py:207-208
+    kf.set_trajectory_model()
+    kf.set_trajectory_uncertainty(q)
+    grid = [base + dt.timedelta(days=d) for d in range(0, 49, 8)]
+    kf.run(grid, mean, None, prior_inv.tocsr(), iter_obs_op=True)
+    lg.removeHandler(itlog)
+    res = {"mask": mask, "x_true": x_true, "x0": mean, "q": q,
+           "prior_inv_block": kt.tip_prior()[2],
+           "grid": np.array([g.toordinal() for g in grid]),
+           "mapper_0": mappers[0], "mapper_1": mappers[1]}
+    res.update(_gp_arrays("gp", gps))
+    res.update(_obs_arrays(obs))
+    res.update(_run_arrays(out, itlog))
+    np.savez_compressed(os.path.join(OUT, "run_tip.npz"), **res)
+
+
+def run_linear(kafka):
+    """Config-1 shape: TIP state, one linear band observing slot 6, LAI propagator."""
+    rng = np.random.default_rng(5)
+    P = 7
+    mask = _small_mask(rng, 12, 15)
+    N = int(mask.sum())
+    row = np.zeros(P)
+    row[6] = 1.0
+    op = syn.LinearBandOperator(row, 0.0)
+    x_true = syn.TIP_MEAN + 0.5 * syn.TIP_SIGMA * rng.standard_normal((N, P))
+    base = dt.datetime(2017, 1, 1)
+    dates = [base + dt.timedelta(days=d) for d in range(1, 11)]
+    obs = syn.LinearObservations(mask, dates, op, x_true, rng, sigma_obs=0.05, p_observed=0.85)
+    kt = kafka.inference.kf_tools
+
+    def create_linear_tuple_operator(n_params, emulator, metadata, mask_, state_mask, x_prev, band):
+        # same contract as utils.py:181-219 with a linear forward model
+        n = x_prev.shape[0] // n_params
+        H = sp.lil_matrix((n, n_params * n), dtype=np.float32)
+        H0 = np.zeros(n, dtype=np.float32)
+        for i, m in enumerate(mask_[state_mask].flatten()):
+            if m:
+                H[i, n_params * i:n_params * (i + 1)] = emulator.row
+                H0[i] = emulator.row @ x_prev[n_params * i:n_params * (i + 1)] + emulator.offset
+        return (H0, H.tocsr())
+
+    mean, prior_inv = kt.tip_prior_full({"n_pixels": N})
+    itlog = _IterLog()
+    lg = logging.getLogger("kafka.linear_kf.linear_kf")
+    lg.addHandler(itlog)
+    lg.setLevel(logging.INFO)
+    out = _RefOutput()
+    kf = kafka.LinearKalman(obs, out, mask, create_linear_tuple_operator, syn.TIP_PARAMETERS,
+                            state_propagation=kt.propagate_information_filter_LAI, prior=None)
+    q = np.zeros(N * P)
+    q[6::7] = 0.04
+    kf.set_trajectory_model()
+    kf.set_trajectory_uncertainty(q)
+    grid = [base + dt.timedelta(days=d) for d in range(0, 12)]
+    kf.run(grid, mean, None, prior_inv.tocsr())
+    lg.removeHandler(itlog)
+    res = {"mask": mask, "x_true": x_true, "x0": mean, "q": q, "row": row,
+           "prior_inv_block": kt.tip_prior()[2],
+           "grid": np.array([g.toordinal() for g in grid])}
+    res.update(_obs_arrays(obs))
+    res.update(_run_arrays(out, itlog))
+    np.savez_compressed(os.path.join(OUT, "run_linear.npz"), **res)
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    kafka = ref_shim.load()
+    kat_propagators(kafka)
+    kat_time_grid(kafka)
+    barrax_mask()
+    solve_and_run_s2(kafka)
+    run_tip(kafka)
+    run_linear(kafka)
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()
