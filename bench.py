@@ -1,0 +1,471 @@
+#!/usr/bin/env python
+"""Benchmark of the KaFKA assimilation step on B200 (see DESIGN.md, section
+"Measurement").
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+Workload (config.workload): one GPU's shard of BASELINE.json configs[3] -- the
+full Sentinel-2 tile (10980 x 10980 px) sharded by pixel over 8 GPUs, i.e.
+1373 x 10980 = 15 075 540 px per GPU -- with the 10-parameter PROSAIL state, 10
+bands, one 250-point GP emulator per band, iterated linearisation.  Weak
+scaling: every rank holds one such shard, N=8 is the full tile.  A *step* is one
+observation date assimilated for every pixel of the shard (all bands, all
+iterations); metric = pixel-dates/s summed over ranks.
+
+* value : inputs resident in HBM (device rasters), CUDA-event timed
+* e2e   : LinearKalman.run() with HOST observation rasters; host->device copies
+          and the device->host read of the posterior inside the timed region
+* roofline / cpu_baseline : see DESIGN.md
+"""
+import argparse
+import ctypes
+import datetime as dt
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+P, B, T = 10, 10, 250
+TILE = 10980
+SHARD_ROWS = 1373                     # ceil(10980 / 8)
+BYTES_PER_PIXEL_DATE = 16 * P + 8 * P * (P + 1) + 17 * B          # 1210
+FLOPS_PER_PIXEL_ITER = B * T * (5 * P + 28) + B * (P * P + 3 * P) + P ** 3 / 3 + 2 * P * P
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=SHARD_ROWS, help="raster rows per GPU (x 10980 columns)")
+    ap.add_argument("--cols", type=int, default=TILE)
+    ap.add_argument("--cpu-sample", type=int, default=131072, help="pixels of the workload timed on the host")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------
+# synthetic workload
+# --------------------------------------------------------------------------
+def make_emulators(seed=1234):
+    from kafka_inferenceengine_b200 import synthetic as syn
+    rng = np.random.default_rng(seed)
+    return [syn.make_emulator(rng, syn.SAIL_MEAN, syn.SAIL_SIGMA, n_train=T) for _ in range(B)]
+
+
+def synth_on_device(gps, n_pix, seed, device):
+    """x_true ~ N(prior), reflectance = emulator(x_true) + 5 % noise, observed with
+    probability 0.9 and rho > 0, inverse variance 1/(0.05 rho)^2 (inf where
+    masked) -- Sentinel2_Observations.py:168-178 shaped, generated on the device."""
+    import torch
+    from kafka_inferenceengine_b200 import synthetic as syn
+    from kafka_inferenceengine_b200.device import DeviceVector
+    from kafka_inferenceengine_b200.inference.utils import emulator_table, linearize_bands
+    gen = torch.Generator(device=device).manual_seed(seed)
+    xt = DeviceVector.empty(n_pix, P, device)
+    mean = torch.from_numpy(syn.SAIL_MEAN).to(device)[:, None]
+    sig = torch.from_numpy(syn.SAIL_SIGMA).to(device)[:, None]
+    xt.data.copy_(mean + sig * torch.randn(xt.data.shape, generator=gen, dtype=torch.float64, device=device))
+    tabs = [(emulator_table(g, device), np.arange(P)) for g in gps]
+    rho = torch.empty((B, xt.ld), dtype=torch.float64, device=device)
+    linearize_bands(xt, tabs, None, False, h0=rho, want_jac=False)       # forward model only
+    rho = rho[:, :n_pix].contiguous()
+    rho = rho * (1.0 + 0.05 * torch.randn(rho.shape, generator=gen, dtype=torch.float64, device=device))
+    mask = (rho > 0) & (torch.rand(rho.shape, generator=gen, device=device) < 0.9)
+    rho = torch.where(mask, rho, torch.zeros_like(rho))
+    inv = torch.where(mask, 1.0 / (0.05 * rho) ** 2, torch.full_like(rho, float("inf")))
+    return rho, inv, mask.to(torch.uint8)
+
+
+class DeviceObservations(object):
+    """Observation collaborator handing out DEVICE rasters (inputs resident in HBM)."""
+
+    def __init__(self, dates, gps, rho, inv, mask, shape):
+        from kafka_inferenceengine_b200 import synthetic as syn
+        self.dates = list(dates)
+        self.bands_per_observation = {d: B for d in self.dates}
+        self._bands = [syn.BandData(rho[b].view(shape), inv[b].view(shape), mask[b].view(shape), {"band": b}, gps[b])
+                       for b in range(B)]
+
+    def get_band_data(self, date, band):
+        return self._bands[band]
+
+
+class HostObservations(object):
+    """Same data as host numpy rasters (the reference's data contract:
+    observations (ny,nx) float64, inverse-variance raster, boolean mask)."""
+
+    def __init__(self, dates, gps, rho, inv, mask, shape):
+        from kafka_inferenceengine_b200 import synthetic as syn
+        self.dates = list(dates)
+        self.bands_per_observation = {d: B for d in self.dates}
+        self._bands = [syn.BandData(rho[b].cpu().numpy().reshape(shape), inv[b].cpu().numpy().reshape(shape),
+                                    mask[b].cpu().numpy().reshape(shape).astype(bool), {"band": b}, gps[b])
+                       for b in range(B)]
+
+    def get_band_data(self, date, band):
+        return self._bands[band]
+
+
+class ReadbackOutput(object):
+    """Output collaborator: reads the posterior mean and diag(P^-1) back to the
+    host (what KafkaOutput.dump_data consumes, observations.py:374-375,392-393)."""
+
+    def __init__(self):
+        self.d2h_bytes = 0
+        self.last = None
+
+    def dump_data(self, timestep, x_analysis, P_analysis, P_analysis_inv, state_mask, n_params):
+        x = np.asarray(x_analysis)
+        d = P_analysis_inv.diagonal()
+        self.d2h_bytes += x.nbytes + d.nbytes
+        self.last = (x, d)
+
+
+class NullOutput(object):
+    def dump_data(self, *a):
+        pass
+
+
+# --------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------
+class ClockSampler(object):
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [c.strip() for c in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[2 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------
+# CPU baseline: the reference's algorithm restated (oracle A', scipy sparse +
+# float32 SuperLU; GP by numpy) on a bounded sample of the same workload
+# --------------------------------------------------------------------------
+def _cpu_chunk(args):
+    gp_arrays, y, w, m, chunk = args
+    from oracle import kafka_cpu as kc
+    from oracle.gp import GaussianProcess
+    from kafka_inferenceengine_b200 import synthetic as syn
+    gps = [GaussianProcess(a[0], a[1], a[2]) for a in gp_arrays]
+    n = y.shape[1]
+    inv = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
+    blocks = np.repeat(inv[None], n, axis=0)
+    x0 = np.tile(syn.SAIL_MEAN, n)
+    ops = [(lambda xp, gp=gps[b], mm=m[b]: kc.emulator_operator(gp, xp, P, mm)) for b in range(B)]
+    t0 = time.perf_counter()
+    x, A, _, iters, _ = kc.do_all_bands(ops, [y[b] for b in range(B)], [w[b] for b in range(B)],
+                                        [m[b] for b in range(B)], x0, blocks, P, mode="sparse32")
+    return time.perf_counter() - t0, iters, n
+
+
+def cpu_baseline(gps, rho, inv, mask, n_sample, procs=1, chunk=16384):
+    """Time the CPU port on `n_sample` pixels of the workload, chunked like the
+    reference's drivers (<= 256 x 256 px per LinearKalman, kafka_test_Py36.py:241)."""
+    n_sample = int(min(n_sample, rho.shape[1]))
+    y = rho[:, :n_sample].cpu().numpy()
+    m = mask[:, :n_sample].cpu().numpy().astype(bool)
+    w = np.where(m, inv[:, :n_sample].cpu().numpy(), 0.0)
+    gp_arrays = [(g.inputs, g.targets, g.theta) for g in gps]
+    jobs = [(gp_arrays, y[:, s:s + chunk], w[:, s:s + chunk], m[:, s:s + chunk], chunk)
+            for s in range(0, n_sample, chunk)]
+    t0 = time.perf_counter()
+    if procs > 1:
+        import multiprocessing as mp
+        for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+            os.environ[var] = "1"          # one BLAS thread per worker process (spawned children inherit)
+        with mp.get_context("spawn").Pool(procs) as pool:
+            res = pool.map(_cpu_chunk, jobs)
+    else:
+        res = [_cpu_chunk(j) for j in jobs]
+    wall = time.perf_counter() - t0
+    return n_sample / wall, wall, [r[1] for r in res]
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm (oracle port; the reference is
+    pure Python and cannot travel to the GPU box) on all host cores, each step a
+    bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    cores = os.cpu_count() or 1
+    procs = max(1, min(cores, 32))
+    gps = make_emulators()
+    dev = torch.device("cuda", 0) if torch.cuda.is_available() else None
+    n_sample = procs * 4 * 8192
+    if dev is not None:
+        rho, inv, mask = synth_on_device(gps, n_sample, 99, dev)
+    else:                                   # no GPU: numpy forward model from the oracle
+        from oracle.gp import GaussianProcess
+        from kafka_inferenceengine_b200 import synthetic as syn
+        rng = np.random.default_rng(99)
+        xt = syn.SAIL_MEAN + syn.SAIL_SIGMA * rng.standard_normal((n_sample, P))
+        r = np.array([GaussianProcess(g.inputs, g.targets, g.theta).predict(xt, do_unc=False)[0] for g in gps])
+        r = r * (1 + 0.05 * rng.standard_normal(r.shape))
+        mk = (r > 0) & (rng.random(r.shape) < 0.9)
+        r = np.where(mk, r, 0.0)
+        with np.errstate(divide="ignore"):
+            iv = np.where(mk, 1.0 / (0.05 * r) ** 2, np.inf)
+        rho, inv, mask = torch.from_numpy(r), torch.from_numpy(iv), torch.from_numpy(mk.astype(np.uint8))
+    times = []
+    for s in range(args.warmup + args.steps):
+        rate, wall, iters = cpu_baseline(gps, rho, inv, mask, n_sample, procs=procs, chunk=8192)
+        if s >= args.warmup:
+            times.append(wall)
+    ms = 1e3 * float(np.mean(times))
+    value = n_sample / (ms * 1e-3)
+    line = {"impl": "reference", "metric": "pixel-dates/sec", "value": value, "unit": "pixel-dates/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 build, f32 sparse LU",
+            "data": "synthetic",
+            "config": workload_config(args, note="bounded sample per step: %d px in %d chunks of 8192 px on %d "
+                                      "processes" % (n_sample, n_sample // 8192, procs)),
+            "cpu_baseline": {"value": value, "unit": "pixel-dates/s", "cores": procs, "kind": "port",
+                             "sample": "%d px per step, all bands, iterated to convergence (%s solves)"
+                                       % (n_sample, sorted(set(iters)))},
+            "e2e": {"value": value, "unit": "pixel-dates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def workload_config(args, note=None):
+    cfg = {"workload": "BASELINE configs[3] shard: full Sentinel-2 tile 10980x10980 px sharded by pixel over 8 GPUs "
+                       "= %d x %d px per GPU; 10-param PROSAIL state, 10 bands, 250-point GP emulator per band, "
+                       "iterated linearisation (tol 1e-3, >=2 solves), prior-only advance" % (args.rows, args.cols),
+           "pixels_per_gpu": args.rows * args.cols, "n_params": P, "n_bands": B, "n_train": T,
+           "l2_policy": "inputs larger than L2 (>2 GB of rasters per step vs 126 MB L2)"}
+    if note:
+        cfg["note"] = note
+    return cfg
+
+
+# --------------------------------------------------------------------------
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import kafka_inferenceengine_b200 as kb
+    from kafka_inferenceengine_b200 import _lib
+    from kafka_inferenceengine_b200 import synthetic as syn
+    from kafka_inferenceengine_b200.device import BlockDiag, DeviceVector
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d" % args.gpus)
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    comm = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+        comm = dist.group.WORLD
+
+    shape = (args.rows, args.cols)
+    n_pix = args.rows * args.cols
+    gps = make_emulators()
+    rho, inv, mask = synth_on_device(gps, n_pix, 1234 + rank, device)
+    state_mask = np.ones(shape, dtype=bool)
+    base = dt.datetime(2017, 7, 3)
+    date = base + dt.timedelta(hours=12)
+    grid = [base, base + dt.timedelta(days=1)]
+    inv_block = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
+
+    def make_filter(obs, out):
+        prior = syn.BroadcastPrior(syn.SAIL_MEAN, inv_block, n_pix, lambda blk, n: BlockDiag.from_block(blk, n, device))
+        kf = kb.LinearKalman(obs, out, state_mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS,
+                             state_propagation=None, prior=prior, linear=False, device=device, comm=comm)
+        kf.set_trajectory_model()
+        return kf, prior
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- value: inputs resident in HBM ------------------------
+    obs_dev = DeviceObservations([date], gps, rho, inv, mask, shape)
+    kf, prior = make_filter(obs_dev, NullOutput())
+    x0 = DeviceVector.broadcast(syn.SAIL_MEAN, n_pix, device)
+    Pinv0 = BlockDiag.from_block(inv_block, n_pix, device)
+    data = [obs_dev.get_band_data(date, b) for b in range(B)]
+
+    def step_resident():
+        return kf.do_all_bands(date, data, x0, None, Pinv0)
+
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    kf.profile = {}
+    kf.last_iterations = []
+    launches0 = _lib.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step_resident()
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    launches = _lib.launch_count - launches0
+    clocks = sampler.stop() if sampler else None
+    iters = list(kf.last_iterations)
+    prof = {k: [a.elapsed_time(b) for a, b in v] for k, v in kf.profile.items()}
+    kf.profile = None
+    ms_step = ms_total / args.steps
+    value = world * n_pix / (ms_step * 1e-3)
+
+    # ---------------- e2e: host rasters through LinearKalman.run -----------
+    e2e = None
+    if not args.no_e2e:
+        obs_host = HostObservations([date], gps, rho, inv, mask, shape)
+        out = ReadbackOutput()
+        kf2, prior2 = make_filter(obs_host, out)
+        kf2.set_trajectory_uncertainty(0.0)
+        x0h, Pinv0h = prior2.process_prior(None)
+        for _ in range(max(1, args.warmup - 1)):
+            kf2.run(grid, x0h, None, Pinv0h, iter_obs_op=True)
+        barrier()
+        h2d0, d2h0 = kf2._stager.h2d_bytes, out.d2h_bytes
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            kf2.run(grid, x0h, None, Pinv0h, iter_obs_op=True)
+        torch.cuda.synchronize()
+        ms_e2e = max_over_ranks(1e3 * (time.perf_counter() - t0)) / args.steps
+        barrier()
+        e2e = {"value": world * n_pix / (ms_e2e * 1e-3), "unit": "pixel-dates/s", "ms_per_step": ms_e2e,
+               "h2d_bytes_per_step": (kf2._stager.h2d_bytes - h2d0) // args.steps + x0h.nbytes,
+               "d2h_bytes_per_step": (out.d2h_bytes - d2h0) // args.steps,
+               "api": "LinearKalman.run(time_grid, x_forecast(host), None, P_forecast_inverse) with host rasters from "
+                      "observations.get_band_data and output.dump_data reading x and diag(P^-1) back"}
+        del kf2, obs_host
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---------------- roofline ---------------------------------------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    fp64_peak = None
+    try:
+        probe = ctypes.CDLL(os.path.join(ROOT, "benchmarks", "libkafka_probe.so"))
+        probe.kafka_probe_fp64_tflops.restype = ctypes.c_double
+        fp64_peak = float(probe.kafka_probe_fp64_tflops(5))
+    except OSError:
+        pass
+    gp_ms = float(np.mean(prof.get("gp_linearize", [float("nan")])))
+    sv_ms = float(np.mean(prof.get("solve_bands", [float("nan")])))
+    n_iter_mean = float(np.mean(iters))
+    gp_bytes = n_pix * (8 * P + B * (1 + 8 + 8 * P))            # x once, mask, h0, Jacobian out
+    gp_flops = n_pix * B * T * (5 * P + 28)
+    sv_bytes = n_pix * (BYTES_PER_PIXEL_DATE + 8 * B * P + 8 * B + 8 * P + 8 * B)   # + J, H0, x_prev in, innovations out
+    gp_tf = gp_flops / (gp_ms * 1e-3) / 1e12
+    roofline = {
+        "kernel": "gp_linearize_kernel<10,2> (GP emulator mean+Jacobian, all bands, one launch per iteration)",
+        "bound": "hbm",
+        "achieved": gp_bytes / (gp_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+        "frac": gp_bytes / (gp_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": gp_bytes, "ms_per_launch": gp_ms,
+        "share_of_step": gp_ms * n_iter_mean / ms_step,
+        "note": "this kernel is fp64-pipe bound, not HBM bound (SURVEY 8d: ~195 kflop vs ~1 kB per pixel-iteration); "
+                "the binding roofline is 'fp64' below",
+        "fp64": {"achieved": gp_tf, "peak": fp64_peak, "unit": "TFLOP/s (algorithmic: B*T*(5D+28) per pixel)",
+                 "frac": (gp_tf / fp64_peak) if fp64_peak else None,
+                 "peak_source": "DFMA probe measured in this run (benchmarks/probe.cu)"},
+        "solve_kernel": {"kernel": "solve_bands_kernel<10> (normal equations + Cholesky + partial norm)",
+                         "bound": "hbm", "achieved": sv_bytes / (sv_ms * 1e-3) / 1e9, "peak": hbm_peak,
+                         "unit": "GB/s", "frac": sv_bytes / (sv_ms * 1e-3) / 1e9 / hbm_peak,
+                         "algorithmic_bytes_per_launch": sv_bytes, "ms_per_launch": sv_ms},
+        "step": {"bytes_per_pixel_date": BYTES_PER_PIXEL_DATE,
+                 "achieved": n_pix * BYTES_PER_PIXEL_DATE / (ms_step * 1e-3) / 1e9, "unit": "GB/s",
+                 "frac": n_pix * BYTES_PER_PIXEL_DATE / (ms_step * 1e-3) / 1e9 / hbm_peak},
+    }
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        rate, wall, its = cpu_baseline(gps, rho, inv, mask, args.cpu_sample, procs=1)
+        cpu = {"value": rate, "unit": "pixel-dates/s", "cores": 1, "kind": "port",
+               "sample": "%d px of the same workload in chunks of 16384 px, all bands, iterated to convergence "
+                         "(%s solves), %.1f s; oracle A' = numpy GP + scipy.sparse build + float32 SuperLU as "
+                         "solvers.py:100-145" % (min(args.cpu_sample, n_pix), sorted(set(its)), wall)}
+
+    line = {"metric": "pixel-dates/sec", "value": value, "unit": "pixel-dates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args), "solver_iterations_per_step": iters,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

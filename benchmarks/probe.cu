@@ -1,0 +1,50 @@
+// Measurement aid (NOT part of the product ABI): fp64 FMA peak of the device, the
+// roofline denominator for the emulator kernel (MEASURED_PEAKS.json has no fp64
+// figure).  Each thread runs `iters` rounds of 8 independent dependent-FMA chains.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+__global__ void __launch_bounds__(256) fp64_fma_probe(double* out, int iters, double a, double b) {
+    double v0 = threadIdx.x * 1e-9, v1 = v0 + 1e-3, v2 = v0 + 2e-3, v3 = v0 + 3e-3;
+    double v4 = v0 + 4e-3, v5 = v0 + 5e-3, v6 = v0 + 6e-3, v7 = v0 + 7e-3;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            v0 = fma(v0, a, b); v1 = fma(v1, a, b); v2 = fma(v2, a, b); v3 = fma(v3, a, b);
+            v4 = fma(v4, a, b); v5 = fma(v5, a, b); v6 = fma(v6, a, b); v7 = fma(v7, a, b);
+        }
+    }
+    double s = v0 + v1 + v2 + v3 + v4 + v5 + v6 + v7;
+    if (s == 123.456) out[0] = s;     // never true; keeps the chains alive
+}
+
+extern "C" {
+// returns achieved TFLOP/s (2 flops per FMA), best of `reps`
+double kafka_probe_fp64_tflops(int reps) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    double* out = nullptr;
+    if (cudaMalloc(&out, 8) != cudaSuccess) return -1.0;
+    const int iters = 4096, threads = 256, blocks = sms * 8;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0.0;
+    for (int r = 0; r < reps + 1; ++r) {
+        cudaEventRecord(e0);
+        fp64_fma_probe<<<blocks, threads>>>(out, iters, 0.999999, 1e-7);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double flops = 2.0 * 8 * 16 * (double)iters * threads * blocks;
+        double tf = flops / (ms * 1e-3) / 1e12;
+        if (r > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    return best;
+}
+}

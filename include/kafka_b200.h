@@ -1,0 +1,209 @@
+/*
+ * kafka_b200.h -- C ABI of libkafka_b200.so: the B200 (sm_100a) implementation of
+ * KaFKA's per-pixel assimilation path.
+ *
+ * The reference (QCDIS/KaFKA-InferenceEngine) is pure Python: there is no FFI
+ * to mirror, so every entry point below names the reference FUNCTION it
+ * replaces (file:line relative to the reference root).  INTEGRATION.md shows the
+ * ctypes binding a maintainer would add to the reference.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every data pointer is a DEVICE pointer into
+ *    caller-owned memory unless the name ends in _host;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = default stream);
+ *  - return value: 0 = OK, <0 = bad argument (KAFKA_E_*), >0 = cudaError_t;
+ *    kafka_last_error() gives the text for the calling thread;
+ *  - nothing here allocates or frees device memory; scratch is passed in.
+ *
+ * Device layouts ("planar", pixel index fastest; `ld` = elements between planes,
+ * ld >= n_pix):
+ *  - state vector      x[p*ld + i]            p < n_params           (fp64)
+ *  - precision blocks  a[c*ld + i]            c = r(r+1)/2 + q, q<=r (fp64,
+ *                      packed lower triangle of the symmetric P x P block)
+ *  - per-band vectors  y[b*ld + i], w[b*ld + i], h0[b*ld + i]
+ *  - Jacobians         jac[(b*n_dim + d)*ld + i]   d = emulator input dimension
+ * The reference's interleaved vector x[n_params*i + p]
+ * (kafka/inference/utils.py:201) and its block-diagonal sparse matrices are
+ * converted at the boundary by the layout functions below.
+ */
+#ifndef KAFKA_B200_H
+#define KAFKA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KAFKA_MAX_PARAMS 16
+#define KAFKA_MAX_BANDS 16
+#define KAFKA_MAX_DIM 16
+
+#define KAFKA_E_BADARG (-1)
+#define KAFKA_E_UNSUPPORTED (-2)
+#define KAFKA_E_TOOLARGE (-3)
+
+/* band operator kinds for kafka_solve_bands */
+#define KAFKA_BAND_ARRAYS 0 /* h0/jac arrays (emulator output or supplied Jacobians) */
+#define KAFKA_BAND_LINEAR 1 /* constant row: H0 = row.x_prev + offset, J = row        */
+
+/* flags */
+#define KAFKA_ROUND_F32 1u      /* round H0/J to float32 as the reference stores them \
+                                   (kafka/inference/utils.py:193-195)                  */
+#define KAFKA_PRIOR_BROADCAST 2u /* pinv_f is ONE packed block shared by all pixels    */
+
+const char* kafka_last_error(void);
+int kafka_version(void);
+
+/* ---- a1: state-mask compaction and pixel indexing ------------------------
+ * Replaces `state_mask.sum()` (kafka/linear_kf.py:79-80) and the boolean-mask
+ * gathers `arr[state_mask]` (kafka/inference/solvers.py:90-92).  idx[k] = linear
+ * (row-major) raster index of the k-th True pixel.  `scratch` holds at least
+ * kafka_compact_scratch_elems(n_raster) int32; *n_true_host receives the count
+ * (the call synchronises the stream).  idx may be NULL to only count. */
+int64_t kafka_compact_scratch_elems(int64_t n_raster);
+int kafka_compact_mask(const uint8_t* mask, int64_t n_raster, int32_t* idx, int64_t idx_capacity,
+                       int32_t* scratch, int64_t* n_true_host, void* stream);
+
+/* Gather one band's rasters into compacted planar vectors, replacing
+ * sort_band_data's R/y/mask extraction (kafka/inference/solvers.py:90-93):
+ *   m = obs_mask[idx]; y = m ? obs[idx] : 0; w = m ? inv_var[idx] : 0
+ * (w is gated instead of multiplied: masked pixels carry inv_var = inf,
+ * kafka/input_output/Sentinel2_Observations.py:175-178).  m_out may be NULL. */
+int kafka_gather_band(const double* obs, const double* inv_var, const uint8_t* obs_mask,
+                      const int32_t* idx, int64_t n_pix, double* y, double* w, uint8_t* m_out,
+                      void* stream);
+
+/* Output stage, replaces KafkaOutput.dump_data's scatter
+ * (kafka/input_output/observations.py:374-375,392-393): for parameter p writes
+ * mean_raster[p][idx[i]] = (float)x[p][i] and, if diag is given,
+ * unc_raster[p][idx[i]] = (float)(1/sqrt(diag[p][i])).  Rasters (n_params x
+ * n_raster float32) must be zero-filled by the caller. */
+int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, int64_t n_pix,
+                         int n_params, const int32_t* idx, int64_t n_raster, float* mean_raster,
+                         float* unc_raster, void* stream);
+
+/* ---- layout conversion at the boundary -----------------------------------
+ * interleaved x[n_params*i+p] (kafka/inference/utils.py:201) <-> planar. */
+int kafka_interleaved_to_planar(const double* x_il, int64_t n_pix, int n_params, double* x_pl,
+                                int64_t ld, void* stream);
+int kafka_planar_to_interleaved(const double* x_pl, int64_t ld, int64_t n_pix, int n_params,
+                                double* x_il, void* stream);
+/* dense blocks[i][r][q] (what block_diag consumes, kafka/inference/utils.py:329-337)
+ * <-> packed planar; unpacking mirrors the lower triangle. */
+int kafka_blocks_to_packed(const double* blocks, int64_t n_pix, int n_params, double* a_packed,
+                           int64_t ld, void* stream);
+int kafka_packed_to_blocks(const double* a_packed, int64_t ld, int64_t n_pix, int n_params,
+                           double* blocks, void* stream);
+/* main diagonal of the block-diagonal matrix, interleaved like
+ * `P_analysis_inverse.diagonal()` (kafka/input_output/observations.py:393). */
+int kafka_packed_diagonal(const double* a_packed, int64_t ld, int64_t n_pix, int n_params,
+                          double* diag_il, void* stream);
+
+/* ---- a7: Gaussian-process emulator ----------------------------------------
+ * Host-side packing of one emulator (fields of gp_emulator.GaussianProcess:
+ * inputs[T][D], theta[D+2] = LOG hyper-parameters, invQt[T]) into the table the
+ * kernels stream through shared memory.  Table = kafka_gp_table_doubles(T,D)
+ * doubles: theta_e[D], centre[D], then T rows {zh[D], e, alpha}, padded to 16 B. */
+int64_t kafka_gp_table_doubles(int n_train, int n_dim);
+int kafka_gp_pack_host(const double* inputs_host, const double* theta_host,
+                       const double* invqt_host, int n_train, int n_dim, double* table_host);
+
+typedef struct {
+    const double* table;             /* device, from kafka_gp_pack_host         */
+    int32_t n_train;                 /* T                                        */
+    int32_t n_dim;                   /* D                                        */
+    int32_t mapper[KAFKA_MAX_DIM];   /* state slot feeding emulator input d
+                                        (kafka/inference/utils.py:148-153)       */
+} kafka_gp_band;
+
+/* Replaces run_emulator + gp.predict(x, do_unc=False)
+ * (kafka/inference/utils.py:68-106,206): for every pixel i and band b evaluates
+ * mean h0[b][i] and Jacobian jac[b][d][i] at x[mapper_b[d]][i].  All bands of one
+ * call share n_dim.  obs_mask (u8 [b*ld+i], may be NULL) zeroes rows of
+ * unobserved pixels (utils.py:199-215).  flags: KAFKA_ROUND_F32. */
+int kafka_gp_linearize(const double* x, int64_t ld, int64_t n_pix, const kafka_gp_band* bands_host,
+                       int n_bands, const uint8_t* obs_mask, double* h0, double* jac,
+                       uint32_t flags, void* stream);
+
+/* gp.predict on free-standing inputs xin[d*ld + i]: mean, optional Jacobian
+ * jac[d*ld+i], optional predictive variance (needs inv_q, the T x T inverse of
+ * the training covariance, row-major, device) -- the do_unc=True branch that
+ * the reference never takes on this path. */
+int kafka_gp_predict(const double* xin, int64_t ld, int64_t n_pts, const double* table,
+                     int n_train, int n_dim, const double* inv_q, double* mean, double* jac,
+                     double* var, void* stream);
+
+/* gp.hessian (kafka/inference/kf_tools.py:28): hess[(d*D+e)*ld + i]. */
+int kafka_gp_hessian(const double* xin, int64_t ld, int64_t n_pts, const double* table,
+                     int n_train, int n_dim, double* hess, void* stream);
+
+/* ---- a8/a9/a10: fused normal-equation build + Cholesky solve --------------- */
+typedef struct {
+    int32_t kind;                      /* KAFKA_BAND_ARRAYS / KAFKA_BAND_LINEAR              */
+    int32_t n_dim;                     /* ARRAYS: Jacobian planes of this band               */
+    int32_t mapper[KAFKA_MAX_DIM];     /* ARRAYS: state slot of Jacobian plane d             */
+    double row[KAFKA_MAX_PARAMS];      /* LINEAR: operator row                               */
+    double offset;                     /* LINEAR: H0 = row.x_prev + offset                   */
+    const double* h0;                  /* ARRAYS: [ld] device                                */
+    const double* jac;                 /* ARRAYS: [n_dim][ld] device                         */
+    const double* y;                   /* [ld] observations, 0 where unobserved              */
+    const double* w;                   /* [ld] inverse variance, 0 where unobserved          */
+} kafka_solve_band;
+
+int64_t kafka_solve_scratch_doubles(int64_t n_pix);
+
+/* One linearised update for every pixel, replacing sort_band_data +
+ * variational_kalman_multiband (kafka/inference/solvers.py:81-145) and the
+ * convergence norm of do_all_bands (kafka/linear_kf.py:293):
+ *     y'_b = y_b + J_b.x_prev - H0_b
+ *     A    = sum_b w_b J_b J_b^T + Pinv_f          (packed, written to a_out)
+ *     rhs  = sum_b w_b y'_b J_b + Pinv_f x_f
+ *     x    = A^-1 rhs   (fp64 Cholesky per pixel)   (written to x_out)
+ *     *norm2 = sum_i sum_p (x - x_prev)^2           (deterministic two-stage sum)
+ * Optional outputs (may be NULL): innovations[b*ld+i] = y_b - H0_b
+ * (solvers.py:142), fwd[b*ld+i] = J_b.(x - x_f) + H0_b (solvers.py:137),
+ * n_bad = number of pixels whose block was not positive definite (their x is
+ * left at x_f).  `scratch` holds kafka_solve_scratch_doubles(n_pix) doubles.
+ * flags: KAFKA_PRIOR_BROADCAST. */
+int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve_band* bands_host,
+                      int n_bands, const double* x_prev, const double* x_f, const double* pinv_f,
+                      double* x_out, double* a_out, double* innovations, double* fwd,
+                      double* norm2, int32_t* n_bad, double* scratch, uint32_t flags,
+                      void* stream);
+
+/* ---- a12-a17: advance / propagation ----------------------------------------
+ * propagate_information_filter_LAI (kafka/inference/kf_tools.py:292-314),
+ * generalised from its hard-coded 7-parameter TIP prior: every slot is reset to
+ * prior_mean_host except `carry_slot`, whose value is carried over and whose
+ * precision becomes 1/(1/a[slot,slot] + q[slot]); the block is
+ * prior_inv_host (n_params^2, row-major) elsewhere.  Block values are rounded to
+ * float32 like the reference's block_diag(..., dtype=float32) (:312). */
+int kafka_advance_carry_slot(const double* x_a, const double* a_packed, const double* q,
+                             int64_t ld, int64_t n_pix, int n_params, int carry_slot,
+                             const double* prior_mean_host, const double* prior_inv_host,
+                             double* x_f, double* pinv_f, void* stream);
+/* propagate_information_filter_approx_SLOW (kf_tools.py:247-289): diagonal
+ * m/(1+m q), off-diagonals dropped. */
+int kafka_advance_approx(const double* a_packed, const double* q, int64_t ld, int64_t n_pix,
+                         int n_params, double* pinv_f, void* stream);
+/* propagate_information_filter_SLOW (kf_tools.py:208-245): (I + Pinv Q)^-1 Pinv
+ * per block. */
+int kafka_advance_exact(const double* a_packed, const double* q, int64_t ld, int64_t n_pix,
+                        int n_params, double* pinv_f, int32_t* n_bad, void* stream);
+/* propagate_standard_kalman (kf_tools.py:174-205) for diagonal M:
+ * x_f = m*x_a, P_f = P_a + diag(q).  m may be NULL (identity). */
+int kafka_advance_standard(const double* x_a, const double* p_packed, const double* m,
+                           const double* q, int64_t ld, int64_t n_pix, int n_params, double* x_f,
+                           double* p_f, void* stream);
+/* blend_prior (kf_tools.py:75-96) including its cross-weighted right-hand side
+ * b = Pinv_f mu_prior + Cinv_prior x_f (:90).  prior_* may be broadcast (one
+ * vector / one packed block) when KAFKA_PRIOR_BROADCAST is set. */
+int kafka_blend_prior(const double* prior_mean, const double* prior_inv, const double* x_f,
+                      const double* pinv_f, int64_t ld, int64_t n_pix, int n_params, double* x_out,
+                      double* c_out, int32_t* n_bad, uint32_t flags, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KAFKA_B200_H */

@@ -1,0 +1,137 @@
+"""ctypes binding of libkafka_b200.so (declarations: include/kafka_b200.h).
+
+There is NO fallback: if the library is missing the import of any compute path
+raises, and every non-zero status from the library raises ``KafkaCudaError``.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libkafka_b200.so")
+
+MAX_PARAMS = 16
+MAX_BANDS = 16
+MAX_DIM = 16
+BAND_ARRAYS = 0
+BAND_LINEAR = 1
+ROUND_F32 = 1
+PRIOR_BROADCAST = 2
+
+
+class KafkaCudaError(RuntimeError):
+    pass
+
+
+class GpBand(C.Structure):
+    _fields_ = [("table", C.c_void_p), ("n_train", C.c_int32), ("n_dim", C.c_int32),
+                ("mapper", C.c_int32 * MAX_DIM)]
+
+
+class SolveBand(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("n_dim", C.c_int32), ("mapper", C.c_int32 * MAX_DIM),
+                ("row", C.c_double * MAX_PARAMS), ("offset", C.c_double),
+                ("h0", C.c_void_p), ("jac", C.c_void_p), ("y", C.c_void_p), ("w", C.c_void_p)]
+
+
+_p, _i64, _i32, _u32 = C.c_void_p, C.c_int64, C.c_int, C.c_uint32
+
+# name -> (restype, argtypes).  Every symbol declared in include/kafka_b200.h.
+SIGNATURES = {
+    "kafka_last_error": (C.c_char_p, []),
+    "kafka_version": (C.c_int, []),
+    "kafka_compact_scratch_elems": (_i64, [_i64]),
+    "kafka_compact_mask": (C.c_int, [_p, _i64, _p, _i64, _p, C.POINTER(C.c_int64), _p]),
+    "kafka_gather_band": (C.c_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p]),
+    "kafka_scatter_output": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p, _p, _p]),
+    "kafka_interleaved_to_planar": (C.c_int, [_p, _i64, _i32, _p, _i64, _p]),
+    "kafka_planar_to_interleaved": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
+    "kafka_blocks_to_packed": (C.c_int, [_p, _i64, _i32, _p, _i64, _p]),
+    "kafka_packed_to_blocks": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
+    "kafka_packed_diagonal": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
+    "kafka_gp_table_doubles": (_i64, [_i32, _i32]),
+    "kafka_gp_pack_host": (C.c_int, [_p, _p, _p, _i32, _i32, _p]),
+    "kafka_gp_linearize": (C.c_int, [_p, _i64, _i64, C.POINTER(GpBand), _i32, _p, _p, _p, _u32, _p]),
+    "kafka_gp_predict": (C.c_int, [_p, _i64, _i64, _p, _i32, _i32, _p, _p, _p, _p, _p]),
+    "kafka_gp_hessian": (C.c_int, [_p, _i64, _i64, _p, _i32, _i32, _p, _p]),
+    "kafka_solve_scratch_doubles": (_i64, [_i64]),
+    "kafka_solve_bands": (C.c_int, [_i64, _i64, _i32, C.POINTER(SolveBand), _i32, _p, _p, _p, _p, _p, _p, _p,
+                                    _p, _p, _p, _u32, _p]),
+    "kafka_advance_carry_slot": (C.c_int, [_p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _p, _p, _p]),
+    "kafka_advance_approx": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p]),
+    "kafka_advance_exact": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p, _p]),
+    "kafka_advance_standard": (C.c_int, [_p, _p, _p, _p, _i64, _i64, _i32, _p, _p, _p]),
+    "kafka_blend_prior": (C.c_int, [_p, _p, _p, _p, _i64, _i64, _i32, _p, _p, _p, _u32, _p]),
+}
+
+_lib = None
+
+
+def get_lib():
+    """Load the CUDA library or raise (no CPU path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "libkafka_b200.so is not built (%s). Run `python -m kafka_inferenceengine_b200.build` "
+            "(needs nvcc); this package has no CPU fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+# kernels launched by one successful call of each entry point (for bench.py's
+# gpu_launches count; the set of kernels is in csrc/*.cu)
+KERNELS_PER_CALL = {"kafka_compact_mask": 3, "kafka_solve_bands": 2}
+launch_count = 0
+
+
+def check(status, what):
+    global launch_count
+    if status == 0 and not what.endswith("_host"):
+        name = what.split("(")[0]
+        launch_count += 2 if name == "kafka_compact_mask" and what.endswith("(count)") else \
+            KERNELS_PER_CALL.get(name, 1)
+    if status != 0:
+        msg = get_lib().kafka_last_error().decode("utf-8", "replace")
+        raise KafkaCudaError("%s failed with status %d: %s" % (what, status, msg))
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (or None)."""
+    if t is None:
+        return None
+    return C.c_void_p(t.data_ptr())
+
+
+def np_ptr(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def gp_pack(inputs, theta, invqt):
+    """Host-side table for one emulator (kafka_gp_pack_host)."""
+    lib = get_lib()
+    inputs = np.ascontiguousarray(inputs, dtype=np.float64)
+    theta = np.ascontiguousarray(theta, dtype=np.float64)
+    invqt = np.ascontiguousarray(invqt, dtype=np.float64)
+    T, D = inputs.shape
+    if theta.shape != (D + 2,) or invqt.shape != (T,):
+        raise ValueError("emulator fields have inconsistent shapes")
+    n = lib.kafka_gp_table_doubles(T, D)
+    if n < 0:
+        raise ValueError("emulator with T=%d, D=%d is not supported (D <= %d)" % (T, D, MAX_DIM))
+    table = np.empty(n, dtype=np.float64)
+    check(lib.kafka_gp_pack_host(np_ptr(inputs), np_ptr(theta), np_ptr(invqt), T, D, np_ptr(table)),
+          "kafka_gp_pack_host")
+    return table

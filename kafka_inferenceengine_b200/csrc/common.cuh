@@ -1,0 +1,66 @@
+// Shared helpers for libkafka_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/kafka_b200.h"
+
+namespace kafka {
+
+void set_error(const char* fmt, ...);
+
+#define KAFKA_CHECK_ARG(cond, ...)                \
+    do {                                          \
+        if (!(cond)) {                            \
+            kafka::set_error(__VA_ARGS__);        \
+            return KAFKA_E_BADARG;                \
+        }                                         \
+    } while (0)
+
+#define KAFKA_CUDA(call)                                                              \
+    do {                                                                              \
+        cudaError_t e_ = (call);                                                      \
+        if (e_ != cudaSuccess) {                                                      \
+            kafka::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                             __FILE__, __LINE__);                                     \
+            return (int)e_;                                                           \
+        }                                                                             \
+    } while (0)
+
+inline int launch_status(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("launch of %s failed: %s", what, cudaGetErrorString(e));
+        return (int)e;
+    }
+    return 0;
+}
+
+inline int num_sms() {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+            sms = 148;  // B200
+    }
+    return sms;
+}
+
+__host__ __device__ constexpr int tri(int r, int q) { return r * (r + 1) / 2 + q; }
+__host__ __device__ constexpr int tri_count(int p) { return p * (p + 1) / 2; }
+
+// streaming (read-once) global loads/stores: keep them out of L1
+__device__ __forceinline__ double ldg_stream(const double* p) { return __ldcs(p); }
+__device__ __forceinline__ void stg_stream(double* p, double v) { __stcs(p, v); }
+
+__device__ __forceinline__ double round_f32(double v) { return (double)(float)v; }
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace kafka

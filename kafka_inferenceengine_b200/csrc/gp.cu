@@ -1,0 +1,471 @@
+// Gaussian-process (ARD squared-exponential) emulator kernels for sm_100a.
+//
+// Replaces run_emulator + gp.predict / gp.hessian of the reference
+// (kafka/inference/utils.py:68-106,206; kafka/inference/kf_tools.py:28).
+//
+// Maths (see include/kafka_b200.h and oracle/gp.py).  With a per-emulator centre c,
+// X' = X - c, x' = x - c, zh_jd = theta_d X'_jd:
+//     k_j   = exp( e_j - 0.5 sum_d theta_d x'_d^2 + sum_d zh_jd x'_d ),
+//             e_j = ln s_f - 0.5 sum_d theta_d X'_jd^2
+//     w_j   = k_j alpha_j,   mean = sum_j w_j,   G_d = sum_j w_j zh_jd
+//     dmean/dx_d = G_d - theta_d x'_d mean
+// i.e. 2D+3 fp64 FMAs + one exp per (pixel, band, training point); the training
+// table (T rows of {zh[D], e, alpha}) is staged once per CTA in shared memory by
+// a TMA bulk copy and then read as warp-wide broadcasts.  The kernel is bound by
+// the fp64 pipe, not by HBM.
+#include <math.h>
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace kafka {
+
+__constant__ double c_exp2_tab[32] = {
+#include "exp_table.inc"
+};
+
+// ---- table layout -----------------------------------------------------------
+__host__ __device__ constexpr int dpad(int D) { return (D + 1) & ~1; }
+__host__ __device__ constexpr int tab_hdr(int D) { return 2 * dpad(D) + 2; }   // theta_e, centre, s_f, nugget
+__host__ __device__ constexpr int tab_row(int D) { return dpad(D) + 2; }       // zh[DP], e, alpha
+
+// ---- mbarrier / TMA bulk copy (global -> shared) -------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    }
+}
+
+// ---- exp: 2^(k/32) table + degree-6 polynomial, ~11 fp64 ops --------------------
+// |rel err| < 4e-16 on [-708, 709]; underflows to 0 below, NaN propagates.
+__device__ __forceinline__ double fast_exp(double x, const double* __restrict__ tab32) {
+    const double kL = 4.61662413084468283841e+01;        // 32/ln2
+    const double kC1 = 2.16608493865351192653e-02;       // ln2/32, high bits (k*C1 exact)
+    const double kC2 = 5.96317165397058656257e-12;       // ln2/32 - C1
+    const double kMagic = 6755399441055744.0;            // 1.5 * 2^52
+    double t = fma(x, kL, kMagic);
+    int k = __double2loint(t);
+    double kd = t - kMagic;
+    double r = fma(kd, -kC1, x);
+    r = fma(kd, -kC2, r);
+    double p = fma(r, 1.0 / 720.0, 1.0 / 120.0);
+    p = fma(p, r, 1.0 / 24.0);
+    p = fma(p, r, 1.0 / 6.0);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    double v = tab32[k & 31] * p;
+    int hi = __double2hiint(v) + ((k >> 5) << 20);
+    double res = __hiloint2double(hi, __double2loint(v));
+    if (!(x >= -708.0)) res = (x != x) ? x : 0.0;
+    if (x > 709.0) res = CUDART_INF;
+    return res;
+}
+
+// ---- linearise: mean + Jacobian for every (pixel, band) -------------------------
+struct GpBandDev {
+    const double* table;
+    int n_train;
+    int mapper[KAFKA_MAX_DIM];
+};
+struct GpLinParams {
+    GpBandDev bands[KAFKA_MAX_BANDS];
+    const double* x;
+    const uint8_t* obs_mask;
+    double* h0;
+    double* jac;
+    int64_t ld;
+    int64_t n_pix;
+    uint32_t flags;
+};
+
+constexpr int kGpThreads = 128;
+
+template <int D, int PPT>
+__global__ void __launch_bounds__(kGpThreads)
+gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
+    constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
+    extern __shared__ __align__(16) double smem[];
+    __shared__ uint64_t bar;
+    __shared__ double s_exp[32];
+
+    const GpBandDev& band = prm.bands[blockIdx.y];
+    const int T = band.n_train;
+    const uint32_t bytes = (uint32_t)((HDR + T * RS) * sizeof(double));
+
+    if (threadIdx.x == 0) mbar_init(&bar, 1);
+    if (threadIdx.x < 32) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(&bar, bytes);
+        constexpr uint32_t kChunk = 16384;
+        for (uint32_t off = 0; off < bytes; off += kChunk)
+            tma_bulk_g2s(reinterpret_cast<char*>(smem) + off, reinterpret_cast<const char*>(band.table) + off,
+                         min(kChunk, bytes - off), &bar);
+    }
+
+    // pixel states while the table is in flight
+    const int64_t tile0 = (int64_t)blockIdx.x * (kGpThreads * PPT);
+    int64_t pix[PPT];
+    bool live[PPT];
+    double xr[PPT][D];
+    bool any_live = false;
+#pragma unroll
+    for (int pp = 0; pp < PPT; ++pp) {
+        pix[pp] = tile0 + pp * kGpThreads + threadIdx.x;
+        bool in = pix[pp] < prm.n_pix;
+        live[pp] = in && (prm.obs_mask == nullptr || prm.obs_mask[(int64_t)blockIdx.y * prm.ld + pix[pp]] != 0);
+        any_live |= live[pp];
+#pragma unroll
+        for (int d = 0; d < D; ++d)
+            xr[pp][d] = in ? prm.x[(int64_t)band.mapper[d] * prm.ld + pix[pp]] : 0.0;
+    }
+
+    mbar_wait(&bar, 0);
+
+    const double* theta_e = smem;
+    const double* centre = smem + DP;
+    const double* rows = smem + HDR;
+
+    double sh[PPT], mu[PPT], G[PPT][D];
+#pragma unroll
+    for (int pp = 0; pp < PPT; ++pp) {
+        double s = 0.0;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            xr[pp][d] -= centre[d];
+            s = fma(theta_e[d] * xr[pp][d], xr[pp][d], s);
+            G[pp][d] = 0.0;
+        }
+        sh[pp] = -0.5 * s;
+        mu[pp] = 0.0;
+    }
+
+    if (__any_sync(0xffffffffu, any_live)) {
+#pragma unroll 2
+        for (int j = 0; j < T; ++j) {
+            const double* row = rows + j * RS;
+            double zh[DP];
+#pragma unroll
+            for (int d = 0; d < DP; d += 2) {
+                double2 v = *reinterpret_cast<const double2*>(row + d);
+                zh[d] = v.x;
+                zh[d + 1] = v.y;
+            }
+            double2 ea = *reinterpret_cast<const double2*>(row + DP);
+#pragma unroll
+            for (int pp = 0; pp < PPT; ++pp) {
+                double a0 = ea.x + sh[pp], a1 = 0.0;
+#pragma unroll
+                for (int d = 0; d + 1 < D; d += 2) {
+                    a0 = fma(zh[d], xr[pp][d], a0);
+                    a1 = fma(zh[d + 1], xr[pp][d + 1], a1);
+                }
+                if (D & 1) a0 = fma(zh[D - 1], xr[pp][D - 1], a0);
+                double w = fast_exp(a0 + a1, s_exp) * ea.y;
+                mu[pp] += w;
+#pragma unroll
+                for (int d = 0; d < D; ++d) G[pp][d] = fma(w, zh[d], G[pp][d]);
+            }
+        }
+    }
+
+    const bool r32 = (prm.flags & KAFKA_ROUND_F32) != 0;
+#pragma unroll
+    for (int pp = 0; pp < PPT; ++pp) {
+        if (pix[pp] >= prm.n_pix) continue;
+        double m = live[pp] ? mu[pp] : 0.0;
+        prm.h0[(int64_t)blockIdx.y * prm.ld + pix[pp]] = r32 ? round_f32(m) : m;
+        if (prm.jac) {
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                double g = live[pp] ? G[pp][d] - theta_e[d] * xr[pp][d] * mu[pp] : 0.0;
+                prm.jac[((int64_t)blockIdx.y * D + d) * prm.ld + pix[pp]] = r32 ? round_f32(g) : g;
+            }
+        }
+    }
+}
+
+// ---- Hessian: hess_de = sum_j w_j u_jd u_je - delta_de theta_d mean, u_jd = zh_jd - theta_d x'_d
+template <int D>
+__global__ void __launch_bounds__(kGpThreads)
+gp_hessian_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, const double* __restrict__ table, int T,
+                  double* __restrict__ hess) {
+    constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D), L = tri_count(D);
+    extern __shared__ __align__(16) double smem[];
+    __shared__ double s_exp[32];
+    const int total = HDR + T * RS;
+    for (int k = threadIdx.x; k < total; k += kGpThreads) smem[k] = table[k];
+    if (threadIdx.x < 32) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    __syncthreads();
+    int64_t i = (int64_t)blockIdx.x * kGpThreads + threadIdx.x;
+    if (i >= n_pts) return;
+    const double* theta_e = smem;
+    const double* centre = smem + DP;
+    const double* rows = smem + HDR;
+    double xr[D], tx[D], acc[L], mu = 0.0, s = 0.0;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        xr[d] = xin[(int64_t)d * ld + i] - centre[d];
+        tx[d] = theta_e[d] * xr[d];
+        s = fma(tx[d], xr[d], s);
+    }
+#pragma unroll
+    for (int c = 0; c < L; ++c) acc[c] = 0.0;
+    const double sh = -0.5 * s;
+    for (int j = 0; j < T; ++j) {
+        const double* row = rows + j * RS;
+        double a = row[DP] + sh, u[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            a = fma(row[d], xr[d], a);
+            u[d] = row[d] - tx[d];
+        }
+        double w = fast_exp(a, s_exp) * row[DP + 1];
+        mu += w;
+#pragma unroll
+        for (int r = 0; r < D; ++r) {
+            double wu = w * u[r];
+#pragma unroll
+            for (int q = 0; q <= r; ++q) acc[tri(r, q)] = fma(wu, u[q], acc[tri(r, q)]);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < D; ++r)
+#pragma unroll
+        for (int q = 0; q <= r; ++q) {
+            double v = acc[tri(r, q)] - (r == q ? theta_e[r] * mu : 0.0);
+            hess[((int64_t)r * D + q) * ld + i] = v;
+            hess[((int64_t)q * D + r) * ld + i] = v;
+        }
+}
+
+// ---- predictive variance: s_f - k^T Q^-1 k, one warp per point ---------------------
+__global__ void __launch_bounds__(128)
+gp_variance_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, const double* __restrict__ table, int T,
+                   int D, const double* __restrict__ inv_q, double* __restrict__ var) {
+    extern __shared__ double kbuf[];             // [4 warps][T]
+    __shared__ double s_exp[32];
+    if (threadIdx.x < 32) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    __syncthreads();
+    const int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int64_t i = (int64_t)blockIdx.x * 4 + wid;
+    if (i >= n_pts) return;
+    double* kv = kbuf + (size_t)wid * T;
+    double s = 0.0;
+    for (int d = 0; d < D; ++d) {
+        double xc = xin[(int64_t)d * ld + i] - table[DP + d];
+        s = fma(table[d] * xc, xc, s);
+    }
+    for (int j = lane; j < T; j += 32) {
+        const double* row = table + HDR + (size_t)j * RS;
+        double a = row[DP] - 0.5 * s;
+        for (int d = 0; d < D; ++d) a = fma(row[d], xin[(int64_t)d * ld + i] - table[DP + d], a);
+        kv[j] = fast_exp(a, s_exp);
+    }
+    __syncwarp();
+    double acc = 0.0;
+    for (int r = 0; r < T; ++r) {
+        const double* qrow = inv_q + (size_t)r * T;
+        double part = 0.0;
+        for (int j = lane; j < T; j += 32) part = fma(qrow[j], kv[j], part);
+        part = warp_sum(part);
+        acc = fma(kv[r], part, acc);
+    }
+    if (lane == 0) var[i] = table[2 * DP] - acc;
+}
+
+template <int D, int PPT>
+static int launch_linearize(const GpLinParams& prm, int n_bands, int max_T, cudaStream_t s) {
+    size_t smem = (size_t)(tab_hdr(D) + max_T * tab_row(D)) * sizeof(double);
+    if (smem > 200 * 1024) {
+        set_error("kafka_gp_linearize: training table of %zu bytes does not fit shared memory", smem);
+        return KAFKA_E_TOOLARGE;
+    }
+    auto kern = gp_linearize_kernel<D, PPT>;
+    KAFKA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((prm.n_pix + kGpThreads * PPT - 1) / (kGpThreads * PPT)), (unsigned)n_bands);
+    kern<<<grid, kGpThreads, smem, s>>>(prm);
+    return launch_status("gp_linearize_kernel");
+}
+
+template <int D>
+static int dispatch_ppt(const GpLinParams& prm, int n_bands, int max_T, cudaStream_t s) {
+    // two pixels per thread halve the shared-memory operand traffic per FMA; only
+    // worth it when the grid still fills the machine several times over
+    int64_t ctas2 = (prm.n_pix + 2 * kGpThreads - 1) / (2 * kGpThreads) * n_bands;
+    if (ctas2 >= 8 * (int64_t)num_sms()) return launch_linearize<D, 2>(prm, n_bands, max_T, s);
+    return launch_linearize<D, 1>(prm, n_bands, max_T, s);
+}
+
+#define KAFKA_DISPATCH_D(D_, ...) \
+    switch (D_) { \
+        case 1: { constexpr int kD = 1; __VA_ARGS__; } break; \
+        case 2: { constexpr int kD = 2; __VA_ARGS__; } break; \
+        case 3: { constexpr int kD = 3; __VA_ARGS__; } break; \
+        case 4: { constexpr int kD = 4; __VA_ARGS__; } break; \
+        case 5: { constexpr int kD = 5; __VA_ARGS__; } break; \
+        case 6: { constexpr int kD = 6; __VA_ARGS__; } break; \
+        case 7: { constexpr int kD = 7; __VA_ARGS__; } break; \
+        case 8: { constexpr int kD = 8; __VA_ARGS__; } break; \
+        case 9: { constexpr int kD = 9; __VA_ARGS__; } break; \
+        case 10: { constexpr int kD = 10; __VA_ARGS__; } break; \
+        case 11: { constexpr int kD = 11; __VA_ARGS__; } break; \
+        case 12: { constexpr int kD = 12; __VA_ARGS__; } break; \
+        case 13: { constexpr int kD = 13; __VA_ARGS__; } break; \
+        case 14: { constexpr int kD = 14; __VA_ARGS__; } break; \
+        case 15: { constexpr int kD = 15; __VA_ARGS__; } break; \
+        case 16: { constexpr int kD = 16; __VA_ARGS__; } break; \
+        default: break; \
+    }
+
+}  // namespace kafka
+
+using namespace kafka;
+
+extern "C" {
+
+int64_t kafka_gp_table_doubles(int n_train, int n_dim) {
+    if (n_train < 1 || n_dim < 1 || n_dim > KAFKA_MAX_DIM) return -1;
+    return (int64_t)tab_hdr(n_dim) + (int64_t)n_train * tab_row(n_dim);
+}
+
+int kafka_gp_pack_host(const double* inputs, const double* theta, const double* invqt, int T, int D,
+                       double* table) {
+    KAFKA_CHECK_ARG(inputs && theta && invqt && table, "kafka_gp_pack_host: null pointer");
+    KAFKA_CHECK_ARG(T >= 1 && D >= 1 && D <= KAFKA_MAX_DIM, "kafka_gp_pack_host: T=%d D=%d unsupported", T, D);
+    const int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
+    for (int k = 0; k < HDR + T * RS; ++k) table[k] = 0.0;
+    double* theta_e = table;
+    double* centre = table + DP;
+    for (int d = 0; d < D; ++d) {
+        theta_e[d] = exp(theta[d]);
+        long double s = 0;
+        for (int j = 0; j < T; ++j) s += inputs[(size_t)j * D + d];
+        centre[d] = (double)(s / T);
+    }
+    table[2 * DP] = exp(theta[D]);
+    table[2 * DP + 1] = exp(theta[D + 1]);
+    for (int j = 0; j < T; ++j) {
+        double* row = table + HDR + (size_t)j * RS;
+        double c = 0.0;
+        for (int d = 0; d < D; ++d) {
+            double xc = inputs[(size_t)j * D + d] - centre[d];
+            row[d] = theta_e[d] * xc;
+            c = fma(row[d], xc, c);
+        }
+        row[DP] = theta[D] - 0.5 * c;
+        row[DP + 1] = invqt[j];
+    }
+    return 0;
+}
+
+int kafka_gp_linearize(const double* x, int64_t ld, int64_t n_pix, const kafka_gp_band* bands, int n_bands,
+                       const uint8_t* obs_mask, double* h0, double* jac, uint32_t flags, void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "kafka_gp_linearize: need 0 <= n_pix <= ld");
+    KAFKA_CHECK_ARG(n_bands >= 1 && n_bands <= KAFKA_MAX_BANDS, "kafka_gp_linearize: n_bands=%d outside 1..%d", n_bands,
+                    KAFKA_MAX_BANDS);
+    KAFKA_CHECK_ARG(bands, "kafka_gp_linearize: bands is null");
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(x && h0, "kafka_gp_linearize: null pointer");
+    GpLinParams prm;
+    memset(&prm, 0, sizeof(prm));
+    const int D = bands[0].n_dim;
+    KAFKA_CHECK_ARG(D >= 1 && D <= KAFKA_MAX_DIM, "kafka_gp_linearize: n_dim=%d outside 1..%d", D, KAFKA_MAX_DIM);
+    int max_T = 0;
+    for (int b = 0; b < n_bands; ++b) {
+        KAFKA_CHECK_ARG(bands[b].n_dim == D, "kafka_gp_linearize: all bands of one call must share n_dim");
+        KAFKA_CHECK_ARG(bands[b].table && bands[b].n_train >= 1, "kafka_gp_linearize: band %d has no table", b);
+        KAFKA_CHECK_ARG((reinterpret_cast<uintptr_t>(bands[b].table) & 15u) == 0,
+                        "kafka_gp_linearize: band %d table must be 16-byte aligned", b);
+        prm.bands[b].table = bands[b].table;
+        prm.bands[b].n_train = bands[b].n_train;
+        for (int d = 0; d < D; ++d) {
+            KAFKA_CHECK_ARG(bands[b].mapper[d] >= 0, "kafka_gp_linearize: negative mapper entry");
+            prm.bands[b].mapper[d] = bands[b].mapper[d];
+        }
+        max_T = bands[b].n_train > max_T ? bands[b].n_train : max_T;
+    }
+    prm.x = x;
+    prm.obs_mask = obs_mask;
+    prm.h0 = h0;
+    prm.jac = jac;
+    prm.ld = ld;
+    prm.n_pix = n_pix;
+    prm.flags = flags;
+    int rc = KAFKA_E_UNSUPPORTED;
+    KAFKA_DISPATCH_D(D, rc = dispatch_ppt<kD>(prm, n_bands, max_T, (cudaStream_t)stream));
+    return rc;
+}
+
+int kafka_gp_predict(const double* xin, int64_t ld, int64_t n_pts, const double* table, int n_train, int n_dim,
+                     const double* inv_q, double* mean, double* jac, double* var, void* stream) {
+    KAFKA_CHECK_ARG(n_dim >= 1 && n_dim <= KAFKA_MAX_DIM, "kafka_gp_predict: n_dim=%d", n_dim);
+    KAFKA_CHECK_ARG(!var || inv_q, "kafka_gp_predict: variance requested without inv_q");
+    if (n_pts == 0) return 0;
+    KAFKA_CHECK_ARG(mean, "kafka_gp_predict: mean is null");
+    kafka_gp_band band;
+    band.table = table;
+    band.n_train = n_train;
+    band.n_dim = n_dim;
+    for (int d = 0; d < KAFKA_MAX_DIM; ++d) band.mapper[d] = d;
+    int rc = kafka_gp_linearize(xin, ld, n_pts, &band, 1, nullptr, mean, jac, 0u, stream);
+    if (rc != 0 || !var) return rc;
+    size_t smem = (size_t)4 * n_train * sizeof(double);
+    KAFKA_CUDA(cudaFuncSetAttribute(gp_variance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gp_variance_kernel<<<(unsigned)((n_pts + 3) / 4), 128, smem, (cudaStream_t)stream>>>(xin, ld, n_pts, table, n_train,
+                                                                                       n_dim, inv_q, var);
+    return launch_status("gp_variance_kernel");
+}
+
+int kafka_gp_hessian(const double* xin, int64_t ld, int64_t n_pts, const double* table, int n_train, int n_dim,
+                     double* hess, void* stream) {
+    KAFKA_CHECK_ARG(n_dim >= 1 && n_dim <= KAFKA_MAX_DIM, "kafka_gp_hessian: n_dim=%d", n_dim);
+    KAFKA_CHECK_ARG(n_pts >= 0 && ld >= n_pts, "kafka_gp_hessian: need 0 <= n_pts <= ld");
+    if (n_pts == 0) return 0;
+    KAFKA_CHECK_ARG(xin && table && hess && n_train >= 1, "kafka_gp_hessian: null pointer");
+    size_t smem = (size_t)(tab_hdr(n_dim) + n_train * tab_row(n_dim)) * sizeof(double);
+    if (smem > 200 * 1024) {
+        set_error("kafka_gp_hessian: training table of %zu bytes does not fit shared memory", smem);
+        return KAFKA_E_TOOLARGE;
+    }
+    int rc = KAFKA_E_UNSUPPORTED;
+    unsigned grid = (unsigned)((n_pts + kGpThreads - 1) / kGpThreads);
+    KAFKA_DISPATCH_D(n_dim, {
+        auto kern = gp_hessian_kernel<kD>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) {
+            set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+            rc = (int)e;
+        } else {
+            kern<<<grid, kGpThreads, smem, (cudaStream_t)stream>>>(xin, ld, n_pts, table, n_train, hess);
+            rc = launch_status("gp_hessian_kernel");
+        }
+    });
+    return rc;
+}
+
+}  // extern "C"

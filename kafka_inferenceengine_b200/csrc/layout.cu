@@ -1,0 +1,341 @@
+// State-mask compaction, pixel indexing and boundary layout conversion (sm_100a).
+// All of it is HBM-bound byte/index work: coalesced loads, shared-memory
+// transposes, no tensor cores.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace kafka {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// ---------------------------------------------------------------------------
+// compaction: count -> scan -> write
+// ---------------------------------------------------------------------------
+constexpr int kCompactThreads = 256;
+constexpr int kCompactPerThread = 16;
+constexpr int kCompactTile = kCompactThreads * kCompactPerThread;  // 4096 mask bytes / CTA
+
+__device__ __forceinline__ uint32_t load_mask_bits(const uint8_t* __restrict__ mask, int64_t base,
+                                                   int64_t n, bool aligned) {
+    // bit k of the result = mask[base + k] != 0, k < 16
+    uint32_t bits = 0;
+    if (aligned && base + kCompactPerThread <= n) {
+        uint4 v = __ldcs(reinterpret_cast<const uint4*>(mask + base));
+        uint32_t wds[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int wi = 0; wi < 4; ++wi)
+#pragma unroll
+            for (int b = 0; b < 4; ++b)
+                bits |= (((wds[wi] >> (8 * b)) & 0xffu) != 0u ? 1u : 0u) << (wi * 4 + b);
+    } else {
+        for (int k = 0; k < kCompactPerThread; ++k)
+            if (base + k < n && mask[base + k] != 0) bits |= 1u << k;
+    }
+    return bits;
+}
+
+__global__ void __launch_bounds__(kCompactThreads)
+compact_count_kernel(const uint8_t* __restrict__ mask, int64_t n, int32_t* __restrict__ block_counts,
+                     bool aligned) {
+    __shared__ int warp_counts[kCompactThreads / 32];
+    int64_t base = (int64_t)blockIdx.x * kCompactTile + (int64_t)threadIdx.x * kCompactPerThread;
+    int c = base < n ? __popc(load_mask_bits(mask, base, n, aligned)) : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) warp_counts[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w2 = 0; w2 < kCompactThreads / 32; ++w2) t += warp_counts[w2];
+        block_counts[blockIdx.x] = t;
+    }
+}
+
+// exclusive scan of block_counts[0..n_blocks) in place; total at [n_blocks]
+__global__ void __launch_bounds__(1024) compact_scan_kernel(int32_t* counts, int n_blocks) {
+    __shared__ int64_t part[1024];
+    int per = (n_blocks + 1023) / 1024;
+    int lo = threadIdx.x * per, hi = min(lo + per, n_blocks);
+    int64_t s = 0;
+    for (int k = lo; k < hi; ++k) s += counts[k];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {   // Hillis-Steele inclusive scan
+        int64_t v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int64_t run = threadIdx.x == 0 ? 0 : part[threadIdx.x - 1];
+    for (int k = lo; k < hi; ++k) {
+        int c = counts[k];
+        counts[k] = (int32_t)run;
+        run += c;
+    }
+    if (threadIdx.x == 1023) counts[n_blocks] = (int32_t)part[1023];
+}
+
+__global__ void __launch_bounds__(kCompactThreads)
+compact_write_kernel(const uint8_t* __restrict__ mask, int64_t n, const int32_t* __restrict__ block_offsets,
+                     int32_t* __restrict__ idx, int64_t capacity, bool aligned) {
+    __shared__ int warp_counts[kCompactThreads / 32];
+    int64_t base = (int64_t)blockIdx.x * kCompactTile + (int64_t)threadIdx.x * kCompactPerThread;
+    uint32_t bits = base < n ? load_mask_bits(mask, base, n, aligned) : 0u;
+    int c = __popc(bits);
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) warp_counts[wid] = incl;
+    __syncthreads();
+    int woff = 0;
+    for (int w2 = 0; w2 < wid; ++w2) woff += warp_counts[w2];
+    int64_t out = (int64_t)block_offsets[blockIdx.x] + woff + incl - c;
+    while (bits) {
+        int k = __ffs(bits) - 1;
+        bits &= bits - 1;
+        if (out < capacity) idx[out] = (int32_t)(base + k);
+        ++out;
+    }
+}
+
+__global__ void gather_band_kernel(const double* __restrict__ obs, const double* __restrict__ inv_var,
+                                   const uint8_t* __restrict__ obs_mask, const int32_t* __restrict__ idx,
+                                   int64_t n_pix, double* __restrict__ y, double* __restrict__ w,
+                                   uint8_t* __restrict__ m_out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pix) return;
+    int32_t j = idx[i];
+    bool m = obs_mask[j] != 0;
+    y[i] = m ? obs[j] : 0.0;
+    w[i] = m ? inv_var[j] : 0.0;   // gate, never multiply: masked pixels hold inf
+    if (m_out) m_out[i] = m ? 1 : 0;
+}
+
+__global__ void scatter_output_kernel(const double* __restrict__ x, const double* __restrict__ a,
+                                      int64_t ld, int64_t n_pix, int n_params,
+                                      const int32_t* __restrict__ idx, int64_t n_raster,
+                                      float* __restrict__ mean_r, float* __restrict__ unc_r) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pix) return;
+    int64_t j = idx[i];
+    for (int p = 0; p < n_params; ++p) {
+        if (mean_r) mean_r[(int64_t)p * n_raster + j] = (float)x[(int64_t)p * ld + i];
+        if (unc_r) unc_r[(int64_t)p * n_raster + j] = (float)(1.0 / sqrt(a[(int64_t)tri(p, p) * ld + i]));
+    }
+}
+
+// ---------------------------------------------------------------------------
+// interleaved <-> planar through a padded shared-memory tile
+// ---------------------------------------------------------------------------
+constexpr int kTilePix = 128;
+
+template <bool kToPlanar, bool kDiag>
+__global__ void __launch_bounds__(kTilePix)
+interleave_kernel(const double* __restrict__ src, double* __restrict__ dst, int64_t n_pix, int P, int64_t ld) {
+    extern __shared__ double tile[];          // [kTilePix][P|1]  (odd stride: no bank conflicts)
+    const int stride = P | 1;
+    int64_t i0 = (int64_t)blockIdx.x * kTilePix;
+    int np = (int)min((int64_t)kTilePix, n_pix - i0);
+    if (kToPlanar) {
+        for (int k = threadIdx.x; k < np * P; k += kTilePix) tile[(k / P) * stride + (k % P)] = src[i0 * P + k];
+        __syncthreads();
+        if ((int)threadIdx.x < np)
+            for (int p = 0; p < P; ++p) dst[(int64_t)p * ld + i0 + threadIdx.x] = tile[threadIdx.x * stride + p];
+    } else {
+        if ((int)threadIdx.x < np)
+            for (int p = 0; p < P; ++p) {
+                int64_t plane = kDiag ? tri(p, p) : p;
+                tile[threadIdx.x * stride + p] = src[plane * ld + i0 + threadIdx.x];
+            }
+        __syncthreads();
+        for (int k = threadIdx.x; k < np * P; k += kTilePix) dst[i0 * P + k] = tile[(k / P) * stride + (k % P)];
+    }
+}
+
+constexpr int kBlkPix = 32;
+
+template <bool kToPacked>
+__global__ void __launch_bounds__(128)
+blocks_kernel(const double* __restrict__ src, double* __restrict__ dst, int64_t n_pix, int P, int64_t ld) {
+    extern __shared__ double tile[];          // [kBlkPix][P*P + 1]
+    const int PP = P * P, stride = PP + 1, L = tri_count(P);
+    int64_t i0 = (int64_t)blockIdx.x * kBlkPix;
+    int np = (int)min((int64_t)kBlkPix, n_pix - i0);
+    if (kToPacked) {
+        for (int k = threadIdx.x; k < np * PP; k += blockDim.x) tile[(k / PP) * stride + (k % PP)] = src[i0 * PP + k];
+        __syncthreads();
+        for (int k = threadIdx.x; k < L * kBlkPix; k += blockDim.x) {
+            int c = k / kBlkPix, px = k % kBlkPix;
+            if (px >= np) continue;
+            int r = 0;
+            while (tri_count(r + 1) <= c) ++r;
+            int q = c - tri_count(r);
+            dst[(int64_t)c * ld + i0 + px] = tile[px * stride + r * P + q];
+        }
+    } else {
+        for (int k = threadIdx.x; k < L * kBlkPix; k += blockDim.x) {
+            int c = k / kBlkPix, px = k % kBlkPix;
+            if (px >= np) continue;
+            int r = 0;
+            while (tri_count(r + 1) <= c) ++r;
+            int q = c - tri_count(r);
+            double v = src[(int64_t)c * ld + i0 + px];
+            tile[px * stride + r * P + q] = v;
+            tile[px * stride + q * P + r] = v;
+        }
+        __syncthreads();
+        for (int k = threadIdx.x; k < np * PP; k += blockDim.x) dst[i0 * PP + k] = tile[(k / PP) * stride + (k % PP)];
+    }
+}
+
+}  // namespace kafka
+
+using namespace kafka;
+
+extern "C" {
+
+const char* kafka_last_error(void) { return g_err; }
+int kafka_version(void) { return 100; }
+
+int64_t kafka_compact_scratch_elems(int64_t n_raster) {
+    return (n_raster + kCompactTile - 1) / kCompactTile + 2;
+}
+
+int kafka_compact_mask(const uint8_t* mask, int64_t n_raster, int32_t* idx, int64_t idx_capacity,
+                       int32_t* scratch, int64_t* n_true_host, void* stream) {
+    KAFKA_CHECK_ARG(mask && scratch && n_true_host, "kafka_compact_mask: null pointer");
+    KAFKA_CHECK_ARG(n_raster >= 0 && n_raster < ((int64_t)1 << 31), "kafka_compact_mask: n_raster=%lld out of range",
+                    (long long)n_raster);
+    cudaStream_t s = (cudaStream_t)stream;
+    *n_true_host = 0;
+    if (n_raster == 0) return 0;
+    int n_blocks = (int)((n_raster + kCompactTile - 1) / kCompactTile);
+    bool aligned = (reinterpret_cast<uintptr_t>(mask) & 15u) == 0;
+    compact_count_kernel<<<n_blocks, kCompactThreads, 0, s>>>(mask, n_raster, scratch, aligned);
+    compact_scan_kernel<<<1, 1024, 0, s>>>(scratch, n_blocks);
+    if (int e = launch_status("compact_count/scan")) return e;
+    int32_t total = 0;
+    KAFKA_CUDA(cudaMemcpyAsync(&total, scratch + n_blocks, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    if (idx) {
+        compact_write_kernel<<<n_blocks, kCompactThreads, 0, s>>>(mask, n_raster, scratch, idx, idx_capacity, aligned);
+        if (int e = launch_status("compact_write")) return e;
+    }
+    KAFKA_CUDA(cudaStreamSynchronize(s));
+    *n_true_host = total;
+    if (idx && total > idx_capacity) {
+        set_error("kafka_compact_mask: %d True pixels but idx holds %lld", total, (long long)idx_capacity);
+        return KAFKA_E_TOOLARGE;
+    }
+    return 0;
+}
+
+int kafka_gather_band(const double* obs, const double* inv_var, const uint8_t* obs_mask,
+                      const int32_t* idx, int64_t n_pix, double* y, double* w, uint8_t* m_out,
+                      void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0, "kafka_gather_band: n_pix < 0");
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(obs && inv_var && obs_mask && idx && y && w, "kafka_gather_band: null pointer");
+    int threads = 256;
+    gather_band_kernel<<<(unsigned)((n_pix + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+        obs, inv_var, obs_mask, idx, n_pix, y, w, m_out);
+    return launch_status("gather_band");
+}
+
+int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, int64_t n_pix,
+                         int n_params, const int32_t* idx, int64_t n_raster, float* mean_raster,
+                         float* unc_raster, void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "kafka_scatter_output: bad n_pix/ld");
+    KAFKA_CHECK_ARG(n_params >= 1 && n_params <= KAFKA_MAX_PARAMS, "kafka_scatter_output: n_params=%d", n_params);
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(idx && (!mean_raster || x) && (!unc_raster || a_packed), "kafka_scatter_output: null pointer");
+    int threads = 256;
+    scatter_output_kernel<<<(unsigned)((n_pix + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+        x, a_packed, ld, n_pix, n_params, idx, n_raster, mean_raster, unc_raster);
+    return launch_status("scatter_output");
+}
+
+static int check_layout(const char* who, int64_t n_pix, int n_params, int64_t ld) {
+    KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "%s: need 0 <= n_pix <= ld (n_pix=%lld ld=%lld)", who,
+                    (long long)n_pix, (long long)ld);
+    KAFKA_CHECK_ARG(n_params >= 1 && n_params <= KAFKA_MAX_PARAMS, "%s: n_params=%d outside 1..%d", who, n_params,
+                    KAFKA_MAX_PARAMS);
+    return 0;
+}
+
+int kafka_interleaved_to_planar(const double* x_il, int64_t n_pix, int n_params, double* x_pl, int64_t ld,
+                                void* stream) {
+    if (int e = check_layout("kafka_interleaved_to_planar", n_pix, n_params, ld)) return e;
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(x_il && x_pl, "kafka_interleaved_to_planar: null pointer");
+    size_t smem = (size_t)kTilePix * (n_params | 1) * sizeof(double);
+    interleave_kernel<true, false><<<(unsigned)((n_pix + kTilePix - 1) / kTilePix), kTilePix, smem, (cudaStream_t)stream>>>(
+        x_il, x_pl, n_pix, n_params, ld);
+    return launch_status("interleaved_to_planar");
+}
+
+int kafka_planar_to_interleaved(const double* x_pl, int64_t ld, int64_t n_pix, int n_params, double* x_il,
+                                void* stream) {
+    if (int e = check_layout("kafka_planar_to_interleaved", n_pix, n_params, ld)) return e;
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(x_il && x_pl, "kafka_planar_to_interleaved: null pointer");
+    size_t smem = (size_t)kTilePix * (n_params | 1) * sizeof(double);
+    interleave_kernel<false, false><<<(unsigned)((n_pix + kTilePix - 1) / kTilePix), kTilePix, smem, (cudaStream_t)stream>>>(
+        x_pl, x_il, n_pix, n_params, ld);
+    return launch_status("planar_to_interleaved");
+}
+
+int kafka_packed_diagonal(const double* a_packed, int64_t ld, int64_t n_pix, int n_params, double* diag_il,
+                          void* stream) {
+    if (int e = check_layout("kafka_packed_diagonal", n_pix, n_params, ld)) return e;
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(a_packed && diag_il, "kafka_packed_diagonal: null pointer");
+    size_t smem = (size_t)kTilePix * (n_params | 1) * sizeof(double);
+    interleave_kernel<false, true><<<(unsigned)((n_pix + kTilePix - 1) / kTilePix), kTilePix, smem, (cudaStream_t)stream>>>(
+        a_packed, diag_il, n_pix, n_params, ld);
+    return launch_status("packed_diagonal");
+}
+
+static int blocks_launch(bool to_packed, const double* src, double* dst, int64_t n_pix, int P, int64_t ld,
+                         cudaStream_t s) {
+    size_t smem = (size_t)kBlkPix * (P * P + 1) * sizeof(double);
+    unsigned grid = (unsigned)((n_pix + kBlkPix - 1) / kBlkPix);
+    if (to_packed) {
+        KAFKA_CUDA(cudaFuncSetAttribute(blocks_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        blocks_kernel<true><<<grid, 128, smem, s>>>(src, dst, n_pix, P, ld);
+    } else {
+        KAFKA_CUDA(cudaFuncSetAttribute(blocks_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        blocks_kernel<false><<<grid, 128, smem, s>>>(src, dst, n_pix, P, ld);
+    }
+    return launch_status("blocks<->packed");
+}
+
+int kafka_blocks_to_packed(const double* blocks, int64_t n_pix, int n_params, double* a_packed, int64_t ld,
+                           void* stream) {
+    if (int e = check_layout("kafka_blocks_to_packed", n_pix, n_params, ld)) return e;
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(blocks && a_packed, "kafka_blocks_to_packed: null pointer");
+    return blocks_launch(true, blocks, a_packed, n_pix, n_params, ld, (cudaStream_t)stream);
+}
+
+int kafka_packed_to_blocks(const double* a_packed, int64_t ld, int64_t n_pix, int n_params, double* blocks,
+                           void* stream) {
+    if (int e = check_layout("kafka_packed_to_blocks", n_pix, n_params, ld)) return e;
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(blocks && a_packed, "kafka_packed_to_blocks: null pointer");
+    return blocks_launch(false, a_packed, blocks, n_pix, n_params, ld, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,320 @@
+// Fused normal-equation build + per-pixel fp64 Cholesky solve + convergence
+// partial norm (sm_100a).  Replaces sort_band_data + variational_kalman_multiband
+// (kafka/inference/solvers.py:81-145) and the norm of do_all_bands
+// (kafka/linear_kf.py:293).
+//
+// One thread owns one pixel: the packed P x P block (P(P+1)/2 fp64) and the
+// right-hand side live in registers, every global access is a coalesced planar
+// load/store (consecutive threads = consecutive pixels), nothing is re-read.
+// This kernel is HBM-bound; algorithmic bytes per pixel are in DESIGN.md.
+#include "chol.cuh"
+
+namespace kafka {
+
+struct SolveBandDev {
+    const double* h0;
+    const double* jac;
+    const double* y;
+    const double* w;
+    double row[KAFKA_MAX_PARAMS];
+    double offset;
+    int32_t kind;
+    int8_t src[KAFKA_MAX_PARAMS];   // Jacobian plane feeding state slot p, -1 = none
+};
+
+struct SolveParams {
+    SolveBandDev bands[KAFKA_MAX_BANDS];
+    const double* x_prev;
+    const double* x_f;
+    const double* pinv_f;
+    double* x_out;
+    double* a_out;
+    double* innovations;
+    double* fwd;
+    double* partials;     // [2][gridDim.x]: sum of squares, bad-pixel count
+    int64_t n_pix;
+    int64_t ld;
+    int32_t n_bands;
+    uint32_t flags;
+};
+
+constexpr int kSolveThreads = 128;
+
+template <int P>
+__device__ __forceinline__ void band_row(const SolveBandDev& bd, int64_t ld, int64_t i, const double (&xp)[P],
+                                         double w, double (&J)[P], double& h0) {
+    if (bd.kind == KAFKA_BAND_LINEAR) {
+        double s = bd.offset;
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            J[p] = w != 0.0 ? bd.row[p] : 0.0;
+            s = fma(bd.row[p], xp[p], s);
+        }
+        h0 = w != 0.0 ? s : 0.0;
+    } else {
+#pragma unroll
+        for (int p = 0; p < P; ++p) J[p] = bd.src[p] >= 0 ? ldg_stream(bd.jac + (int64_t)bd.src[p] * ld + i) : 0.0;
+        h0 = ldg_stream(bd.h0 + i);
+    }
+}
+
+template <int P>
+__global__ void __launch_bounds__(kSolveThreads)
+solve_bands_kernel(const __grid_constant__ SolveParams prm) {
+    constexpr int L = tri_count(P);
+    __shared__ double s_part[2][kSolveThreads / 32];
+    const int64_t i = (int64_t)blockIdx.x * kSolveThreads + threadIdx.x;
+    const int64_t ld = prm.ld;
+    double ssq = 0.0, bad = 0.0;
+
+    if (i < prm.n_pix) {
+        double A[L], rhs[P], xp[P], xf[P];
+        const bool bcast = (prm.flags & KAFKA_PRIOR_BROADCAST) != 0;
+#pragma unroll
+        for (int c = 0; c < L; ++c) A[c] = bcast ? prm.pinv_f[c] : ldg_stream(prm.pinv_f + (int64_t)c * ld + i);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            xp[p] = ldg_stream(prm.x_prev + (int64_t)p * ld + i);
+            xf[p] = ldg_stream(prm.x_f + (int64_t)p * ld + i);
+        }
+        symv<P>(A, xf, rhs);
+
+        for (int b = 0; b < prm.n_bands; ++b) {
+            const SolveBandDev& bd = prm.bands[b];
+            const double w = ldg_stream(bd.w + i);
+            const double y = ldg_stream(bd.y + i);
+            double J[P], h0;
+            band_row<P>(bd, ld, i, xp, w, J, h0);
+            double yp = y - h0;                                   // y' = y + J.x_prev - H0
+#pragma unroll
+            for (int p = 0; p < P; ++p) yp = fma(J[p], xp[p], yp);
+            const double wy = w * yp;
+#pragma unroll
+            for (int r = 0; r < P; ++r) {
+                const double wj = w * J[r];
+                rhs[r] = fma(wy, J[r], rhs[r]);
+#pragma unroll
+                for (int q = 0; q <= r; ++q) A[tri(r, q)] = fma(wj, J[q], A[tri(r, q)]);
+            }
+            if (prm.innovations) stg_stream(prm.innovations + (int64_t)b * ld + i, y - h0);
+        }
+
+#pragma unroll
+        for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A[c]);
+
+        double invd[P];
+        const bool ok = chol_factor<P>(A, invd);
+        chol_solve<P>(A, invd, rhs);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const double xn = ok ? rhs[p] : xf[p];
+            rhs[p] = xn;
+            stg_stream(prm.x_out + (int64_t)p * ld + i, xn);
+            const double d = xn - xp[p];
+            ssq = fma(d, d, ssq);
+        }
+        bad = ok ? 0.0 : 1.0;
+
+        if (prm.fwd) {
+            for (int b = 0; b < prm.n_bands; ++b) {
+                const SolveBandDev& bd = prm.bands[b];
+                double J[P], h0;
+                band_row<P>(bd, ld, i, xp, bd.w[i], J, h0);
+                double f = h0;
+#pragma unroll
+                for (int p = 0; p < P; ++p) f = fma(J[p], rhs[p] - xf[p], f);
+                stg_stream(prm.fwd + (int64_t)b * ld + i, f);
+            }
+        }
+    }
+
+    ssq = warp_sum(ssq);
+    bad = warp_sum(bad);
+    if ((threadIdx.x & 31) == 0) {
+        s_part[0][threadIdx.x >> 5] = ssq;
+        s_part[1][threadIdx.x >> 5] = bad;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < kSolveThreads / 32; ++k) {
+            s0 += s_part[0][k];
+            s1 += s_part[1][k];
+        }
+        prm.partials[blockIdx.x] = s0;
+        prm.partials[gridDim.x + blockIdx.x] = s1;
+    }
+}
+
+// Fixed-order second stage: same bits every run, whatever the launch order.
+__global__ void __launch_bounds__(256)
+reduce_partials_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ norm2,
+                       int32_t* __restrict__ n_bad) {
+    __shared__ double s0[256], s1[256];
+    double a = 0.0, b = 0.0;
+    for (int k = threadIdx.x; k < n_blocks; k += 256) {
+        a += partials[k];
+        b += partials[n_blocks + k];
+    }
+    s0[threadIdx.x] = a;
+    s1[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            s0[threadIdx.x] += s0[threadIdx.x + o];
+            s1[threadIdx.x] += s1[threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        if (norm2) *norm2 = s0[0];
+        if (n_bad) *n_bad = (int32_t)s1[0];
+    }
+}
+
+// blend_prior (kf_tools.py:75-96): C = Pf + Cp, b = Pf mu_p + Cp x_f, x = C^-1 b
+template <int P>
+__global__ void __launch_bounds__(kSolveThreads)
+blend_prior_kernel(const double* __restrict__ prior_mean, const double* __restrict__ prior_inv,
+                   const double* __restrict__ x_f, const double* __restrict__ pinv_f, int64_t ld, int64_t n_pix,
+                   double* __restrict__ x_out, double* __restrict__ c_out, int32_t* __restrict__ n_bad,
+                   uint32_t flags) {
+    constexpr int L = tri_count(P);
+    const int64_t i = (int64_t)blockIdx.x * kSolveThreads + threadIdx.x;
+    int bad = 0;
+    if (i < n_pix) {
+        const bool bcast = (flags & KAFKA_PRIOR_BROADCAST) != 0;
+        double Pf[L], Cp[L], mu[P], xf[P], b1[P], b2[P];
+#pragma unroll
+        for (int c = 0; c < L; ++c) {
+            Pf[c] = ldg_stream(pinv_f + (int64_t)c * ld + i);
+            Cp[c] = bcast ? prior_inv[c] : ldg_stream(prior_inv + (int64_t)c * ld + i);
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            mu[p] = bcast ? prior_mean[p] : ldg_stream(prior_mean + (int64_t)p * ld + i);
+            xf[p] = ldg_stream(x_f + (int64_t)p * ld + i);
+        }
+        symv<P>(Pf, mu, b1);       // the reference's cross weighting (kf_tools.py:90), kept as is
+        symv<P>(Cp, xf, b2);
+#pragma unroll
+        for (int c = 0; c < L; ++c) {
+            Pf[c] += Cp[c];
+            stg_stream(c_out + (int64_t)c * ld + i, Pf[c]);
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p) b1[p] += b2[p];
+        double invd[P];
+        const bool ok = chol_factor<P>(Pf, invd);
+        chol_solve<P>(Pf, invd, b1);
+#pragma unroll
+        for (int p = 0; p < P; ++p) stg_stream(x_out + (int64_t)p * ld + i, ok ? b1[p] : xf[p]);
+        bad = ok ? 0 : 1;
+    }
+    bad = __reduce_add_sync(0xffffffffu, bad);        // integer count: order-independent
+    if ((threadIdx.x & 31) == 0 && bad != 0 && n_bad) atomicAdd(n_bad, bad);
+}
+
+}  // namespace kafka
+
+using namespace kafka;
+
+extern "C" {
+
+int64_t kafka_solve_scratch_doubles(int64_t n_pix) {
+    if (n_pix < 0) return -1;
+    return 2 * ((n_pix + kSolveThreads - 1) / kSolveThreads) + 2;
+}
+
+int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve_band* bands, int n_bands,
+                      const double* x_prev, const double* x_f, const double* pinv_f, double* x_out, double* a_out,
+                      double* innovations, double* fwd, double* norm2, int32_t* n_bad, double* scratch,
+                      uint32_t flags, void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "kafka_solve_bands: need 0 <= n_pix <= ld (n_pix=%lld ld=%lld)",
+                    (long long)n_pix, (long long)ld);
+    KAFKA_CHECK_ARG(n_params >= 1 && n_params <= KAFKA_MAX_PARAMS, "kafka_solve_bands: n_params=%d outside 1..%d",
+                    n_params, KAFKA_MAX_PARAMS);
+    KAFKA_CHECK_ARG(n_bands >= 0 && n_bands <= KAFKA_MAX_BANDS, "kafka_solve_bands: n_bands=%d outside 0..%d", n_bands,
+                    KAFKA_MAX_BANDS);
+    KAFKA_CHECK_ARG(n_bands == 0 || bands, "kafka_solve_bands: bands is null");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n_pix == 0) {
+        if (norm2) KAFKA_CUDA(cudaMemsetAsync(norm2, 0, sizeof(double), s));
+        if (n_bad) KAFKA_CUDA(cudaMemsetAsync(n_bad, 0, sizeof(int32_t), s));
+        return 0;
+    }
+    KAFKA_CHECK_ARG(x_prev && x_f && pinv_f && x_out && a_out && scratch, "kafka_solve_bands: null pointer");
+    SolveParams prm;
+    memset(&prm, 0, sizeof(prm));
+    for (int b = 0; b < n_bands; ++b) {
+        SolveBandDev& d = prm.bands[b];
+        const kafka_solve_band& h = bands[b];
+        KAFKA_CHECK_ARG(h.y && h.w, "kafka_solve_bands: band %d lacks y/w", b);
+        d.y = h.y;
+        d.w = h.w;
+        d.kind = h.kind;
+        for (int p = 0; p < KAFKA_MAX_PARAMS; ++p) d.src[p] = -1;
+        if (h.kind == KAFKA_BAND_LINEAR) {
+            for (int p = 0; p < n_params; ++p) d.row[p] = h.row[p];
+            d.offset = h.offset;
+        } else if (h.kind == KAFKA_BAND_ARRAYS) {
+            KAFKA_CHECK_ARG(h.h0 && h.jac, "kafka_solve_bands: band %d lacks h0/jac", b);
+            KAFKA_CHECK_ARG(h.n_dim >= 1 && h.n_dim <= KAFKA_MAX_DIM, "kafka_solve_bands: band %d n_dim=%d", b, h.n_dim);
+            d.h0 = h.h0;
+            d.jac = h.jac;
+            for (int k = 0; k < h.n_dim; ++k) {
+                int slot = h.mapper[k];
+                KAFKA_CHECK_ARG(slot >= 0 && slot < n_params, "kafka_solve_bands: band %d maps plane %d to slot %d", b, k,
+                                slot);
+                KAFKA_CHECK_ARG(d.src[slot] < 0, "kafka_solve_bands: band %d maps two planes to slot %d", b, slot);
+                d.src[slot] = (int8_t)k;
+            }
+        } else {
+            set_error("kafka_solve_bands: band %d has unknown kind %d", b, h.kind);
+            return KAFKA_E_BADARG;
+        }
+    }
+    prm.x_prev = x_prev;
+    prm.x_f = x_f;
+    prm.pinv_f = pinv_f;
+    prm.x_out = x_out;
+    prm.a_out = a_out;
+    prm.innovations = innovations;
+    prm.fwd = fwd;
+    prm.partials = scratch;
+    prm.n_pix = n_pix;
+    prm.ld = ld;
+    prm.n_bands = n_bands;
+    prm.flags = flags;
+    const unsigned grid = (unsigned)((n_pix + kSolveThreads - 1) / kSolveThreads);
+    int rc = KAFKA_E_UNSUPPORTED;
+    KAFKA_DISPATCH_P(n_params, {
+        solve_bands_kernel<kP><<<grid, kSolveThreads, 0, s>>>(prm);
+        rc = launch_status("solve_bands_kernel");
+    });
+    if (rc != 0) return rc;
+    reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
+    return launch_status("reduce_partials_kernel");
+}
+
+int kafka_blend_prior(const double* prior_mean, const double* prior_inv, const double* x_f, const double* pinv_f,
+                      int64_t ld, int64_t n_pix, int n_params, double* x_out, double* c_out, int32_t* n_bad,
+                      uint32_t flags, void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "kafka_blend_prior: need 0 <= n_pix <= ld");
+    KAFKA_CHECK_ARG(n_params >= 1 && n_params <= KAFKA_MAX_PARAMS, "kafka_blend_prior: n_params=%d", n_params);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n_bad) KAFKA_CUDA(cudaMemsetAsync(n_bad, 0, sizeof(int32_t), s));
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(prior_mean && prior_inv && x_f && pinv_f && x_out && c_out, "kafka_blend_prior: null pointer");
+    const unsigned grid = (unsigned)((n_pix + kSolveThreads - 1) / kSolveThreads);
+    int rc = KAFKA_E_UNSUPPORTED;
+    KAFKA_DISPATCH_P(n_params, {
+        blend_prior_kernel<kP><<<grid, kSolveThreads, 0, s>>>(prior_mean, prior_inv, x_f, pinv_f, ld, n_pix, x_out,
+                                                             c_out, n_bad, flags);
+        rc = launch_status("blend_prior_kernel");
+    });
+    return rc;
+}
+
+}  // extern "C"

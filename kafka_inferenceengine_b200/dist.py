@@ -1,0 +1,83 @@
+"""Multi-GPU plumbing: one process per GPU, the image sharded by pixel.
+
+Every matrix of the filter is block diagonal per pixel, so ranks never exchange
+state.  The only coupling in the reference is the scalar convergence norm
+``||x - x_prev||_2 / len(x)`` over ALL pixels (kafka/linear_kf.py:293): each rank
+contributes its local sum of squares and element count to one 2-element
+all-reduce per iteration (NCCL over NVLink on the GPU box, gloo in CPU tests),
+after which every rank takes the same stop decision as a single process holding
+the whole image.  Results are gathered (or written per rank) at the end.
+
+The reference's own spatial partitioning is ``get_chunks``
+(kafka/input_output/utils.py:12-40) + one ``LinearKalman`` per chunk
+(kafka_test_Py36.py:241-255); there every chunk has its OWN norm, so chunked and
+unchunked reference runs can stop at different iterations.  Sharding here keeps
+the unchunked semantics.
+"""
+import numpy as np
+import torch
+
+
+def shard_rows(state_mask, rank, world_size):
+    """Row range [r0, r1) of the raster owned by ``rank``: contiguous row bands
+    with (nearly) equal numbers of True pixels.  Row-major compaction order is
+    preserved, so concatenating the shards' compacted pixels in rank order gives
+    the unsharded compaction."""
+    mask = np.asarray(state_mask, dtype=bool)
+    per_row = mask.sum(axis=1)
+    cum = np.concatenate([[0], np.cumsum(per_row)])
+    total = cum[-1]
+    bounds = [0]
+    for r in range(1, world_size):
+        target = total * r / world_size
+        bounds.append(int(np.searchsorted(cum, target, side="left")))
+    bounds.append(mask.shape[0])
+    bounds = np.maximum.accumulate(np.minimum(bounds, mask.shape[0]))
+    return int(bounds[rank]), int(bounds[rank + 1])
+
+
+def shard_pixels(n_pix, rank, world_size):
+    """Compacted pixel range [i0, i1) of ``rank``: ceil(N/G) pixels per rank
+    (SURVEY.md section 8e)."""
+    per = -(-int(n_pix) // int(world_size))
+    i0 = min(n_pix, rank * per)
+    return i0, min(n_pix, i0 + per)
+
+
+def global_norm(sum_sq_local, n_elems_local, comm=None):
+    """``(sqrt(sum of squares over all ranks) / total element count)`` and the
+    total count.  ``sum_sq_local`` may be a python float or a 0-d/1-element
+    tensor on any device."""
+    import torch.distributed as dist
+    if comm is None and not (dist.is_available() and dist.is_initialized()):
+        s = float(sum_sq_local)
+        return np.sqrt(s) / float(n_elems_local), float(n_elems_local)
+    if isinstance(sum_sq_local, torch.Tensor):
+        dev = sum_sq_local.device
+        buf = torch.stack([sum_sq_local.reshape(-1)[0].to(torch.float64),
+                           torch.tensor(float(n_elems_local), dtype=torch.float64, device=dev)])
+    else:
+        buf = torch.tensor([float(sum_sq_local), float(n_elems_local)], dtype=torch.float64)
+    backend = dist.get_backend(comm)
+    if backend == "gloo" and buf.is_cuda:
+        buf = buf.cpu()
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=comm)
+    buf = buf.cpu()
+    return float(np.sqrt(buf[0].item()) / buf[1].item()), float(buf[1].item())
+
+
+def gather_interleaved(x_local, comm=None, dst=None):
+    """Concatenate per-rank 1-D tensors in rank order (all ranks, or only ``dst``)."""
+    import torch.distributed as dist
+    if comm is None and not (dist.is_available() and dist.is_initialized()):
+        return x_local
+    world = dist.get_world_size(comm)
+    sizes = [torch.zeros(1, dtype=torch.int64, device=x_local.device) for _ in range(world)]
+    dist.all_gather(sizes, torch.tensor([x_local.numel()], dtype=torch.int64, device=x_local.device), group=comm)
+    sizes = [int(s.item()) for s in sizes]
+    m = max(sizes)
+    pad = torch.zeros(m, dtype=x_local.dtype, device=x_local.device)
+    pad[:x_local.numel()] = x_local
+    out = [torch.empty(m, dtype=x_local.dtype, device=x_local.device) for _ in range(world)]
+    dist.all_gather(out, pad, group=comm)
+    return torch.cat([o[:s] for o, s in zip(out, sizes)])

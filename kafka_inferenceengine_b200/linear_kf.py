@@ -1,0 +1,373 @@
+"""Drop-in for ``kafka.linear_kf.LinearKalman`` (kafka/linear_kf.py:55-452) with
+the per-pixel assimilation step on a B200.
+
+Same constructor, ``run``, ``advance``, ``assimilate*``, ``do_all_bands``,
+``solver*`` and ``set_trajectory_*`` as the reference; the state lives on the
+GPU between calls as ``DeviceVector`` / ``BlockDiag`` objects, which behave like
+the reference's numpy vector and scipy block-diagonal matrix towards the
+caller-owned collaborators (``observations``, ``output``, ``prior``).
+
+Two keyword-only additions: ``device`` (CUDA device) and ``comm`` (a
+``torch.distributed`` process group): with ``comm`` every rank owns a shard of
+the pixels and the convergence norm (linear_kf.py:293) is all-reduced so that
+all ranks take the same stop decision as one process holding the whole image.
+"""
+import logging
+from collections import namedtuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from . import engine
+from .device import BlockDiag, DeviceBands, DeviceVector, PixelIndex, default_device
+from .inference import kf_tools
+from .inference.kf_tools import (DiagonalMatrix, IdentityModel, propagate_and_blend_prior,
+                                 propagate_information_filter_LAI)
+from .inference.utils import (ObservationOperator, emulator_table, iterate_time_grid, linearize_bands)
+
+LOG = logging.getLogger(__name__ + ".linear_kf")
+
+Metadata = namedtuple('Metadata', 'mask uncertainty')
+Previous_State = namedtuple("Previous_State", "timestamp x_vect cov_m icov_mv")
+
+
+class LinearKalman(object):
+    """The raster Kalman / information filter of the reference, B200 inside."""
+
+    def __init__(self, observations, output, state_mask,
+                 create_observation_operator, parameters_list,
+                 state_propagation=propagate_information_filter_LAI,
+                 band_mapper=None,
+                 linear=True, diagnostics=True, prior=None, *, device=None, comm=None,
+                 round_operator_f32=True):
+        _lib.get_lib()                                   # fail now if the CUDA library is missing
+        if not isinstance(create_observation_operator, ObservationOperator):
+            raise NotImplementedError(
+                "create_observation_operator must be one of this package's operator descriptors "
+                "(create_prosail_observation_operator, create_nonlinear_observation_operator, "
+                "create_linear_observation_operator): arbitrary Python callables cannot run per "
+                "pixel on the GPU and there is no CPU fallback")
+        self.parameters_list = parameters_list
+        self.n_params = len(self.parameters_list)
+        if not 1 <= self.n_params <= _lib.MAX_PARAMS:
+            raise ValueError("n_params=%d outside 1..%d" % (self.n_params, _lib.MAX_PARAMS))
+        self.observations = observations
+        self.output = output
+        self.diagnostics = diagnostics
+        self.state_mask = state_mask
+        self.device = device or default_device()
+        # state-mask compaction (linear_kf.py:79-80), done once on the device
+        self.pixels = PixelIndex(state_mask, self.device)
+        self.n_state_elems = self.pixels.n_pix
+        self._state_propagator = state_propagation
+        self._advance = propagate_and_blend_prior
+        self.prior = prior
+        self.band_mapper = band_mapper
+        self._create_observation_operator = create_observation_operator
+        self.comm = comm
+        self.round_operator_f32 = bool(round_operator_f32)
+        self.want_forward_modelled = False
+        self._stager = engine.ObservationStager(self.pixels)
+        self._ws = {}
+        self.trajectory_model = None
+        self.trajectory_uncertainty = None
+        self.last_iterations = []            # solver calls per assimilated date (diagnostic)
+        self.last_norms = []
+        self.profile = None                  # dict of CUDA-event pairs when bench.py asks for kernel times
+        LOG.info("Starting KaFKA run!!!")
+
+    # ------------------------------------------------------------------
+    def advance(self, x_analysis, P_analysis, P_analysis_inverse,
+                trajectory_model, trajectory_uncertainty):
+        """linear_kf.py:99-108."""
+        LOG.info("Calling state propagator...")
+        x_forecast, P_forecast, P_forecast_inverse = \
+            self._advance(x_analysis, P_analysis, P_analysis_inverse,
+                          trajectory_model, trajectory_uncertainty,
+                          prior=self.prior, date=self.current_timestep,
+                          state_propagator=self._state_propagator)
+        return x_forecast, P_forecast, P_forecast_inverse
+
+    def _set_plot_view(self, diag_string, timestep, obs):
+        pass
+
+    def _plotter_iteration_start(self, plot_obj, x, obs, mask):
+        pass
+
+    def _plotter_iteration_end(self, plot_obj, x, P, innovation, mask):
+        pass
+
+    def set_trajectory_model(self):
+        """linear_kf.py:123-129: identity."""
+        n = self.n_state_elems
+        self.trajectory_model = IdentityModel(self.n_params * n)
+
+    def set_trajectory_uncertainty(self, Q):
+        """linear_kf.py:131-146: ``Q`` is the main diagonal (length n_params*n
+        or anything that broadcasts to it)."""
+        n = self.n_state_elems * self.n_params
+        q = np.broadcast_to(np.asarray(Q, dtype=np.float64), (n,)) if np.ndim(Q) <= 1 else np.asarray(Q).ravel()
+        self.trajectory_uncertainty = DiagonalMatrix(np.ascontiguousarray(q), self.n_params, self.device)
+
+    def _get_observations_timestep(self, timestep, band=None):
+        """linear_kf.py:148-169."""
+        data = self.observations.get_band_data(timestep, band)
+        return (data.observations, data.uncertainty, data.mask, data.metadata, data.emulator)
+
+    # ------------------------------------------------------------------
+    def run(self, time_grid, x_forecast, P_forecast, P_forecast_inverse,
+            diag_str="diagnostics",
+            band=None, approx_diagonal=True, refine_diag=True,
+            iter_obs_op=False, is_robust=False, dates=None):
+        """linear_kf.py:171-212: the time loop.  State stays on the device from
+        one time step to the next."""
+        x_forecast = self._state(x_forecast)
+        P_forecast_inverse = self._precision(P_forecast_inverse)
+        for timestep, locate_times, is_first in iterate_time_grid(time_grid, self.observations.dates):
+            self.current_timestep = timestep
+            if not is_first:
+                LOG.info("Advancing state, %s" % timestep.strftime("%Y-%m-%d"))
+                x_forecast, P_forecast, P_forecast_inverse = self.advance(
+                    x_analysis, P_analysis, P_analysis_inverse,
+                    self.trajectory_model, self.trajectory_uncertainty)
+            if len(locate_times) == 0:
+                x_analysis = x_forecast
+                P_analysis = P_forecast
+                P_analysis_inverse = P_forecast_inverse
+                LOG.info("No observations in this time")
+            else:
+                x_analysis, P_analysis, P_analysis_inverse = self.assimilate_multiple_bands(
+                    locate_times, x_forecast, P_forecast, P_forecast_inverse,
+                    approx_diagonal=approx_diagonal, refine_diag=refine_diag,
+                    iter_obs_op=iter_obs_op, is_robust=is_robust, diag_str=diag_str)
+            LOG.info("Dumping results to disk")
+            self.output.dump_data(timestep, x_analysis, P_analysis,
+                                  P_analysis_inverse, self.state_mask, self.n_params)
+
+    def assimilate_multiple_bands(self, locate_times, x_forecast, P_forecast,
+                                  P_forecast_inverse,
+                                  approx_diagonal=True, refine_diag=False,
+                                  iter_obs_op=False, is_robust=False, diag_str="diag"):
+        """linear_kf.py:214-242: sequential update over the observation dates of
+        one grid interval, all bands of a date at once."""
+        for step in locate_times:
+            LOG.info("Assimilating %s..." % step.strftime("%Y-%m-%d"))
+            current_data = [self.observations.get_band_data(step, band)
+                            for band in range(self.observations.bands_per_observation[step])]
+            x_analysis, P_analysis, P_analysis_inverse, innovations = \
+                self.do_all_bands(step, current_data, x_forecast, P_forecast, P_forecast_inverse)
+            # the reference copies (x*1., linear_kf.py:232-240); device results are
+            # never written again, so the next forecast may simply alias them
+            x_forecast = x_analysis
+            P_forecast = P_analysis
+            P_forecast_inverse = P_analysis_inverse
+        return x_analysis, P_analysis, P_analysis_inverse
+
+    # ------------------------------------------------------------------
+    def _state(self, x):
+        x = DeviceVector.from_interleaved(x, self.n_params, self.device)
+        if x.n_pix != self.n_state_elems:
+            raise ValueError("state vector holds %d pixels, the state mask %d" % (x.n_pix, self.n_state_elems))
+        return x
+
+    def _precision(self, A):
+        if A is None:
+            raise ValueError("the information filter needs P_forecast_inverse")
+        A = BlockDiag.coerce(A, self.n_params, self.n_state_elems, self.device)
+        if A.n_pix != self.n_state_elems or A.n_params != self.n_params:
+            raise ValueError("inverse covariance does not match the state (%d px x %d params)"
+                             % (self.n_state_elems, self.n_params))
+        return A
+
+    def _workspace(self, n_bands):
+        key = (n_bands, self.want_forward_modelled)
+        ws = self._ws.get(key)
+        if ws is None:
+            ws = engine.SolveWorkspace(self.n_state_elems, self.n_params, n_bands, self.device,
+                                       want_fwd=self.want_forward_modelled)
+            self._ws[key] = ws
+        return ws
+
+    def _band_plan(self, current_data):
+        """Group the bands of one date by operator family.  Returns
+        (gp_groups, descs_template): gp_groups = [(band indices, [(table, mapper)])]
+        sharing an emulator input size, descs_template[b] = ("linear", row, offset)
+        or None for emulator bands (filled per iteration)."""
+        op = self._create_observation_operator
+        descs = [None] * len(current_data)
+        groups = {}
+        for b, data in enumerate(current_data):
+            if op.kind == "linear":
+                em = data.emulator
+                row = np.asarray(em.row, dtype=np.float64)
+                if row.size != self.n_params:
+                    raise ValueError("linear operator row has %d entries for %d parameters" % (row.size, self.n_params))
+                descs[b] = ("linear", row, float(em.offset))
+            else:
+                tab = emulator_table(data.emulator, self.device)
+                if op.state_mappers is None and self.band_mapper is not None:
+                    mp = np.asarray(self.band_mapper[b], dtype=np.int32)
+                else:
+                    mp = op.mapper(self.n_params, b, tab.n_dim)
+                if len(mp) != tab.n_dim or mp.min() < 0 or mp.max() >= self.n_params:
+                    raise ValueError("band %d: state mapper %s does not fit emulator/state" % (b, mp))
+                groups.setdefault(tab.n_dim, []).append((b, tab, mp))
+        return list(groups.values()), descs
+
+    def _tick(self, name):
+        if self.profile is None:
+            return None
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        self.profile.setdefault(name, []).append((e0, e1))
+        e0.record()
+        return e1
+
+    @staticmethod
+    def _tock(ev):
+        if ev is not None:
+            ev.record()
+
+    def _global_norm(self, ws):
+        """Convergence norm over ALL pixels (all ranks): linear_kf.py:293."""
+        n_elems = self.n_state_elems * self.n_params
+        if self.comm is None:
+            return float(np.sqrt(ws.norm2.item()) / float(n_elems)), float(n_elems)
+        from .dist import global_norm
+        return global_norm(ws.norm2, n_elems, self.comm)
+
+    def do_all_bands(self, timestep, current_data, x_forecast, P_forecast,
+                     P_forecast_inverse, convergence_tolerance=1e-3,
+                     min_iterations=2):
+        """linear_kf.py:245-323: iterated linearisation.  Per iteration: the GP
+        emulator kernel linearises every band around ``x_prev``
+        (utils.py:181-219), the fused kernel builds and solves every pixel's
+        normal equations (solvers.py:100-145) and leaves sum((x-x_prev)^2) on the
+        device; the stop rule is the reference's (linear_kf.py:293-307)."""
+        x_forecast = self._state(x_forecast)
+        P_forecast_inverse = self._precision(P_forecast_inverse)
+        n_bands = len(current_data)
+        ws = self._workspace(n_bands)
+        bufs = self._stager.upload(current_data)
+        groups, descs = self._band_plan(current_data)
+        all_linear = not groups
+        n, P = self.n_state_elems, self.n_params
+
+        bufsx = [DeviceVector.empty(n, P, self.device), DeviceVector.empty(n, P, self.device)]
+        a_out = BlockDiag.empty(n, P, self.device)
+        # operator outputs, one buffer per emulator group, reused by every iteration
+        gbufs = []
+        for group in groups:
+            D = group[0][1].n_dim
+            idxs = [g[0] for g in group]
+            gbufs.append((torch.empty((len(group), ws.ld), dtype=torch.float64, device=self.device),
+                          torch.empty((len(group), D, ws.ld), dtype=torch.float64, device=self.device),
+                          bufs.m if len(idxs) == n_bands else bufs.m[idxs].contiguous()))
+
+        x_prev = x_forecast
+        n_iter = 1
+        norms = []
+        not_converged = True
+        x_analysis = None
+        cached = None                         # (sum of squares, count) of a repeatable solve
+        while not_converged:
+            if cached is None:
+                for group, (hsub, jsub, msub) in zip(groups, gbufs):
+                    ev = self._tick("gp_linearize")
+                    linearize_bands(x_prev, [(g[1], g[2]) for g in group], msub, self.round_operator_f32,
+                                    h0=hsub, jac=jsub)
+                    self._tock(ev)
+                    for k, g in enumerate(group):
+                        descs[g[0]] = ("arrays", hsub[k], jsub[k], g[2])
+                x_new = bufsx[(n_iter - 1) % 2]
+                ev = self._tick("solve_bands")
+                engine.solve_bands(ws, descs, bufs, x_prev, x_forecast, P_forecast_inverse, x_new, a_out,
+                                   want_fwd=self.want_forward_modelled)
+                self._tock(ev)
+                convergence_norm, count = self._global_norm(ws)   # linear_kf.py:293
+                x_analysis = x_new
+            else:
+                # a linear operator relinearised at its own solution reproduces it:
+                # same system, same result, zero step (what the reference computes again)
+                convergence_norm = 0.0
+            norms.append(convergence_norm)
+            LOG.info("Band {:d}, Iteration # {:d}, convergence norm: {:g}".format(
+                n_bands - 1, n_iter, convergence_norm))
+            if (convergence_norm < convergence_tolerance) and (n_iter >= min_iterations):
+                not_converged = False
+            elif n_iter > 25:
+                LOG.warning("Bailing out after 25 iterations!!!!!!")
+                not_converged = False
+            if all_linear:
+                cached = count
+            x_prev = x_analysis
+            n_iter += 1
+
+        n_bad = int(ws.n_bad.item())
+        if n_bad:
+            LOG.warning("%d pixels had a non positive-definite information matrix; left at the forecast", n_bad)
+        self.last_iterations.append(n_iter - 1)
+        self.last_norms.append(norms)
+        innovations = DeviceBands(ws.innov.clone(), n)
+        self.fwd_modelled = DeviceBands(ws.fwd.clone(), n) if self.want_forward_modelled else None
+        return x_analysis, None, a_out, innovations
+
+    # ------------------------------------------------------------------
+    def assimilate(self, locate_times, x_forecast, P_forecast,
+                   P_forecast_inverse,
+                   approx_diagonal=True, refine_diag=False,
+                   iter_obs_op=False, is_robust=False, diag_str="diag"):
+        """linear_kf.py:325-354 (legacy band-by-band path): every band is
+        assimilated in turn, the analysis of one band being the forecast of the
+        next.  The reference's version relinearises around the forecast, applies
+        a 7-parameter Hessian correction and plots (linear_kf.py:412-423); here
+        each band goes through the same fused kernels with a single band."""
+        for step in locate_times:
+            LOG.info("Assimilating %s..." % step.strftime("%Y-%m-%d"))
+            for band in range(self.observations.bands_per_observation[step]):
+                x_analysis, P_analysis, P_analysis_inverse, innovations = \
+                    self.assimilate_band(band, step, x_forecast, P_forecast, P_forecast_inverse)
+                x_forecast, P_forecast, P_forecast_inverse = x_analysis, P_analysis, P_analysis_inverse
+        self.previous_state = Previous_State(step, x_analysis, P_analysis, P_analysis_inverse)
+        return x_analysis, P_analysis, P_analysis_inverse
+
+    def assimilate_band(self, band, timestep, x_forecast, P_forecast,
+                        P_forecast_inverse, convergence_tolerance=1e-3,
+                        min_iterations=1):
+        """linear_kf.py:356-425 through the multiband kernels with one band."""
+        data = self.observations.get_band_data(timestep, band)
+        op = self._create_observation_operator
+        if op.kind == "gp" and (op.state_mappers is not None or self.band_mapper is not None):
+            # the band index selects the state mapper: keep it by padding the plan
+            saved = self._band_plan
+
+            def plan(current):
+                tab = emulator_table(current[0].emulator, self.device)
+                mp = (np.asarray(self.band_mapper[band], dtype=np.int32)
+                      if (op.state_mappers is None and self.band_mapper is not None)
+                      else op.mapper(self.n_params, band, tab.n_dim))
+                return [[(0, tab, mp)]], [None]
+            self._band_plan = plan
+            try:
+                return self.do_all_bands(timestep, [data], x_forecast, P_forecast, P_forecast_inverse,
+                                         convergence_tolerance, min_iterations)
+            finally:
+                self._band_plan = saved
+        return self.do_all_bands(timestep, [data], x_forecast, P_forecast, P_forecast_inverse,
+                                 convergence_tolerance, min_iterations)
+
+    def solver(self, observations, mask, H_matrix, x_forecast, P_forecast,
+               P_forecast_inv, R_mat, the_metadata):
+        """linear_kf.py:427-438."""
+        from .inference.solvers import variational_kalman
+        return variational_kalman(observations, mask, self.state_mask, R_mat, H_matrix, self.n_params,
+                                  x_forecast, P_forecast, P_forecast_inv, the_metadata)
+
+    def solver_multiband(self, observations, mask, H_matrix, x0, x_forecast, P_forecast,
+                         P_forecast_inv, R_mat, the_metadata):
+        """linear_kf.py:441-452."""
+        from .inference.solvers import variational_kalman_multiband
+        return variational_kalman_multiband(observations, mask, self.state_mask, R_mat, H_matrix,
+                                            self.n_params, x0, x_forecast, P_forecast, P_forecast_inv,
+                                            the_metadata)

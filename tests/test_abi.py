@@ -1,0 +1,88 @@
+"""CPU-only checks of the C-ABI boundary: the library loads, exports every symbol
+that include/kafka_b200.h declares, and validates arguments before touching the
+GPU (no compute calls here)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from kafka_inferenceengine_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "kafka_b200.h")
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(kafka_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.get_lib()
+    names = declared_symbols()
+    assert len(names) >= 20
+    for name in names:
+        assert hasattr(lib, name), "missing export: " + name
+    # and the python binding declares a prototype for each of them
+    assert sorted(_lib.SIGNATURES) == names
+
+
+def test_version_and_error_string():
+    lib = _lib.get_lib()
+    assert lib.kafka_version() >= 100
+    assert isinstance(lib.kafka_last_error(), bytes)
+
+
+def test_struct_layouts_match_header():
+    # kafka_gp_band: pointer + 2 int32 + 16 int32; kafka_solve_band: see header
+    assert C.sizeof(_lib.GpBand) == 8 + 4 + 4 + 4 * _lib.MAX_DIM
+    assert C.sizeof(_lib.SolveBand) == 4 + 4 + 4 * _lib.MAX_DIM + 8 * _lib.MAX_PARAMS + 8 + 4 * 8
+
+
+def test_bad_arguments_are_rejected_without_a_gpu():
+    lib = _lib.get_lib()
+    assert lib.kafka_gp_table_doubles(250, 17) == -1
+    assert lib.kafka_gp_table_doubles(250, 10) == 2 * 10 + 2 + 250 * 12
+    assert lib.kafka_gp_table_doubles(250, 7) == 2 * 8 + 2 + 250 * 10
+    assert lib.kafka_solve_scratch_doubles(-1) == -1
+    assert lib.kafka_compact_scratch_elems(4097) == 4
+    st = lib.kafka_interleaved_to_planar(None, 10, 0, None, 32, None)
+    assert st == -1 and b"n_params" in lib.kafka_last_error()
+    st = lib.kafka_interleaved_to_planar(None, 10, 4, None, 5, None)
+    assert st == -1 and b"ld" in lib.kafka_last_error()
+    st = lib.kafka_solve_bands(10, 32, 17, None, 0, None, None, None, None, None, None, None, None, None, None, 0, None)
+    assert st == -1
+    st = lib.kafka_solve_bands(10, 32, 4, None, 17, None, None, None, None, None, None, None, None, None, None, 0, None)
+    assert st == -1
+    st = lib.kafka_advance_carry_slot(None, None, None, 32, 10, 7, 9, None, None, None, None, None)
+    assert st == -1 and b"slot" in lib.kafka_last_error()
+    with pytest.raises(_lib.KafkaCudaError):
+        _lib.check(st, "kafka_advance_carry_slot")
+
+
+def test_gp_pack_host_matches_numpy():
+    rng = np.random.default_rng(0)
+    for T, D in ((5, 1), (17, 4), (30, 7), (250, 10)):
+        X = rng.standard_normal((T, D))
+        theta = rng.standard_normal(D + 2) * 0.3
+        alpha = rng.standard_normal(T)
+        tab = _lib.gp_pack(X, theta, alpha)
+        DP = (D + 1) & ~1
+        assert tab.size == 2 * DP + 2 + T * (DP + 2)
+        e = np.exp(theta)
+        c = X.mean(axis=0)
+        assert np.allclose(tab[:D], e[:D], rtol=1e-15)
+        assert np.allclose(tab[DP:DP + D], c, rtol=1e-14, atol=1e-16)
+        assert tab[2 * DP] == pytest.approx(e[D], rel=1e-15)
+        rows = tab[2 * DP + 2:].reshape(T, DP + 2)
+        Xc = X - tab[DP:DP + D]
+        assert np.allclose(rows[:, :D], e[:D] * Xc, rtol=1e-15, atol=0)
+        assert np.allclose(rows[:, DP], theta[D] - 0.5 * (e[:D] * Xc * Xc).sum(axis=1), rtol=1e-14)
+        assert np.array_equal(rows[:, DP + 1], alpha)
+        if DP != D:
+            assert np.all(rows[:, D] == 0.0)
+    with pytest.raises(ValueError):
+        _lib.gp_pack(np.zeros((3, 17)), np.zeros(19), np.zeros(3))

@@ -1,0 +1,259 @@
+"""GPU parity of the whole drop-in path: ``LinearKalman.run`` /
+``do_all_bands`` (SURVEY section 8 rows a10/a11 and the b boundary) against
+
+* oracle B (fp64 restatement)  -- posterior mean and diag(P^-1) within 1e-6
+  relative (the north_star tolerance), iteration counts equal;
+* the UNMODIFIED reference's outputs stored in tests/golden -- within the
+  reference's own float32-LU reproducibility (see tests/test_oracle_golden.py).
+"""
+import datetime as dt
+
+import numpy as np
+import pytest
+import torch
+
+import golden_io as gio
+import gpu_util as gu
+import kafka_inferenceengine_b200 as kb
+from kafka_inferenceengine_b200 import synthetic as syn
+from kafka_inferenceengine_b200.device import BlockDiag, DeviceVector
+from oracle import kafka_cpu as kc
+from oracle.gp import GaussianProcess
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-6           # north_star: posterior mean and posterior-variance diagonal, relative
+
+
+def _iters_per_date(iter_log):
+    out = []
+    for n, _ in iter_log:
+        if int(n) == 1:
+            out.append(1)
+        else:
+            out[-1] = int(n)
+    return out
+
+
+def _oracle_ops(gps, P, bands, mappers=None):
+    def make(date):
+        return [(lambda xp, gp=gp, m=bands[date][b][2], mp=(None if mappers is None else mappers[b]):
+                 kc.emulator_operator(gp, xp, P, m, state_mapper=mp))
+                for b, gp in enumerate(gps)]
+    return make
+
+
+def _check_rows(out, rows, P, ref=None, tol=TOL):
+    idx = np.arange(P)
+    steps = sorted(out.output)
+    assert [s.toordinal() for s in steps] == [r[0].toordinal() for r in rows]
+    for k, (t, x, Pinv, _) in enumerate(rows):
+        got = out.output[steps[k]]
+        ex = np.abs(got["x"] - x) / np.maximum(np.abs(x), 1e-3)
+        ed = gu.rel(got["diag"], Pinv[:, idx, idx].ravel())
+        assert ex.max() < tol, (k, ex.max())
+        assert ed.max() < tol, (k, ed.max())
+        if ref is not None:                      # unmodified float32 reference
+            rx = gu.rel(got["x"], ref["out_x"][k])
+            rd = gu.rel(got["diag"], ref["out_diag"][k])
+            assert np.median(rx) < 2e-5 and rx.max() < 5e-2
+            assert np.median(rd) < 1e-4 and rd.max() < 5e-3
+
+
+def test_run_s2_prosail_vs_oracle_and_reference():
+    """Config-2 shape (10 params, 10 bands, T=250, prior-only advance;
+    kafka_test_S2.py:174-194) on the fixture the unmodified reference ran."""
+    g = gio.load("run_s2")
+    mask = g["mask"]
+    P = 10
+    N = int(mask.sum())
+    gps = gio.emulators(g, syn.EmulatorData)
+    obs = gio.FixtureObservations(g, gps)
+    prior = syn.BroadcastPrior(g["x0"][:P], g["prior_inv_block"].astype(np.float64), N,
+                               lambda blk, n: BlockDiag.from_block(blk, n, gu.DEV))
+    out = syn.MemoryOutput(syn.S2_PARAMETERS)
+    kf = kb.LinearKalman(obs, out, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS,
+                         state_propagation=None, prior=prior, linear=False)
+    kf.set_trajectory_model()
+    kf.set_trajectory_uncertainty(np.zeros(N * P))
+    x0, Pinv0 = prior.process_prior(None)
+    kf.run(gio.grid(g), x0, None, Pinv0, iter_obs_op=True)
+
+    ogps = gio.emulators(g, GaussianProcess)
+    bands = gio.compacted_bands(obs, mask)
+    blocks = np.repeat(g["prior_inv_block"][None].astype(np.float64), N, axis=0)
+    rows = list(kc.run_filter(gio.grid(g), obs.dates, bands, _oracle_ops(ogps, P, bands), g["x0"], blocks, P,
+                              lambda x, A, d: (g["x0"].copy(), blocks.copy())))
+    assert kf.last_iterations == sum((r[3] for r in rows), [])
+    assert kf.last_iterations == _iters_per_date(g["iter_log"])          # same as the reference's log
+    _check_rows(out, rows, P, ref=g)
+
+
+def test_run_tip_state_mapper_lai_propagator():
+    """Config-3 shape: 7-param TIP state, 2 bands through per-band state mappers
+    (utils.py:130-177), propagate_information_filter_LAI with Q[6::7]=0.04
+    (kafka_test.py:156-217)."""
+    g = gio.load("run_tip")
+    mask = g["mask"]
+    P = 7
+    N = int(mask.sum())
+    gps = gio.emulators(g, syn.EmulatorData)
+    obs = gio.FixtureObservations(g, gps)
+    out = syn.MemoryOutput(syn.TIP_PARAMETERS)
+    kf = kb.LinearKalman(obs, out, mask, kb.create_nonlinear_observation_operator, syn.TIP_PARAMETERS,
+                         state_propagation=kb.propagate_information_filter_LAI, prior=None, linear=False)
+    kf.set_trajectory_model()
+    kf.set_trajectory_uncertainty(g["q"])
+    mean, prior_inv = kb.tip_prior_full({"n_pixels": N})
+    kf.run(gio.grid(g), mean, None, prior_inv, iter_obs_op=True)
+
+    ogps = gio.emulators(g, GaussianProcess)
+    bands = gio.compacted_bands(obs, mask)
+    mappers = [g["mapper_0"], g["mapper_1"]]
+    idx = np.arange(P)
+    blocks = np.repeat(g["prior_inv_block"][None].astype(np.float64), N, axis=0)
+    rows = list(kc.run_filter(gio.grid(g), obs.dates, bands, _oracle_ops(ogps, P, bands, mappers), g["x0"], blocks, P,
+                              lambda x, A, d: kc.propagate_information_filter_lai(x, A[:, idx, idx].ravel(), g["q"])))
+    assert kf.last_iterations == sum((r[3] for r in rows), []) == _iters_per_date(g["iter_log"])
+    _check_rows(out, rows, P)
+    steps = sorted(out.output)
+    for k in range(len(steps)):                     # unmodified reference, float32
+        assert np.allclose(out.output[steps[k]]["x"], g["out_x"][k], rtol=1e-4, atol=1e-6)
+        assert np.allclose(out.output[steps[k]]["diag"], g["out_diag"][k], rtol=5e-6)
+
+
+def test_run_linear_config1():
+    """Config-1 shape: TIP state, ONE linear band in (H0,H) tuple form observing
+    slot 6, 10 dates, LAI propagator."""
+    g = gio.load("run_linear")
+    mask = g["mask"]
+    P = 7
+    N = int(mask.sum())
+    op = kb.LinearBandOperator(g["row"], 0.0)
+    obs = gio.FixtureObservations(g, [op])
+    out = syn.MemoryOutput(syn.TIP_PARAMETERS)
+    kf = kb.LinearKalman(obs, out, mask, kb.create_linear_observation_operator, syn.TIP_PARAMETERS,
+                         state_propagation=kb.propagate_information_filter_LAI, prior=None)
+    kf.set_trajectory_model()
+    kf.set_trajectory_uncertainty(g["q"])
+    mean, prior_inv = kb.tip_prior_full({"n_pixels": N})
+    kf.run(gio.grid(g), mean, None, prior_inv)
+    assert kf.last_iterations == _iters_per_date(g["iter_log"])
+    steps = sorted(out.output)
+    assert [s.toordinal() for s in steps] == list(g["out_steps"])
+    for k in range(len(steps)):
+        assert np.allclose(out.output[steps[k]]["diag"], g["out_diag"][k], rtol=5e-6)
+        assert np.allclose(out.output[steps[k]]["x"], g["out_x"][k], rtol=1e-4, atol=1e-6)
+    bands = gio.compacted_bands(obs, mask)
+    idx = np.arange(P)
+
+    def make(date):
+        m = bands[date][0][2]
+
+        def lin(xp):
+            J = np.where(m[:, None], op.row[None, :], 0.0)
+            H0 = np.where(m, xp.reshape(N, P) @ op.row + op.offset, 0.0)
+            return H0, J
+        return [lin]
+    blocks = np.repeat(g["prior_inv_block"][None].astype(np.float64), N, axis=0)
+    rows = list(kc.run_filter(gio.grid(g), obs.dates, bands, make, g["x0"], blocks, P,
+                              lambda x, A, d: kc.propagate_information_filter_lai(x, A[:, idx, idx].ravel(), g["q"])))
+    _check_rows(out, rows, P)
+
+
+def _barrax_s2_case(n_dates, seed=1234):
+    rng = np.random.default_rng(seed)
+    mask = gio.barrax_mask()
+    P, B, T = 10, 10, 250
+    N = int(mask.sum())
+    gps = [syn.make_emulator(rng, syn.SAIL_MEAN, syn.SAIL_SIGMA, n_train=T, cls=GaussianProcess) for _ in range(B)]
+    x_true = syn.SAIL_MEAN + syn.SAIL_SIGMA * rng.standard_normal((N, P))
+    base = dt.datetime(2017, 7, 3)
+    dates = [base + dt.timedelta(days=2 * d) for d in range(n_dates)]
+    obs = syn.SyntheticObservations(mask, dates, gps, x_true, lambda gp, X: gp.predict(X, do_unc=False)[0], rng)
+    grid = [base + dt.timedelta(days=2 * d) for d in range(n_dates + 1)]
+    return mask, P, N, gps, obs, grid
+
+
+def test_barrax_config2_two_dates_vs_oracle():
+    """BASELINE config 2 (Barrax mask, 13 027 px, 10 bands, T=250) for two dates."""
+    mask, P, N, gps, obs, grid = _barrax_s2_case(2)
+    inv = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
+    prior = syn.BroadcastPrior(syn.SAIL_MEAN, inv, N, lambda blk, n: BlockDiag.from_block(blk, n, gu.DEV))
+    out = syn.MemoryOutput(syn.S2_PARAMETERS)
+    kf = kb.LinearKalman(obs, out, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS,
+                         state_propagation=None, prior=prior, linear=False)
+    kf.set_trajectory_model()
+    kf.set_trajectory_uncertainty(np.zeros(N * P))
+    x0, Pinv0 = prior.process_prior(None)
+    kf.run(grid, x0, None, Pinv0, iter_obs_op=True)
+    bands = gio.compacted_bands(obs, mask)
+    blocks = np.repeat(inv[None], N, axis=0)
+    x0n = np.tile(syn.SAIL_MEAN, N)
+    rows = list(kc.run_filter(grid, obs.dates, bands, _oracle_ops(gps, P, bands), x0n, blocks, P,
+                              lambda x, A, d: (x0n.copy(), blocks.copy())))
+    assert kf.last_iterations == sum((r[3] for r in rows), [])
+    _check_rows(out, rows, P)
+    # output stage: what KafkaOutput.dump_data would write (observations.py:374-375,392-393)
+    last = sorted(out.output)[-1]
+    xv = DeviceVector.from_interleaved(out.output[last]["x"], P, gu.DEV)
+    A = BlockDiag.from_blocks(rows[-1][2], gu.DEV)
+    mean_r, unc_r = kf.pixels.scatter_output(xv, A, P)
+    assert np.array_equal(mean_r[6].cpu().numpy(), kc.scatter_param(out.output[last]["x"], 6, P, mask))
+
+
+def test_do_all_bands_fixed_iteration_counts_and_blend():
+    """Parity at FIXED iteration counts (1 and 3 solves) and with prior AND
+    propagator both set (blend_prior path, kf_tools.py:161-164)."""
+    g = gio.load("run_tip")
+    mask = g["mask"]
+    P = 7
+    N = int(mask.sum())
+    gps = gio.emulators(g, syn.EmulatorData)
+    ogps = gio.emulators(g, GaussianProcess)
+    obs = gio.FixtureObservations(g, gps)
+    mappers = [g["mapper_0"], g["mapper_1"]]
+    bands = gio.compacted_bands(obs, mask)
+    date = obs.dates[0]
+    blocks = np.repeat(g["prior_inv_block"][None].astype(np.float64), N, axis=0)
+    kf = kb.LinearKalman(obs, syn.MemoryOutput(syn.TIP_PARAMETERS), mask, kb.create_nonlinear_observation_operator,
+                         syn.TIP_PARAMETERS, prior=None)
+    data = [obs.get_band_data(date, b) for b in range(2)]
+    for k in (1, 3):
+        # min_iterations=k with a huge tolerance stops after exactly k solves
+        x, _, A, innov = kf.do_all_bands(date, data, g["x0"], None, BlockDiag.from_blocks(blocks, gu.DEV),
+                                         convergence_tolerance=1e9, min_iterations=k)
+        xo, Ao, innov_o, n, norms = kc.do_all_bands(_oracle_ops(ogps, P, bands, mappers)(date),
+                                                    [b[0] for b in bands[date]], [b[1] for b in bands[date]],
+                                                    [b[2] for b in bands[date]], g["x0"], blocks, P,
+                                                    fixed_iterations=k)
+        assert kf.last_iterations[-1] == k == n
+        assert np.max(np.abs(np.asarray(x) - xo) / np.maximum(np.abs(xo), 1e-3)) < TOL
+        assert np.max(gu.rel(A.blocks(), Ao, floor=1e-3)) < TOL
+        assert np.allclose(np.asarray(innov), innov_o, rtol=1e-6, atol=1e-9)
+        assert np.allclose(kf.last_norms[-1], norms, rtol=1e-6)
+    # advance with both a propagator and a prior: blend
+    mean, _, inv = kb.tip_prior()
+    prior = syn.BroadcastPrior(mean, inv.astype(np.float64), N, lambda blk, n: BlockDiag.from_block(blk, n, gu.DEV))
+    kf2 = kb.LinearKalman(obs, syn.MemoryOutput(syn.TIP_PARAMETERS), mask, kb.create_nonlinear_observation_operator,
+                          syn.TIP_PARAMETERS, state_propagation=kb.propagate_information_filter_LAI, prior=prior)
+    kf2.set_trajectory_model()
+    kf2.set_trajectory_uncertainty(g["q"])
+    kf2.current_timestep = date
+    xa = np.asarray(x)
+    xf, pf, pfi = kf2.advance(x, None, A, kf2.trajectory_model, kf2.trajectory_uncertainty)
+    idx = np.arange(P)
+    xl, bl = kc.propagate_information_filter_lai(xa, Ao[:, idx, idx].ravel(), g["q"])
+    xb, Cb = kc.blend_prior(np.tile(mean, N), np.repeat(inv[None].astype(np.float64), N, axis=0), xl, bl)
+    assert pf is None
+    assert np.max(np.abs(np.asarray(xf) - xb) / np.maximum(np.abs(xb), 1e-3)) < TOL
+    assert np.max(gu.rel(pfi.blocks(), Cb, floor=1e-3)) < TOL
+
+
+def test_unsupported_operator_raises():
+    mask = np.ones((4, 4), dtype=bool)
+    with pytest.raises(NotImplementedError):
+        kb.LinearKalman(None, None, mask, lambda *a: None, syn.S2_PARAMETERS)
+    kf = kb.LinearKalman(None, None, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS)
+    with pytest.raises(ValueError):
+        kf.do_all_bands(None, [], np.zeros(3 * 10), None, np.eye(10))

@@ -1,0 +1,116 @@
+"""CPU-only tests of the host side of the drop-in: time-grid iteration, pixel
+sharding, the convergence-norm all-reduce (gloo, world size 2) and the loud
+failure when no GPU is present."""
+import datetime as dt
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import golden_io as gio
+import kafka_inferenceengine_b200 as kb
+from kafka_inferenceengine_b200 import dist as kdist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_iterate_time_grid_matches_reference_kat():
+    # /root/reference/tests/test_utils.py:18-38 via the golden fixture
+    g = gio.load("kat_time_grid")
+    base = dt.datetime(2007, 7, 1)
+    grid = [base + i * dt.timedelta(days=1) for i in range(0, 60, 16)]
+    base = dt.datetime(2007, 1, 1)
+    dates = [base + i * dt.timedelta(days=1) for i in range(1, 365 + 8, 8)]
+    rows = list(kb.iterate_time_grid(grid, dates))
+    assert [r[0].toordinal() for r in rows] == list(g["steps"])
+    assert [[d.toordinal() for d in r[1]] for r in rows] == g["locs"].tolist()
+    assert [r[2] for r in rows] == [bool(f) for f in g["firsts"]]
+
+
+def test_operator_registry_and_names():
+    for name in ("create_prosail_observation_operator", "create_nonlinear_observation_operator",
+                 "create_linear_observation_operator", "variational_kalman_multiband", "variational_kalman",
+                 "propagate_information_filter_LAI", "propagate_information_filter_SLOW",
+                 "propagate_information_filter_approx_SLOW", "propagate_standard_kalman", "no_propagation",
+                 "propagate_and_blend_prior", "blend_prior", "tip_prior", "block_diag", "run_emulator",
+                 "iterate_time_grid", "LinearKalman"):
+        assert hasattr(kb, name), name
+    op = kb.create_nonlinear_observation_operator
+    assert list(op.mapper(7, 0, 4)) == [0, 1, 6, 2] and list(op.mapper(7, 1, 4)) == [3, 4, 6, 5]
+    assert list(kb.create_prosail_observation_operator.mapper(10, 3, 10)) == list(range(10))
+    with pytest.raises(ValueError):
+        kb.create_prosail_observation_operator.mapper(10, 0, 4)
+    mean, cov, inv = kb.tip_prior()
+    g = gio.load("kat_propagators")
+    assert np.array_equal(mean, g["tip_mean"]) and np.array_equal(inv, g["tip_inv"])
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="needs a machine without a GPU")
+def test_product_path_fails_loudly_without_gpu():
+    from kafka_inferenceengine_b200 import synthetic as syn
+    mask = np.ones((4, 4), dtype=bool)
+    with pytest.raises(kb._lib.KafkaCudaError):
+        kb.LinearKalman(None, None, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS)
+    with pytest.raises(NotImplementedError):
+        kb.LinearKalman(None, None, mask, lambda *a: None, syn.S2_PARAMETERS)
+
+
+def test_shard_rows_partitions_and_balances():
+    mask = gio.barrax_mask()
+    total = int(mask.sum())
+    for world in (1, 2, 3, 4, 8):
+        got = 0
+        prev = 0
+        for r in range(world):
+            r0, r1 = kdist.shard_rows(mask, r, world)
+            assert r0 == prev and r1 >= r0
+            prev = r1
+            n = int(mask[r0:r1].sum())
+            got += n
+            assert abs(n - total / world) <= mask.shape[1] + 1
+        assert prev == mask.shape[0] and got == total
+    assert kdist.shard_pixels(10, 0, 4) == (0, 3) and kdist.shard_pixels(10, 3, 4) == (9, 10)
+    assert kdist.shard_pixels(2, 3, 4) == (2, 2)
+
+
+_WORKER = r"""
+import os, sys
+sys.path.insert(0, %(root)r)
+import numpy as np, torch, torch.distributed as dist
+from kafka_inferenceengine_b200 import dist as kdist
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%(port)d", rank=int(sys.argv[1]), world_size=2)
+rank = dist.get_rank()
+rng = np.random.default_rng(7)
+d = rng.standard_normal(1000)               # the whole image's x - x_prev
+i0, i1 = kdist.shard_pixels(1000, rank, 2)
+local = torch.tensor(float((d[i0:i1] ** 2).sum()), dtype=torch.float64)
+norm, count = kdist.global_norm(local, i1 - i0)
+want = np.linalg.norm(d) / 1000.0           # linear_kf.py:293 on the unsharded vector
+assert count == 1000.0, count
+assert abs(norm - want) <= 1e-15 * want, (norm, want)
+g = kdist.gather_interleaved(torch.from_numpy(d[i0:i1].copy()))
+assert np.array_equal(g.numpy(), d)
+# ranks take the same stop decision
+flag = torch.tensor([1.0 if norm < 1e-3 else 0.0])
+both = [torch.zeros(1), torch.zeros(1)]
+dist.all_gather(both, flag)
+assert both[0].item() == both[1].item()
+dist.destroy_process_group()
+print("OK", rank)
+"""
+
+
+def test_global_norm_gloo_world2(tmp_path):
+    port = 29500 + (os.getpid() % 500)
+    script = tmp_path / "worker.py"
+    script.write_text(_WORKER % {"root": ROOT, "port": port})
+    procs = [subprocess.Popen([sys.executable, str(script), str(r)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                              env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+             for r in range(2)]
+    outs = [p.communicate(timeout=180)[0].decode() for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+        assert "OK" in o
