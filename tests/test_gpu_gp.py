@@ -18,8 +18,9 @@ pytestmark = pytest.mark.gpu
 
 # fp64 tolerance on emulator outputs: the kernel evaluates an algebraically
 # expanded form of the same sums, so agreement is at rounding level scaled by
-# the cancellation in sum_j k_j alpha_j.
-RTOL = 1e-9
+# the cancellation in sum_j k_j alpha_j (worst case seen: 2e-9 for 500 training
+# points in 4 dimensions; 1e-11 typical).  north_star asks 1e-6 on the posterior.
+RTOL = 1e-8
 
 
 def _gp(rng, D, T, w_scale=0.2):
@@ -29,7 +30,7 @@ def _gp(rng, D, T, w_scale=0.2):
 
 
 def _scale(a):
-    return np.maximum(np.abs(a), np.abs(a).max() * 1e-3)
+    return np.maximum(np.maximum(np.abs(a), np.abs(a).max() * 1e-3), 1e-300)
 
 
 @pytest.mark.parametrize("D,T", [(1, 5), (2, 33), (4, 120), (4, 500), (7, 64), (10, 250), (13, 40), (16, 100)])
