@@ -172,6 +172,33 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
                       double* norm2, int32_t* n_bad, double* scratch, uint32_t flags,
                       void* stream);
 
+/* Same update as kafka_solve_bands for callers that cannot allocate device memory
+ * and therefore cannot pass `scratch`.  It has no counterpart in the reference
+ * (pure Python, no device memory at all).  Typical callers: a plug-in inside a
+ * host application that reserved the whole GPU for its own memory pool; a
+ * latency-bound loop that must not hit the device-wide synchronisation of
+ * cudaMalloc/cudaFree; a thin FFI stub that owns nothing but the input and
+ * output arrays it was handed.  The scratch is a fixed array inside the library
+ * (KAFKA_STATIC_SCRATCH_DOUBLES doubles = 2 MiB of device memory on every GPU
+ * that loads the library, until the process exits), so:
+ *   - at most KAFKA_STATIC_MAX_PIXELS pixels per call, else KAFKA_E_TOOLARGE;
+ *   - the call neither allocates nor frees anything (no cudaMalloc/cudaFree, no
+ *     allocating library routine);
+ *   - all calls on a device share the array and it keeps the previous call's
+ *     contents; the slice a call uses is zeroed first on the call's stream, and
+ *     no result depends on older contents;
+ *   - calls that overlap on the GPU (two streams, two host threads) race on the
+ *     array: serialise them or use kafka_solve_bands with private scratch;
+ *   - the first call on each device looks up the array's device address (one-off
+ *     set-up); issue it before any stream capture starts.
+ * Arguments and results are exactly those of kafka_solve_bands minus `scratch`. */
+#define KAFKA_STATIC_SCRATCH_DOUBLES 262144
+#define KAFKA_STATIC_MAX_PIXELS 16777088 /* (262144 - 2) / 2 thread blocks of 128 pixels */
+int kafka_solve_bands_static(int64_t n_pix, int64_t ld, int n_params, const kafka_solve_band* bands_host,
+                             int n_bands, const double* x_prev, const double* x_f, const double* pinv_f,
+                             double* x_out, double* a_out, double* innovations, double* fwd,
+                             double* norm2, int32_t* n_bad, uint32_t flags, void* stream);
+
 /* ---- a12-a17: advance / propagation ----------------------------------------
  * propagate_information_filter_LAI (kafka/inference/kf_tools.py:292-314),
  * generalised from its hard-coded 7-parameter TIP prior: every slot is reset to

@@ -18,6 +18,8 @@ BAND_ARRAYS = 0
 BAND_LINEAR = 1
 ROUND_F32 = 1
 PRIOR_BROADCAST = 2
+STATIC_SCRATCH_DOUBLES = 262144
+STATIC_MAX_PIXELS = 16777088
 
 
 class KafkaCudaError(RuntimeError):
@@ -58,6 +60,8 @@ SIGNATURES = {
     "kafka_solve_scratch_doubles": (_i64, [_i64]),
     "kafka_solve_bands": (C.c_int, [_i64, _i64, _i32, C.POINTER(SolveBand), _i32, _p, _p, _p, _p, _p, _p, _p,
                                     _p, _p, _p, _u32, _p]),
+    "kafka_solve_bands_static": (C.c_int, [_i64, _i64, _i32, C.POINTER(SolveBand), _i32, _p, _p, _p, _p, _p, _p, _p,
+                                           _p, _p, _u32, _p]),
     "kafka_advance_carry_slot": (C.c_int, [_p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _p, _p, _p]),
     "kafka_advance_approx": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p]),
     "kafka_advance_exact": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p, _p]),
@@ -88,7 +92,7 @@ def get_lib():
 
 # kernels launched by one successful call of each entry point (for bench.py's
 # gpu_launches count; the set of kernels is in csrc/*.cu)
-KERNELS_PER_CALL = {"kafka_compact_mask": 3, "kafka_solve_bands": 2}
+KERNELS_PER_CALL = {"kafka_compact_mask": 3, "kafka_solve_bands": 2, "kafka_solve_bands_static": 3}
 launch_count = 0
 
 
