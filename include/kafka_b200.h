@@ -46,6 +46,9 @@ extern "C" {
 /* band operator kinds for kafka_solve_bands */
 #define KAFKA_BAND_ARRAYS 0 /* h0/jac arrays (emulator output or supplied Jacobians) */
 #define KAFKA_BAND_LINEAR 1 /* constant row: H0 = row.x_prev + offset, J = row        */
+#define KAFKA_BAND_UNIFORM 2 /* ONE linearisation shared by all pixels: h0[0], jac[d];   \
+                                the reference's "one unique state vector" shortcut      \
+                                (kafka/inference/utils.py:72-74)                        */
 
 /* flags */
 #define KAFKA_ROUND_F32 1u      /* round H0/J to float32 as the reference stores them \
@@ -82,6 +85,13 @@ int kafka_gather_band(const double* obs, const double* inv_var, const uint8_t* o
 int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, int64_t n_pix,
                          int n_params, const int32_t* idx, int64_t n_raster, float* mean_raster,
                          float* unc_raster, void* stream);
+
+/* Number of pixels whose state differs (bitwise) from pixel 0's: 0 means every
+ * pixel holds the same vector, which is what run_emulator's de-duplication
+ * detects with a Python set (kafka/inference/utils.py:72-74) -- e.g. the first
+ * iteration after a prior reset.  *n_diff is a device int32. */
+int kafka_state_uniform(const double* x, int64_t ld, int64_t n_pix, int n_params, int32_t* n_diff,
+                        void* stream);
 
 /* ---- layout conversion at the boundary -----------------------------------
  * interleaved x[n_params*i+p] (kafka/inference/utils.py:201) <-> planar. */
@@ -140,13 +150,13 @@ int kafka_gp_hessian(const double* xin, int64_t ld, int64_t n_pts, const double*
 
 /* ---- a8/a9/a10: fused normal-equation build + Cholesky solve --------------- */
 typedef struct {
-    int32_t kind;                      /* KAFKA_BAND_ARRAYS / KAFKA_BAND_LINEAR              */
-    int32_t n_dim;                     /* ARRAYS: Jacobian planes of this band               */
-    int32_t mapper[KAFKA_MAX_DIM];     /* ARRAYS: state slot of Jacobian plane d             */
+    int32_t kind;                      /* KAFKA_BAND_ARRAYS / _LINEAR / _UNIFORM             */
+    int32_t n_dim;                     /* ARRAYS, UNIFORM: Jacobian planes of this band      */
+    int32_t mapper[KAFKA_MAX_DIM];     /* ARRAYS, UNIFORM: state slot of Jacobian plane d    */
     double row[KAFKA_MAX_PARAMS];      /* LINEAR: operator row                               */
     double offset;                     /* LINEAR: H0 = row.x_prev + offset                   */
-    const double* h0;                  /* ARRAYS: [ld] device                                */
-    const double* jac;                 /* ARRAYS: [n_dim][ld] device                         */
+    const double* h0;                  /* ARRAYS: [ld] device; UNIFORM: 1 value              */
+    const double* jac;                 /* ARRAYS: [n_dim][ld] device; UNIFORM: [n_dim]       */
     const double* y;                   /* [ld] observations, 0 where unobserved              */
     const double* w;                   /* [ld] inverse variance, 0 where unobserved          */
 } kafka_solve_band;

@@ -16,6 +16,7 @@ MAX_BANDS = 16
 MAX_DIM = 16
 BAND_ARRAYS = 0
 BAND_LINEAR = 1
+BAND_UNIFORM = 2
 ROUND_F32 = 1
 PRIOR_BROADCAST = 2
 STATIC_SCRATCH_DOUBLES = 262144
@@ -47,6 +48,7 @@ SIGNATURES = {
     "kafka_compact_mask": (C.c_int, [_p, _i64, _p, _i64, _p, C.POINTER(C.c_int64), _p]),
     "kafka_gather_band": (C.c_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p]),
     "kafka_scatter_output": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p, _p, _p]),
+    "kafka_state_uniform": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
     "kafka_interleaved_to_planar": (C.c_int, [_p, _i64, _i32, _p, _i64, _p]),
     "kafka_planar_to_interleaved": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
     "kafka_blocks_to_packed": (C.c_int, [_p, _i64, _i32, _p, _i64, _p]),

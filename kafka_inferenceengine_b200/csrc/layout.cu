@@ -137,6 +137,18 @@ __global__ void scatter_output_kernel(const double* __restrict__ x, const double
     }
 }
 
+__global__ void __launch_bounds__(256)
+state_uniform_kernel(const double* __restrict__ x, int64_t ld, int64_t n_pix, int P, int32_t* __restrict__ n_diff) {
+    int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    int diff = 0;
+    if (i < n_pix)
+        for (int p = 0; p < P; ++p)
+            diff |= __double_as_longlong(ldg_stream(x + (int64_t)p * ld + i)) !=
+                    __double_as_longlong(__ldg(x + (int64_t)p * ld));
+    diff = __reduce_add_sync(0xffffffffu, diff);
+    if ((threadIdx.x & 31) == 0 && diff) atomicAdd(n_diff, diff);     // integer count: order-independent
+}
+
 // ---------------------------------------------------------------------------
 // interleaved <-> planar through a padded shared-memory tile
 // ---------------------------------------------------------------------------
@@ -265,6 +277,17 @@ int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, in
     scatter_output_kernel<<<(unsigned)((n_pix + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
         x, a_packed, ld, n_pix, n_params, idx, n_raster, mean_raster, unc_raster);
     return launch_status("scatter_output");
+}
+
+int kafka_state_uniform(const double* x, int64_t ld, int64_t n_pix, int n_params, int32_t* n_diff, void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "kafka_state_uniform: need 0 <= n_pix <= ld");
+    KAFKA_CHECK_ARG(n_params >= 1 && n_params <= KAFKA_MAX_PARAMS, "kafka_state_uniform: n_params=%d", n_params);
+    KAFKA_CHECK_ARG(n_diff, "kafka_state_uniform: n_diff is null");
+    KAFKA_CUDA(cudaMemsetAsync(n_diff, 0, sizeof(int32_t), (cudaStream_t)stream));
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(x, "kafka_state_uniform: x is null");
+    state_uniform_kernel<<<(unsigned)((n_pix + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, ld, n_pix, n_params, n_diff);
+    return launch_status("state_uniform_kernel");
 }
 
 static int check_layout(const char* who, int64_t n_pix, int n_params, int64_t ld) {

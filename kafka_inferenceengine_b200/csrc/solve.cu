@@ -51,6 +51,12 @@ __device__ __forceinline__ void band_row(const SolveBandDev& bd, int64_t ld, int
             s = fma(bd.row[p], xp[p], s);
         }
         h0 = w != 0.0 ? s : 0.0;
+    } else if (bd.kind == KAFKA_BAND_UNIFORM) {
+        // one linearisation point for the whole image: every thread reads the same
+        // D+1 values (L1 broadcast); unobserved pixels keep an empty row (utils.py:199-215)
+#pragma unroll
+        for (int p = 0; p < P; ++p) J[p] = (w != 0.0 && bd.src[p] >= 0) ? __ldg(bd.jac + bd.src[p]) : 0.0;
+        h0 = w != 0.0 ? __ldg(bd.h0) : 0.0;
     } else {
 #pragma unroll
         for (int p = 0; p < P; ++p) J[p] = bd.src[p] >= 0 ? ldg_stream(bd.jac + (int64_t)bd.src[p] * ld + i) : 0.0;
@@ -258,7 +264,7 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         if (h.kind == KAFKA_BAND_LINEAR) {
             for (int p = 0; p < n_params; ++p) d.row[p] = h.row[p];
             d.offset = h.offset;
-        } else if (h.kind == KAFKA_BAND_ARRAYS) {
+        } else if (h.kind == KAFKA_BAND_ARRAYS || h.kind == KAFKA_BAND_UNIFORM) {
             KAFKA_CHECK_ARG(h.h0 && h.jac, "kafka_solve_bands: band %d lacks h0/jac", b);
             KAFKA_CHECK_ARG(h.n_dim >= 1 && h.n_dim <= KAFKA_MAX_DIM, "kafka_solve_bands: band %d n_dim=%d", b, h.n_dim);
             d.h0 = h.h0;

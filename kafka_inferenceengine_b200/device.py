@@ -98,12 +98,31 @@ class DeviceVector(object):
         self.n_pix = int(n_pix)
         self.n_params = int(n_params)
         self._host = None
+        self._uniform = None          # None = unknown, False = pixels differ, ndarray = the shared vector
 
     # -- construction -----------------------------------------------------
     @classmethod
     def empty(cls, n_pix, n_params, device=None):
         device = device or default_device()
         return cls(_empty(n_params, padded(n_pix), device), n_pix, n_params)
+
+    def uniform_value(self):
+        """The state vector shared by ALL pixels, or None when pixels differ.
+        This is the test behind the reference's "one unique vector" shortcut
+        (kafka/inference/utils.py:72-74); decided once per vector by a device
+        reduction (kafka_state_uniform) and cached -- device vectors are never
+        modified after they are handed out."""
+        if self._uniform is None:
+            if self.n_pix == 0:
+                self._uniform = False
+            else:
+                n_diff = torch.zeros(1, dtype=torch.int32, device=self.device)
+                with torch.cuda.device(self.device):
+                    _lib.check(_lib.get_lib().kafka_state_uniform(_lib.ptr(self.data), self.ld, self.n_pix,
+                                                                  self.n_params, _lib.ptr(n_diff), _lib.stream_ptr()),
+                               "kafka_state_uniform")
+                self._uniform = self.data[:, 0].cpu().numpy() if int(n_diff.item()) == 0 else False
+        return None if self._uniform is False else self._uniform
 
     @classmethod
     def from_interleaved(cls, x, n_params, device=None):
@@ -130,6 +149,7 @@ class DeviceVector(object):
         mean = torch.as_tensor(np.asarray(mean, dtype=np.float64), device=device)
         out = cls.empty(n_pix, mean.numel(), device)
         out.data.copy_(mean[:, None].expand(-1, out.ld))
+        out._uniform = mean.cpu().numpy()
         return out
 
     # -- properties ---------------------------------------------------------

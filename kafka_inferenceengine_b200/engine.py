@@ -24,15 +24,25 @@ class BandBuffers(object):
 
 
 class ObservationStager(object):
-    """Pinned host staging + device raster buffers, reused across dates, for the
-    host -> device copy of one date's rasters (observations, inverse variance,
-    mask) followed by the compaction gather (solvers.py:90-93)."""
+    """Host -> device path of one date's rasters (observations, inverse variance,
+    mask), followed by the compaction gather (solvers.py:90-93).
+
+    The collaborator hands over ordinary (pageable) numpy rasters.  They are
+    copied band by band into pinned staging buffers by a small thread pool
+    (numpy releases the GIL for these copies), each band's DMA is queued on a
+    copy stream as soon as its staging is done, and the gather kernel of a band
+    waits only for that band's event -- so host memcpy, PCIe transfer and the
+    gathers overlap.  Buffers are allocated once and reused across dates."""
+
+    N_THREADS = 8
 
     def __init__(self, pix):
         self.pix = pix
         self.device = pix.device
         self._cap = 0
         self.h2d_bytes = 0
+        self._pool = None
+        self._copy_stream = None
 
     def _ensure(self, n_bands):
         if n_bands <= self._cap:
@@ -44,7 +54,12 @@ class ObservationStager(object):
         self.d_obs = torch.empty((n_bands, n), dtype=torch.float64, device=self.device)
         self.d_inv = torch.empty((n_bands, n), dtype=torch.float64, device=self.device)
         self.d_msk = torch.empty((n_bands, n), dtype=torch.uint8, device=self.device)
+        self._events = [torch.cuda.Event() for _ in range(n_bands)]
         self._cap = n_bands
+        if self._pool is None:
+            import concurrent.futures
+            self._pool = concurrent.futures.ThreadPoolExecutor(max_workers=self.N_THREADS)
+            self._copy_stream = torch.cuda.Stream(device=self.device)
 
     @staticmethod
     def _inv_var(unc, n):
@@ -56,6 +71,16 @@ class ObservationStager(object):
         if a.ndim == 2 and a.shape == (n, n):
             return np.diagonal(a)
         return a.reshape(-1)
+
+    def _stage(self, b, d, part, n_parts):
+        n = self.pix.n_raster
+        lo, hi = n * part // n_parts, n * (part + 1) // n_parts
+        obs = np.asarray(d.observations).reshape(-1)
+        np.copyto(self.h_obs[b].numpy()[lo:hi], obs[lo:hi], casting="unsafe")
+        inv = d._kafka_inv_var
+        np.copyto(self.h_inv[b].numpy()[lo:hi], inv[lo:hi], casting="unsafe")
+        msk = np.asarray(d.mask).reshape(-1)
+        np.not_equal(msk[lo:hi], 0, out=self.h_msk[b].numpy()[lo:hi].view(np.bool_))
 
     def upload(self, current_data, out=None):
         pix = self.pix
@@ -70,18 +95,35 @@ class ObservationStager(object):
                                 out.y[b], out.w[b], out.m[b])
             return out
         self._ensure(nb)
+        self._copy_stream.synchronize()              # DMA of the previous date has left the staging buffers
         n = pix.n_raster
-        for b, d in enumerate(current_data):
-            self.h_obs[b].numpy()[:] = np.asarray(d.observations, dtype=np.float64).reshape(-1)
-            self.h_inv[b].numpy()[:] = self._inv_var(d.uncertainty, n)
-            self.h_msk[b].numpy()[:] = np.asarray(d.mask).reshape(-1) != 0
-        self.d_obs[:nb].copy_(self.h_obs[:nb], non_blocking=True)
-        self.d_inv[:nb].copy_(self.h_inv[:nb], non_blocking=True)
-        self.d_msk[:nb].copy_(self.h_msk[:nb], non_blocking=True)
-        self.h2d_bytes += nb * n * 17
+        parts = max(1, min(self.N_THREADS, n // (1 << 20)))         # split big rasters across the pool
+        holders = []
+        for d in current_data:
+            h = _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
+            holders.append(h)
+        futures = [[self._pool.submit(self._stage, b, holders[b], k, parts) for k in range(parts)] for b in range(nb)]
+        main = torch.cuda.current_stream(self.device)
+        self._copy_stream.wait_stream(main)          # staging buffers of the previous date are free
         for b in range(nb):
+            for f in futures[b]:
+                f.result()
+            with torch.cuda.stream(self._copy_stream):
+                self.d_obs[b].copy_(self.h_obs[b], non_blocking=True)
+                self.d_inv[b].copy_(self.h_inv[b], non_blocking=True)
+                self.d_msk[b].copy_(self.h_msk[b], non_blocking=True)
+                self._events[b].record(self._copy_stream)
+            main.wait_event(self._events[b])
             pix.gather_band(self.d_obs[b], self.d_inv[b], self.d_msk[b], out.y[b], out.w[b], out.m[b])
+        self.h2d_bytes += nb * n * 17
         return out
+
+
+class _Staged(object):
+    __slots__ = ("observations", "mask", "_kafka_inv_var")
+
+    def __init__(self, observations, mask, inv_var):
+        self.observations, self.mask, self._kafka_inv_var = observations, mask, inv_var
 
 
 class SolveWorkspace(object):
@@ -106,8 +148,8 @@ class SolveWorkspace(object):
 def make_solve_bands(descs, bufs):
     """ctypes array of kafka_solve_band from python descriptors.
 
-    ``descs[b]`` is ("arrays", h0_row, jac_rows(D, ld), mapper) or
-    ("linear", row, offset)."""
+    ``descs[b]`` is ("arrays", h0_row, jac_rows(D, ld), mapper),
+    ("uniform", h0(1), jac(D), mapper) or ("linear", row, offset)."""
     nb = len(descs)
     arr = (_lib.SolveBand * max(nb, 1))()
     for b, d in enumerate(descs):
@@ -121,7 +163,7 @@ def make_solve_bands(descs, bufs):
                 sb.row[p] = float(row[p])
             sb.offset = float(d[2])
         else:
-            sb.kind = _lib.BAND_ARRAYS
+            sb.kind = _lib.BAND_UNIFORM if d[0] == "uniform" else _lib.BAND_ARRAYS
             _, h0, jac, mapper = d
             sb.h0 = h0.data_ptr()
             sb.jac = jac.data_ptr()

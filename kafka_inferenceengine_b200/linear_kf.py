@@ -40,7 +40,7 @@ class LinearKalman(object):
                  state_propagation=propagate_information_filter_LAI,
                  band_mapper=None,
                  linear=True, diagnostics=True, prior=None, *, device=None, comm=None,
-                 round_operator_f32=True):
+                 round_operator_f32=True, dedup_uniform_state=True):
         _lib.get_lib()                                   # fail now if the CUDA library is missing
         if not isinstance(create_observation_operator, ObservationOperator):
             raise NotImplementedError(
@@ -67,6 +67,7 @@ class LinearKalman(object):
         self._create_observation_operator = create_observation_operator
         self.comm = comm
         self.round_operator_f32 = bool(round_operator_f32)
+        self.dedup_uniform_state = bool(dedup_uniform_state)
         self.want_forward_modelled = False
         self._stager = engine.ObservationStager(self.pixels)
         self._ws = {}
@@ -273,7 +274,18 @@ class LinearKalman(object):
         cached = None                         # (sum of squares, count) of a repeatable solve
         while not_converged:
             if cached is None:
+                shared = x_prev.uniform_value() if (groups and self.dedup_uniform_state) else None
                 for group, (hsub, jsub, msub) in zip(groups, gbufs):
+                    if shared is not None:
+                        # every pixel is linearised at the same point (e.g. first iteration
+                        # after a prior reset): evaluate the emulators ONCE, as the reference's
+                        # run_emulator does for a single unique vector (utils.py:72-74)
+                        one = DeviceVector.broadcast(shared, 1, self.device)
+                        h1, j1 = linearize_bands(one, [(g[1], g[2]) for g in group], None, self.round_operator_f32)
+                        h1, j1 = h1[:, 0].contiguous(), j1[:, :, 0].contiguous()
+                        for k, g in enumerate(group):
+                            descs[g[0]] = ("uniform", h1[k], j1[k], g[2])
+                        continue
                     ev = self._tick("gp_linearize")
                     linearize_bands(x_prev, [(g[1], g[2]) for g in group], msub, self.round_operator_f32,
                                     h0=hsub, jac=jsub)
@@ -287,6 +299,7 @@ class LinearKalman(object):
                 self._tock(ev)
                 convergence_norm, count = self._global_norm(ws)   # linear_kf.py:293
                 x_analysis = x_new
+                x_analysis._uniform = False      # a solved state: skip the shared-vector test next iteration
             else:
                 # a linear operator relinearised at its own solution reproduces it:
                 # same system, same result, zero step (what the reference computes again)

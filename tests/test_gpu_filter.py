@@ -257,3 +257,57 @@ def test_unsupported_operator_raises():
     kf = kb.LinearKalman(None, None, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS)
     with pytest.raises(ValueError):
         kf.do_all_bands(None, [], np.zeros(3 * 10), None, np.eye(10))
+
+
+def test_uniform_first_iteration_shortcut_is_value_neutral():
+    """When every pixel is linearised at the same point (first iteration after a
+    prior reset) the emulators are evaluated once, like the reference's
+    single-unique-vector branch (utils.py:72-74): same results and iteration
+    counts as evaluating every pixel."""
+    mask, P, N, gps, obs, grid = _barrax_s2_case(1, seed=77)
+    inv = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
+    res = []
+    for dedup in (True, False):
+        kf = kb.LinearKalman(obs, syn.MemoryOutput(syn.S2_PARAMETERS), mask, kb.create_prosail_observation_operator,
+                             syn.S2_PARAMETERS, state_propagation=None, prior=None, dedup_uniform_state=dedup)
+        data = [obs.get_band_data(obs.dates[0], b) for b in range(10)]
+        for x0 in (DeviceVector.broadcast(syn.SAIL_MEAN, N, gu.DEV), np.tile(syn.SAIL_MEAN, N)):
+            x, _, A, innov = kf.do_all_bands(obs.dates[0], data, x0, None, BlockDiag.from_block(inv, N, gu.DEV))
+            res.append((np.asarray(x), A.blocks(), np.asarray(innov), kf.last_iterations[-1], kf.last_norms[-1]))
+    ref = res[-1]                                   # dedup off, host input
+    for r in res[:-1]:
+        assert r[3] == ref[3]
+        assert np.max(np.abs(r[0] - ref[0]) / np.maximum(np.abs(ref[0]), 1e-3)) < 1e-12
+        assert np.max(gu.rel(r[1], ref[1], floor=1e-3)) < 1e-12
+        assert np.allclose(r[2], ref[2], rtol=1e-12, atol=1e-15)
+        assert np.allclose(r[4], ref[4], rtol=1e-9)
+    # the detector itself
+    v = DeviceVector.from_interleaved(np.tile(syn.SAIL_MEAN, 5000), P, gu.DEV)
+    assert np.array_equal(v.uniform_value(), syn.SAIL_MEAN)
+    x = np.tile(syn.SAIL_MEAN, 5000)
+    x[P * 4999 + 3] = np.nextafter(x[P * 4999 + 3], 1.0)
+    assert DeviceVector.from_interleaved(x, P, gu.DEV).uniform_value() is None
+
+
+def test_raster_output_stage_matches_reference_arithmetic():
+    """RasterOutput.dump_data = the arithmetic of KafkaOutput.dump_data
+    (input_output/observations.py:374-375,392-393): float32 rasters of the mean
+    and of 1/sqrt(diag(P^-1)), zero outside the state mask."""
+    from kafka_inferenceengine_b200.output import RasterOutput
+    rng = np.random.default_rng(3)
+    mask = gio.barrax_mask()
+    N, P = int(mask.sum()), 10
+    x = rng.standard_normal(N * P)
+    blocks = gu.random_spd(rng, N, P)
+    got = {}
+    out = RasterOutput(syn.S2_PARAMETERS, sink=lambda t, names, mean, unc: got.update(mean=mean.copy(), unc=unc.copy()))
+    out.dump_data(dt.datetime(2017, 7, 3), x, None, kc.blocks_to_sparse(blocks), mask, P)
+    diag = blocks[:, np.arange(P), np.arange(P)].ravel()
+    for ii in range(P):
+        assert np.array_equal(got["mean"][ii], kc.scatter_param(x, ii, P, mask))
+        assert np.allclose(got["unc"][ii], kc.scatter_unc(diag, ii, P, mask), rtol=2e-7, atol=0)
+    assert out.d2h_bytes == 2 * P * mask.size * 4
+    # and with the device objects LinearKalman hands over
+    out.dump_data(dt.datetime(2017, 7, 4), DeviceVector.from_interleaved(x, P, gu.DEV), None,
+                  BlockDiag.from_blocks(blocks, gu.DEV), mask, P)
+    assert np.array_equal(out.last[1], got["mean"])
