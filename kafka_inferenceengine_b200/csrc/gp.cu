@@ -9,10 +9,16 @@
 //             e_j = ln s_f - 0.5 sum_d theta_d X'_jd^2
 //     w_j   = k_j alpha_j,   mean = sum_j w_j,   G_d = sum_j w_j zh_jd
 //     dmean/dx_d = G_d - theta_d x'_d mean
-// i.e. 2D+3 fp64 FMAs + one exp per (pixel, band, training point); the training
-// table (T rows of {zh[D], e, alpha}) is staged once per CTA in shared memory by
-// a TMA bulk copy and then read as warp-wide broadcasts.  The kernel is bound by
-// the fp64 pipe, not by HBM.
+// The table stores zh and e pre-multiplied by L = 64/ln2, so the dot product IS the
+// base-2^(1/64) exponent: k = rint(a), r = a - k is exact, 2^(k/64) comes from a
+// 64-entry table and exp(r ln2/64) from a degree-5 polynomial (|r| <= 1/2, truncation
+// 3.5e-17).  The per-pixel factor exp(-0.5 sum theta x'^2) is pulled out of the loop and
+// applied once at the end (a warp keeps it inside the exponent when one of its pixels is so
+// far from the centre that the un-shifted exponent could overflow).  Per (pixel, band,
+// training point): 2D FMAs + ~11 fp64 ops, i.e. 31 fp64-pipe instructions at D=10 against
+// the 5D+28 = 78 flops of the textbook form.  The training table (T rows of {zh[D], e,
+// alpha}) is staged once per CTA in shared memory by a TMA bulk copy and then read as
+// warp-wide broadcasts.  The kernel is bound by the fp64 pipe, not by HBM.
 #include <math.h>
 #include <math_constants.h>
 
@@ -20,7 +26,7 @@
 
 namespace kafka {
 
-__constant__ double c_exp2_tab[32] = {
+__constant__ double c_exp2_tab[64] = {
 #include "exp_table.inc"
 };
 
@@ -58,30 +64,41 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
-// ---- exp: 2^(k/32) table + degree-6 polynomial, ~11 fp64 ops --------------------
-// |rel err| < 4e-16 on [-708, 709]; underflows to 0 below, NaN propagates.
-__device__ __forceinline__ double fast_exp(double x, const double* __restrict__ tab32) {
-    const double kL = 4.61662413084468283841e+01;        // 32/ln2
-    const double kC1 = 2.16608493865351192653e-02;       // ln2/32, high bits (k*C1 exact)
-    const double kC2 = 5.96317165397058656257e-12;       // ln2/32 - C1
+// ---- exp in base 2^(1/64): argument already scaled by L = 64/ln2 ------------------
+constexpr double kL = 9.23324826168936567683e+01;        // 64/ln2
+constexpr double kInvL = 1.08304246962491450973e-02;     // ln2/64
+constexpr double kFarShift = 600.0 * kL;                 // beyond this the per-pixel factor stays in the exponent
+constexpr uint32_t kHiUnder = 0x40efeb6cu;               // high word of 708 L
+constexpr uint32_t kHiOver = 0x40eff6f7u;                // high word of 709 L
+
+// exp(a / L).  fp64-pipe cost: 3 adds + 5 FMAs + 1 mul; every range test is an integer
+// compare/select on the high word, so the function is branch-free and the compiler can
+// interleave several evaluations.  |rel err| < 3e-16 for -708 L <= a < 709 L; exactly 0
+// below, +inf above, NaN for NaN.
+__device__ __forceinline__ double exp_scaled(double a, const double* __restrict__ tab64) {
     const double kMagic = 6755399441055744.0;            // 1.5 * 2^52
-    double t = fma(x, kL, kMagic);
-    int k = __double2loint(t);
-    double kd = t - kMagic;
-    double r = fma(kd, -kC1, x);
-    r = fma(kd, -kC2, r);
-    double p = fma(r, 1.0 / 720.0, 1.0 / 120.0);
-    p = fma(p, r, 1.0 / 24.0);
-    p = fma(p, r, 1.0 / 6.0);
-    p = fma(p, r, 0.5);
+    const double t = a + kMagic;
+    const int k = __double2loint(t);
+    const double r = a - (t - kMagic);                   // exact, |r| <= 1/2
+    double p = fma(r, 1.24178437017169252822e-12, 5.73285168864040188714e-10);
+    p = fma(p, r, 2.11731371554647762752e-07);
+    p = fma(p, r, 5.86490495505616996649e-05);
+    p = fma(p, r, 1.08304246962491450973e-02);
     p = fma(p, r, 1.0);
-    p = fma(p, r, 1.0);
-    double v = tab32[k & 31] * p;
-    int hi = __double2hiint(v) + ((k >> 5) << 20);
-    double res = __hiloint2double(hi, __double2loint(v));
-    if (!(x >= -708.0)) res = (x != x) ? x : 0.0;
-    if (x > 709.0) res = CUDART_INF;
-    return res;
+    const double v = tab64[k & 63] * p;
+    int hi = __double2hiint(v) + ((k >> 6) << 20);
+    int lo = __double2loint(v);
+    const int ha = __double2hiint(a);
+    const uint32_t mag = (uint32_t)ha & 0x7fffffffu;
+    // (uint32)ha >= 0x80000000 + kHiUnder  <=>  a <= -708 L (or -inf / negative NaN)
+    const bool under = (uint32_t)ha >= (0x80000000u + kHiUnder);
+    const bool over = (uint32_t)(ha - (int)kHiOver) < (0x7ff00001u - kHiOver);   // 709 L <= a <= +inf
+    const bool nan = (mag + (uint32_t)(__double2loint(a) != 0)) > 0x7ff00000u;
+    hi = under ? 0 : hi;
+    hi = over ? 0x7ff00000 : hi;
+    hi = nan ? 0x7ff80000 : hi;
+    lo = (mag >= kHiUnder) ? 0 : lo;
+    return __hiloint2double(hi, lo);
 }
 
 // ---- linearise: mean + Jacobian for every (pixel, band) -------------------------
@@ -103,20 +120,51 @@ struct GpLinParams {
 
 constexpr int kGpThreads = 128;
 
+// Inner loop over the training points of one band for PPT pixels per thread.
+// rows[j] = {L zh[DP], L e, alpha} in shared memory, read as warp-wide broadcasts.
+template <int D, int PPT, bool kShiftInside>
+__device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, int T, const double (&xr)[PPT][D],
+                                              const double (&sh)[PPT], double (&mu)[PPT], double (&G)[PPT][D],
+                                              const double* __restrict__ tab64) {
+    constexpr int DP = dpad(D), RS = tab_row(D);
+#pragma unroll 2
+    for (int j = 0; j < T; ++j) {
+        const double* row = rows + j * RS;
+        double zh[DP];
+#pragma unroll
+        for (int d = 0; d < DP; d += 2) {
+            double2 v = *reinterpret_cast<const double2*>(row + d);
+            zh[d] = v.x;
+            zh[d + 1] = v.y;
+        }
+        const double2 ea = *reinterpret_cast<const double2*>(row + DP);
+#pragma unroll
+        for (int pp = 0; pp < PPT; ++pp) {
+            double a = kShiftInside ? ea.x + sh[pp] : ea.x;
+#pragma unroll
+            for (int d = 0; d < D; ++d) a = fma(zh[d], xr[pp][d], a);
+            const double w = exp_scaled(a, tab64) * ea.y;
+            mu[pp] += w;
+#pragma unroll
+            for (int d = 0; d < D; ++d) G[pp][d] = fma(w, zh[d], G[pp][d]);
+        }
+    }
+}
+
 template <int D, int PPT>
 __global__ void __launch_bounds__(kGpThreads)
 gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     extern __shared__ __align__(16) double smem[];
     __shared__ uint64_t bar;
-    __shared__ double s_exp[32];
+    __shared__ double s_exp[64];
 
     const GpBandDev& band = prm.bands[blockIdx.y];
     const int T = band.n_train;
     const uint32_t bytes = (uint32_t)((HDR + T * RS) * sizeof(double));
 
     if (threadIdx.x == 0) mbar_init(&bar, 1);
-    if (threadIdx.x < 32) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    if (threadIdx.x < 64) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
     __syncthreads();
     if (threadIdx.x == 0) {
         mbar_expect_tx(&bar, bytes);
@@ -150,6 +198,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     const double* rows = smem + HDR;
 
     double sh[PPT], mu[PPT], G[PPT][D];
+    bool far = false;
 #pragma unroll
     for (int pp = 0; pp < PPT; ++pp) {
         double s = 0.0;
@@ -159,37 +208,30 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
             s = fma(theta_e[d] * xr[pp][d], xr[pp][d], s);
             G[pp][d] = 0.0;
         }
-        sh[pp] = -0.5 * s;
+        sh[pp] = (-0.5 * kL) * s;                          // scaled like the table
         mu[pp] = 0.0;
+        far |= live[pp] && !(sh[pp] > -kFarShift);         // also true for NaN; padding lanes do not count
     }
 
     if (__any_sync(0xffffffffu, any_live)) {
-#pragma unroll 2
-        for (int j = 0; j < T; ++j) {
-            const double* row = rows + j * RS;
-            double zh[DP];
-#pragma unroll
-            for (int d = 0; d < DP; d += 2) {
-                double2 v = *reinterpret_cast<const double2*>(row + d);
-                zh[d] = v.x;
-                zh[d + 1] = v.y;
-            }
-            double2 ea = *reinterpret_cast<const double2*>(row + DP);
+        // common case: exp(sh) is applied after the loop; a warp with a far-away pixel keeps
+        // sh inside the exponent so that nothing can overflow
+        if (!__any_sync(0xffffffffu, far)) {
+            gp_accumulate<D, PPT, false>(rows, T, xr, sh, mu, G, s_exp);
 #pragma unroll
             for (int pp = 0; pp < PPT; ++pp) {
-                double a0 = ea.x + sh[pp], a1 = 0.0;
+                const double scale = exp_scaled(sh[pp], s_exp);
+                mu[pp] *= scale;
 #pragma unroll
-                for (int d = 0; d + 1 < D; d += 2) {
-                    a0 = fma(zh[d], xr[pp][d], a0);
-                    a1 = fma(zh[d + 1], xr[pp][d + 1], a1);
-                }
-                if (D & 1) a0 = fma(zh[D - 1], xr[pp][D - 1], a0);
-                double w = fast_exp(a0 + a1, s_exp) * ea.y;
-                mu[pp] += w;
-#pragma unroll
-                for (int d = 0; d < D; ++d) G[pp][d] = fma(w, zh[d], G[pp][d]);
+                for (int d = 0; d < D; ++d) G[pp][d] *= scale;
             }
+        } else {
+            gp_accumulate<D, PPT, true>(rows, T, xr, sh, mu, G, s_exp);
         }
+#pragma unroll
+        for (int pp = 0; pp < PPT; ++pp)
+#pragma unroll
+            for (int d = 0; d < D; ++d) G[pp][d] *= kInvL;  // table rows are L * zh
     }
 
     const bool r32 = (prm.flags & KAFKA_ROUND_F32) != 0;
@@ -215,10 +257,10 @@ gp_hessian_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, con
                   double* __restrict__ hess) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D), L = tri_count(D);
     extern __shared__ __align__(16) double smem[];
-    __shared__ double s_exp[32];
+    __shared__ double s_exp[64];
     const int total = HDR + T * RS;
     for (int k = threadIdx.x; k < total; k += kGpThreads) smem[k] = table[k];
-    if (threadIdx.x < 32) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    if (threadIdx.x < 64) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
     __syncthreads();
     int64_t i = (int64_t)blockIdx.x * kGpThreads + threadIdx.x;
     if (i >= n_pts) return;
@@ -234,16 +276,16 @@ gp_hessian_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, con
     }
 #pragma unroll
     for (int c = 0; c < L; ++c) acc[c] = 0.0;
-    const double sh = -0.5 * s;
+    const double sh = (-0.5 * kL) * s;
     for (int j = 0; j < T; ++j) {
         const double* row = rows + j * RS;
         double a = row[DP] + sh, u[D];
 #pragma unroll
         for (int d = 0; d < D; ++d) {
             a = fma(row[d], xr[d], a);
-            u[d] = row[d] - tx[d];
+            u[d] = fma(row[d], kInvL, -tx[d]);
         }
-        double w = fast_exp(a, s_exp) * row[DP + 1];
+        double w = exp_scaled(a, s_exp) * row[DP + 1];
         mu += w;
 #pragma unroll
         for (int r = 0; r < D; ++r) {
@@ -267,8 +309,8 @@ __global__ void __launch_bounds__(128)
 gp_variance_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, const double* __restrict__ table, int T,
                    int D, const double* __restrict__ inv_q, double* __restrict__ var) {
     extern __shared__ double kbuf[];             // [4 warps][T]
-    __shared__ double s_exp[32];
-    if (threadIdx.x < 32) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    __shared__ double s_exp[64];
+    if (threadIdx.x < 64) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
     __syncthreads();
     const int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -282,9 +324,9 @@ gp_variance_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, co
     }
     for (int j = lane; j < T; j += 32) {
         const double* row = table + HDR + (size_t)j * RS;
-        double a = row[DP] - 0.5 * s;
+        double a = row[DP] - (0.5 * kL) * s;
         for (int d = 0; d < D; ++d) a = fma(row[d], xin[(int64_t)d * ld + i] - table[DP + d], a);
-        kv[j] = fast_exp(a, s_exp);
+        kv[j] = exp_scaled(a, s_exp);
     }
     __syncwarp();
     double acc = 0.0;
@@ -374,10 +416,11 @@ int kafka_gp_pack_host(const double* inputs, const double* theta, const double* 
         double c = 0.0;
         for (int d = 0; d < D; ++d) {
             double xc = inputs[(size_t)j * D + d] - centre[d];
-            row[d] = theta_e[d] * xc;
-            c = fma(row[d], xc, c);
+            double zh = theta_e[d] * xc;
+            c = fma(zh, xc, c);
+            row[d] = kL * zh;                         // rows are stored in units of ln2/64
         }
-        row[DP] = theta[D] - 0.5 * c;
+        row[DP] = kL * (theta[D] - 0.5 * c);
         row[DP + 1] = invqt[j];
     }
     return 0;
