@@ -325,7 +325,8 @@ def main():
     inv_block = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
 
     def make_filter(obs, out):
-        prior = syn.BroadcastPrior(syn.SAIL_MEAN, inv_block, n_pix, lambda blk, n: BlockDiag.from_block(blk, n, device))
+        prior = syn.BroadcastPrior(syn.SAIL_MEAN, inv_block, n_pix, lambda blk, n: BlockDiag.from_block(blk, n, device),
+                                   lambda m, n: DeviceVector.broadcast(m, n, device))
         kf = kb.LinearKalman(obs, out, state_mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS,
                              state_propagation=None, prior=prior, linear=False, device=device, comm=comm)
         kf.set_trajectory_model()
@@ -390,34 +391,41 @@ def main():
     kf.dedup_uniform_state = True
 
     # ---------------- e2e: host rasters through LinearKalman.run -----------
+    # ONE run() call over a time grid with one observation date per interval, as a user
+    # processes a time series: per date the host rasters go host->device (pageable numpy,
+    # staged through pinned memory), the state is reset to the prior (kafka_test_S2.py:177-178),
+    # the date is assimilated and the float32 mean / uncertainty rasters are read back.
     e2e = None
     if not args.no_e2e:
         from kafka_inferenceengine_b200.output import RasterOutput
-        obs_host = HostObservations([date], gps, rho, inv, mask, shape)
+        n_warm = max(2, args.warmup)
+        all_dates = [base + dt.timedelta(days=d, hours=12) for d in range(n_warm + args.steps)]
+        obs_host = HostObservations(all_dates, gps, rho, inv, mask, shape)
         out = RasterOutput(syn.S2_PARAMETERS)          # float32 mean + 1/sqrt(diag) rasters, read back to the host
         kf2, prior2 = make_filter(obs_host, out)
         out.pixels = kf2.pixels
         kf2.set_trajectory_uncertainty(0.0)
         # the prior (one mean vector, one block for all pixels) is a constant of the run and
         # stays on the device; the per-step inputs -- the date's rasters -- come from the host
-        x0h, Pinv0h = x0, Pinv0
-        for _ in range(max(1, args.warmup - 1)):
-            kf2.run(grid, x0h, None, Pinv0h, iter_obs_op=True)
+        x0h, Pinv0h = prior2.process_prior(None)
+        grid_warm = [base + dt.timedelta(days=d) for d in range(n_warm + 1)]
+        grid_timed = [base + dt.timedelta(days=n_warm + d) for d in range(args.steps + 1)]
+        kf2.run(grid_warm, x0h, None, Pinv0h, iter_obs_op=True)
         barrier()
         h2d0, d2h0 = kf2._stager.h2d_bytes, out.d2h_bytes
         t0 = time.perf_counter()
-        for _ in range(args.steps):
-            kf2.run(grid, x0h, None, Pinv0h, iter_obs_op=True)
+        kf2.run(grid_timed, x0h, None, Pinv0h, iter_obs_op=True)
         torch.cuda.synchronize()
         ms_e2e = max_over_ranks(1e3 * (time.perf_counter() - t0)) / args.steps
         barrier()
         e2e = {"value": world * n_pix / (ms_e2e * 1e-3), "unit": "pixel-dates/s", "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": (kf2._stager.h2d_bytes - h2d0) // args.steps,
                "d2h_bytes_per_step": (out.d2h_bytes - d2h0) // args.steps,
-               "api": "LinearKalman.run(time_grid, x_forecast, None, P_forecast_inverse): host numpy rasters from "
-                      "observations.get_band_data (pageable, float64 obs + inverse variance + bool mask), "
-                      "output.dump_data = RasterOutput (float32 mean and 1/sqrt(diag P^-1) rasters read back to "
-                      "host, as KafkaOutput.dump_data writes them)"}
+               "api": "one LinearKalman.run(time_grid, x_forecast, None, P_forecast_inverse) over %d dates: host numpy "
+                      "rasters from observations.get_band_data (pageable, float64 obs + inverse variance + bool mask) "
+                      "copied host->device every date, prior-only advance, output.dump_data = RasterOutput "
+                      "(float32 mean and 1/sqrt(diag P^-1) rasters read back to the host every date, as "
+                      "KafkaOutput.dump_data writes them)" % args.steps}
         del kf2, obs_host
 
     if rank != 0:

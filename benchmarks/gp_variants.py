@@ -1,0 +1,98 @@
+"""Sweep compile-time variants of the GP emulator kernel (csrc/gp.cu tuning knobs).
+
+    python benchmarks/gp_variants.py build     # here (nvcc, no GPU needed)
+    python benchmarks/gp_variants.py run       # on the GPU box
+
+Each variant is a stand-alone .so built from layout.cu (error helpers) + gp.cu with
+-D flags; the run step times kafka_gp_linearize on 4 M pixels x 10 bands x 250
+training points and checks the output against the default build.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(ROOT, "kafka_inferenceengine_b200", "csrc")
+OUT = os.path.join(HERE, "variants")
+VARIANTS = {
+    "default": [],
+    "ppt1": ["-DKAFKA_GP_FORCE_PPT=1"],
+    "ppt1_u4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_UNROLL=4"],
+    "ppt2_u1": ["-DKAFKA_GP_UNROLL=1"],
+    "ppt2_u4": ["-DKAFKA_GP_UNROLL=4"],
+    "ppt2_t256": ["-DKAFKA_GP_THREADS=256"],
+    "ppt2_t64": ["-DKAFKA_GP_THREADS=64"],
+    "ppt2_mb4": ["-DKAFKA_GP_MINBLOCKS=4"],
+    "ppt1_t256": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_THREADS=256"],
+    "ppt1_mb5": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=5"],
+}
+
+
+def build():
+    os.makedirs(OUT, exist_ok=True)
+    procs = []
+    for name, flags in VARIANTS.items():
+        cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler",
+               "-fPIC", "--expt-relaxed-constexpr", "-shared", "-o", os.path.join(OUT, name + ".so"),
+               os.path.join(CSRC, "layout.cu"), os.path.join(CSRC, "gp.cu")] + flags
+        procs.append((name, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
+    for name, p in procs:
+        out = p.communicate()[0].decode()
+        print(name, "ok" if p.returncode == 0 else "FAILED\n" + out)
+
+
+def run():
+    import numpy as np
+    import torch
+    sys.path.insert(0, ROOT)
+    from kafka_inferenceengine_b200 import _lib, synthetic as syn
+    dev = torch.device("cuda:0")
+    P = B = 10
+    n = 4_000_000
+    rng = np.random.default_rng(1)
+    gps = [syn.make_emulator(rng, syn.SAIL_MEAN, syn.SAIL_SIGMA, n_train=250) for _ in range(B)]
+    tabs = [torch.from_numpy(_lib.gp_pack(g.inputs, g.theta, g.invQt)).to(dev) for g in gps]
+    gen = torch.Generator(device=dev).manual_seed(5)
+    x = torch.from_numpy(syn.SAIL_MEAN).to(dev)[:, None] + torch.from_numpy(syn.SAIL_SIGMA).to(dev)[:, None] * \
+        torch.randn((P, n), generator=gen, dtype=torch.float64, device=dev)
+    h0 = torch.empty((B, n), dtype=torch.float64, device=dev)
+    jac = torch.empty((B, P, n), dtype=torch.float64, device=dev)
+    ref = None
+    for name in VARIANTS:
+        path = os.path.join(OUT, name + ".so")
+        if not os.path.exists(path):
+            continue
+        lib = C.CDLL(path)
+        fn = lib.kafka_gp_linearize
+        fn.restype = C.c_int
+        fn.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.POINTER(_lib.GpBand), C.c_int, C.c_void_p, C.c_void_p,
+                       C.c_void_p, C.c_uint32, C.c_void_p]
+        arr = (_lib.GpBand * B)()
+        for b in range(B):
+            arr[b].table, arr[b].n_train, arr[b].n_dim = tabs[b].data_ptr(), 250, P
+            for d in range(P):
+                arr[b].mapper[d] = d
+        def call():
+            rc = fn(x.data_ptr(), n, n, arr, B, None, h0.data_ptr(), jac.data_ptr(), 0, None)
+            assert rc == 0, rc
+        call(); call()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            call()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 3
+        if ref is None:
+            ref = (h0.clone(), jac.clone())
+        err = max(((h0 - ref[0]).abs() / ref[0].abs().clamp_min(1e-3)).max().item(),
+                  ((jac - ref[1]).abs() / ref[1].abs().clamp_min(1e-3)).max().item())
+        tf = n * B * 250 * 78 / (ms * 1e-3) / 1e12
+        print("%-12s %8.3f ms  %6.2f TF/s(algorithmic)  max rel diff vs default %.2e" % (name, ms, tf, err))
+
+
+if __name__ == "__main__":
+    {"build": build, "run": run}[sys.argv[1]]()

@@ -118,7 +118,21 @@ struct GpLinParams {
     uint32_t flags;
 };
 
-constexpr int kGpThreads = 128;
+// tuning knobs (defaults are the measured best; benchmarks/gp_variants.py sweeps them)
+#ifndef KAFKA_GP_THREADS
+#define KAFKA_GP_THREADS 128
+#endif
+#ifndef KAFKA_GP_UNROLL
+#define KAFKA_GP_UNROLL 2
+#endif
+#ifndef KAFKA_GP_MINBLOCKS
+#define KAFKA_GP_MINBLOCKS 1
+#endif
+#ifndef KAFKA_GP_FORCE_PPT
+#define KAFKA_GP_FORCE_PPT 0
+#endif
+constexpr int kGpThreads = KAFKA_GP_THREADS;
+constexpr int kGpUnroll = KAFKA_GP_UNROLL;
 
 // Inner loop over the training points of one band for PPT pixels per thread.
 // rows[j] = {L zh[DP], L e, alpha} in shared memory, read as warp-wide broadcasts.
@@ -127,7 +141,7 @@ __device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, i
                                               const double (&sh)[PPT], double (&mu)[PPT], double (&G)[PPT][D],
                                               const double* __restrict__ tab64) {
     constexpr int DP = dpad(D), RS = tab_row(D);
-#pragma unroll 2
+#pragma unroll kGpUnroll
     for (int j = 0; j < T; ++j) {
         const double* row = rows + j * RS;
         double zh[DP];
@@ -152,7 +166,7 @@ __device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, i
 }
 
 template <int D, int PPT>
-__global__ void __launch_bounds__(kGpThreads)
+__global__ void __launch_bounds__(kGpThreads, KAFKA_GP_MINBLOCKS)
 gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     extern __shared__ __align__(16) double smem[];
@@ -164,7 +178,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     const uint32_t bytes = (uint32_t)((HDR + T * RS) * sizeof(double));
 
     if (threadIdx.x == 0) mbar_init(&bar, 1);
-    if (threadIdx.x < 64) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    for (int k = threadIdx.x; k < 64; k += kGpThreads) s_exp[k] = c_exp2_tab[k];
     __syncthreads();
     if (threadIdx.x == 0) {
         mbar_expect_tx(&bar, bytes);
@@ -359,7 +373,10 @@ static int dispatch_ppt(const GpLinParams& prm, int n_bands, int max_T, cudaStre
     // two pixels per thread halve the shared-memory operand traffic per FMA; only
     // worth it when the grid still fills the machine several times over
     int64_t ctas2 = (prm.n_pix + 2 * kGpThreads - 1) / (2 * kGpThreads) * n_bands;
-    if (ctas2 >= 8 * (int64_t)num_sms()) return launch_linearize<D, 2>(prm, n_bands, max_T, s);
+    bool two = ctas2 >= 8 * (int64_t)num_sms();
+    if (KAFKA_GP_FORCE_PPT == 1) two = false;
+    if (KAFKA_GP_FORCE_PPT == 2) two = true;
+    if (two) return launch_linearize<D, 2>(prm, n_bands, max_T, s);
     return launch_linearize<D, 1>(prm, n_bands, max_T, s);
 }
 

@@ -23,43 +23,64 @@ class BandBuffers(object):
         self.m = torch.zeros((n_bands, ld), dtype=torch.uint8, device=device)
 
 
+class _Slot(object):
+    """One set of pinned staging buffers + device rasters."""
+
+    def __init__(self, n_bands, n, device):
+        self.cap = n_bands
+        self.h_obs = torch.empty((n_bands, n), dtype=torch.float64).pin_memory()
+        self.h_inv = torch.empty((n_bands, n), dtype=torch.float64).pin_memory()
+        self.h_msk = torch.empty((n_bands, n), dtype=torch.uint8).pin_memory()
+        self.d_obs = torch.empty((n_bands, n), dtype=torch.float64, device=device)
+        self.d_inv = torch.empty((n_bands, n), dtype=torch.float64, device=device)
+        self.d_msk = torch.empty((n_bands, n), dtype=torch.uint8, device=device)
+        self.copied = [torch.cuda.Event() for _ in range(n_bands)]   # H2D of band b done
+        self.gathered = None                                         # main stream finished reading d_*
+
+
+class StagedDate(object):
+    """Hand-over between ``stage`` and ``finish``."""
+    __slots__ = ("slot", "n_bands", "device_data")
+
+    def __init__(self, slot, n_bands, device_data=None):
+        self.slot, self.n_bands, self.device_data = slot, n_bands, device_data
+
+
 class ObservationStager(object):
     """Host -> device path of one date's rasters (observations, inverse variance,
     mask), followed by the compaction gather (solvers.py:90-93).
 
-    The collaborator hands over ordinary (pageable) numpy rasters.  They are
-    copied band by band into pinned staging buffers by a small thread pool
-    (numpy releases the GIL for these copies), each band's DMA is queued on a
-    copy stream as soon as its staging is done, and the gather kernel of a band
-    waits only for that band's event -- so host memcpy, PCIe transfer and the
-    gathers overlap.  Buffers are allocated once and reused across dates."""
+    The collaborator hands over ordinary (pageable) numpy rasters.  ``stage``
+    copies them band by band into pinned staging buffers with a small thread
+    pool (numpy releases the GIL for these copies) and queues each band's DMA on
+    a copy stream as soon as its staging is done; ``finish`` makes the compute
+    stream wait for each band's event and runs the gather kernels.  Two buffer
+    sets alternate, so the NEXT date can be staged and copied while the kernels
+    of the current date are still running (``LinearKalman`` does that from its
+    iteration loop).  Buffers are allocated once and reused across dates."""
 
     N_THREADS = 8
+    N_SLOTS = 2
 
     def __init__(self, pix):
         self.pix = pix
         self.device = pix.device
-        self._cap = 0
         self.h2d_bytes = 0
+        self._slots = [None] * self.N_SLOTS
+        self._next = 0
         self._pool = None
         self._copy_stream = None
 
-    def _ensure(self, n_bands):
-        if n_bands <= self._cap:
-            return
-        n = self.pix.n_raster
-        self.h_obs = torch.empty((n_bands, n), dtype=torch.float64).pin_memory()
-        self.h_inv = torch.empty((n_bands, n), dtype=torch.float64).pin_memory()
-        self.h_msk = torch.empty((n_bands, n), dtype=torch.uint8).pin_memory()
-        self.d_obs = torch.empty((n_bands, n), dtype=torch.float64, device=self.device)
-        self.d_inv = torch.empty((n_bands, n), dtype=torch.float64, device=self.device)
-        self.d_msk = torch.empty((n_bands, n), dtype=torch.uint8, device=self.device)
-        self._events = [torch.cuda.Event() for _ in range(n_bands)]
-        self._cap = n_bands
+    def _slot(self, n_bands):
+        k = self._next
+        self._next = (k + 1) % self.N_SLOTS
+        if self._slots[k] is None or self._slots[k].cap < n_bands:
+            self._slots[k] = _Slot(n_bands, self.pix.n_raster, self.device)
         if self._pool is None:
             import concurrent.futures
             self._pool = concurrent.futures.ThreadPoolExecutor(max_workers=self.N_THREADS)
             self._copy_stream = torch.cuda.Stream(device=self.device)
+        return self._slots[k]
 
     @staticmethod
     def _inv_var(unc, n):
@@ -72,51 +93,59 @@ class ObservationStager(object):
             return np.diagonal(a)
         return a.reshape(-1)
 
-    def _stage(self, b, d, part, n_parts):
-        n = self.pix.n_raster
-        lo, hi = n * part // n_parts, n * (part + 1) // n_parts
-        obs = np.asarray(d.observations).reshape(-1)
-        np.copyto(self.h_obs[b].numpy()[lo:hi], obs[lo:hi], casting="unsafe")
-        inv = d._kafka_inv_var
-        np.copyto(self.h_inv[b].numpy()[lo:hi], inv[lo:hi], casting="unsafe")
-        msk = np.asarray(d.mask).reshape(-1)
-        np.not_equal(msk[lo:hi], 0, out=self.h_msk[b].numpy()[lo:hi].view(np.bool_))
+    @staticmethod
+    def _stage_part(slot, b, d, lo, hi):
+        np.copyto(slot.h_obs[b].numpy()[lo:hi], np.asarray(d.observations).reshape(-1)[lo:hi], casting="unsafe")
+        np.copyto(slot.h_inv[b].numpy()[lo:hi], d._kafka_inv_var[lo:hi], casting="unsafe")
+        np.not_equal(np.asarray(d.mask).reshape(-1)[lo:hi], 0, out=slot.h_msk[b].numpy()[lo:hi].view(np.bool_))
 
-    def upload(self, current_data, out=None):
-        pix = self.pix
+    def stage(self, current_data):
+        """Start moving one date's rasters to the device; returns a token for ``finish``."""
         nb = len(current_data)
-        out = out or BandBuffers(nb, pix, self.device)
-        on_device = all(isinstance(d.observations, torch.Tensor) and d.observations.is_cuda for d in current_data)
-        if on_device:
-            # inputs already resident in HBM (device rasters): gather only
-            for b, d in enumerate(current_data):
-                pix.gather_band(d.observations.reshape(-1), d.uncertainty.reshape(-1),
-                                d.mask.reshape(-1).view(torch.uint8) if d.mask.dtype == torch.bool else d.mask.reshape(-1),
-                                out.y[b], out.w[b], out.m[b])
-            return out
-        self._ensure(nb)
-        self._copy_stream.synchronize()              # DMA of the previous date has left the staging buffers
-        n = pix.n_raster
-        parts = max(1, min(self.N_THREADS, n // (1 << 20)))         # split big rasters across the pool
-        holders = []
-        for d in current_data:
-            h = _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
-            holders.append(h)
-        futures = [[self._pool.submit(self._stage, b, holders[b], k, parts) for k in range(parts)] for b in range(nb)]
-        main = torch.cuda.current_stream(self.device)
-        self._copy_stream.wait_stream(main)          # staging buffers of the previous date are free
+        if all(isinstance(d.observations, torch.Tensor) and d.observations.is_cuda for d in current_data):
+            return StagedDate(None, nb, list(current_data))       # already resident in HBM
+        slot = self._slot(nb)
+        n = self.pix.n_raster
+        slot.copied[nb - 1].synchronize()            # host: the DMA that last read these pinned buffers is done
+        if slot.gathered is not None:
+            self._copy_stream.wait_event(slot.gathered)           # device rasters no longer being gathered
+        parts = max(1, min(self.N_THREADS, n // (1 << 20)))       # split big rasters across the pool
+        holders = [_Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n)) for d in current_data]
+        futures = [[self._pool.submit(self._stage_part, slot, b, holders[b], n * k // parts, n * (k + 1) // parts)
+                    for k in range(parts)] for b in range(nb)]
         for b in range(nb):
             for f in futures[b]:
                 f.result()
             with torch.cuda.stream(self._copy_stream):
-                self.d_obs[b].copy_(self.h_obs[b], non_blocking=True)
-                self.d_inv[b].copy_(self.h_inv[b], non_blocking=True)
-                self.d_msk[b].copy_(self.h_msk[b], non_blocking=True)
-                self._events[b].record(self._copy_stream)
-            main.wait_event(self._events[b])
-            pix.gather_band(self.d_obs[b], self.d_inv[b], self.d_msk[b], out.y[b], out.w[b], out.m[b])
+                slot.d_obs[b].copy_(slot.h_obs[b], non_blocking=True)
+                slot.d_inv[b].copy_(slot.h_inv[b], non_blocking=True)
+                slot.d_msk[b].copy_(slot.h_msk[b], non_blocking=True)
+                slot.copied[b].record(self._copy_stream)
         self.h2d_bytes += nb * n * 17
+        return StagedDate(slot, nb)
+
+    def finish(self, token, out=None):
+        """Gather the staged rasters into compacted rows on the compute stream."""
+        pix = self.pix
+        nb = token.n_bands
+        out = out or BandBuffers(nb, pix, self.device)
+        if token.slot is None:
+            for b, d in enumerate(token.device_data):
+                m = d.mask.reshape(-1)
+                pix.gather_band(d.observations.reshape(-1), d.uncertainty.reshape(-1),
+                                m.view(torch.uint8) if m.dtype == torch.bool else m, out.y[b], out.w[b], out.m[b])
+            return out
+        slot = token.slot
+        main = torch.cuda.current_stream(self.device)
+        for b in range(nb):
+            main.wait_event(slot.copied[b])
+            pix.gather_band(slot.d_obs[b], slot.d_inv[b], slot.d_msk[b], out.y[b], out.w[b], out.m[b])
+        slot.gathered = torch.cuda.Event()
+        slot.gathered.record(main)
         return out
+
+    def upload(self, current_data, out=None):
+        return self.finish(self.stage(current_data), out)
 
 
 class _Staged(object):

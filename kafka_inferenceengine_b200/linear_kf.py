@@ -40,7 +40,7 @@ class LinearKalman(object):
                  state_propagation=propagate_information_filter_LAI,
                  band_mapper=None,
                  linear=True, diagnostics=True, prior=None, *, device=None, comm=None,
-                 round_operator_f32=True, dedup_uniform_state=True):
+                 round_operator_f32=True, dedup_uniform_state=True, prefetch_observations=True):
         _lib.get_lib()                                   # fail now if the CUDA library is missing
         if not isinstance(create_observation_operator, ObservationOperator):
             raise NotImplementedError(
@@ -68,6 +68,11 @@ class LinearKalman(object):
         self.comm = comm
         self.round_operator_f32 = bool(round_operator_f32)
         self.dedup_uniform_state = bool(dedup_uniform_state)
+        # stage the NEXT observation date (observations.get_band_data + host->device copy)
+        # while the kernels of the current date run; calls get_band_data one date early
+        self.prefetch_observations = bool(prefetch_observations)
+        self._schedule = []                  # observation dates still to come in run()
+        self._staged = {}                    # date -> (token, current_data)
         self.want_forward_modelled = False
         self._stager = engine.ObservationStager(self.pixels)
         self._ws = {}
@@ -125,7 +130,10 @@ class LinearKalman(object):
         one time step to the next."""
         x_forecast = self._state(x_forecast)
         P_forecast_inverse = self._precision(P_forecast_inverse)
-        for timestep, locate_times, is_first in iterate_time_grid(time_grid, self.observations.dates):
+        plan = list(iterate_time_grid(time_grid, self.observations.dates))
+        self._schedule = [d for _, locs, _ in plan for d in locs]
+        self._staged = {}
+        for timestep, locate_times, is_first in plan:
             self.current_timestep = timestep
             if not is_first:
                 LOG.info("Advancing state, %s" % timestep.strftime("%Y-%m-%d"))
@@ -145,6 +153,8 @@ class LinearKalman(object):
             LOG.info("Dumping results to disk")
             self.output.dump_data(timestep, x_analysis, P_analysis,
                                   P_analysis_inverse, self.state_mask, self.n_params)
+        if hasattr(self.output, "flush"):
+            self.output.flush()
 
     def assimilate_multiple_bands(self, locate_times, x_forecast, P_forecast,
                                   P_forecast_inverse,
@@ -154,8 +164,13 @@ class LinearKalman(object):
         one grid interval, all bands of a date at once."""
         for step in locate_times:
             LOG.info("Assimilating %s..." % step.strftime("%Y-%m-%d"))
-            current_data = [self.observations.get_band_data(step, band)
-                            for band in range(self.observations.bands_per_observation[step])]
+            if self._schedule and self._schedule[0] == step:
+                self._schedule.pop(0)
+            staged = self._staged.pop(step, None)
+            if staged is not None:
+                self._token, current_data = staged
+            else:
+                current_data = self._read_bands(step)
             x_analysis, P_analysis, P_analysis_inverse, innovations = \
                 self.do_all_bands(step, current_data, x_forecast, P_forecast, P_forecast_inverse)
             # the reference copies (x*1., linear_kf.py:232-240); device results are
@@ -166,6 +181,21 @@ class LinearKalman(object):
         return x_analysis, P_analysis, P_analysis_inverse
 
     # ------------------------------------------------------------------
+    def _read_bands(self, step):
+        return [self.observations.get_band_data(step, band)
+                for band in range(self.observations.bands_per_observation[step])]
+
+    def _prefetch_next(self):
+        """Read and start uploading the next observation date of run() while the
+        GPU is busy with the current one."""
+        if not (self.prefetch_observations and self._schedule):
+            return
+        nxt = self._schedule[0]
+        if nxt in self._staged:
+            return
+        data = self._read_bands(nxt)
+        self._staged[nxt] = (self._stager.stage(data), data)
+
     def _state(self, x):
         x = DeviceVector.from_interleaved(x, self.n_params, self.device)
         if x.n_pix != self.n_state_elems:
@@ -250,7 +280,9 @@ class LinearKalman(object):
         P_forecast_inverse = self._precision(P_forecast_inverse)
         n_bands = len(current_data)
         ws = self._workspace(n_bands)
-        bufs = self._stager.upload(current_data)
+        token = getattr(self, "_token", None)
+        self._token = None
+        bufs = self._stager.finish(token if token is not None else self._stager.stage(current_data))
         groups, descs = self._band_plan(current_data)
         all_linear = not groups
         n, P = self.n_state_elems, self.n_params
@@ -297,6 +329,9 @@ class LinearKalman(object):
                 engine.solve_bands(ws, descs, bufs, x_prev, x_forecast, P_forecast_inverse, x_new, a_out,
                                    want_fwd=self.want_forward_modelled)
                 self._tock(ev)
+                if shared is None or n_iter >= 2:
+                    # a full emulator pass is now queued: use the wait to stage the next date
+                    self._prefetch_next()
                 convergence_norm, count = self._global_norm(ws)   # linear_kf.py:293
                 x_analysis = x_new
                 x_analysis._uniform = False      # a solved state: skip the shared-vector test next iteration

@@ -175,17 +175,23 @@ class MemoryOutput(object):
 
 class BroadcastPrior(object):
     """``SAILPrior``-style prior (kafka_test_S2.py:77-118): one mean vector and
-    one inverse covariance block repeated for every state pixel."""
+    one inverse covariance block repeated for every state pixel.
+    ``make_block_diag(block, n)`` builds the matrix; ``make_vector(mean, n)``
+    (optional) the mean vector -- by default a host ``np.tile`` like the
+    reference; both results are cached, the prior does not depend on the date."""
 
-    def __init__(self, mean, inv_cov_block, n_pixels, make_block_diag):
+    def __init__(self, mean, inv_cov_block, n_pixels, make_block_diag, make_vector=None):
         self.mean = np.asarray(mean, dtype=np.float64)
         self.inv_cov = np.asarray(inv_cov_block, dtype=np.float64)
         self.n_pixels = int(n_pixels)
         self._make = make_block_diag
+        self._make_vector = make_vector or (lambda m, n: np.tile(m, n))
+        self._cache = None
 
     def process_prior(self, time, inv_cov=True):
-        x0 = np.tile(self.mean, self.n_pixels)
-        return x0, self._make(self.inv_cov, self.n_pixels)
+        if self._cache is None:
+            self._cache = (self._make_vector(self.mean, self.n_pixels), self._make(self.inv_cov, self.n_pixels))
+        return self._cache
 
 
 def day_grid(start, n, step=1):

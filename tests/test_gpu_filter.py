@@ -302,6 +302,8 @@ def test_raster_output_stage_matches_reference_arithmetic():
     got = {}
     out = RasterOutput(syn.S2_PARAMETERS, sink=lambda t, names, mean, unc: got.update(mean=mean.copy(), unc=unc.copy()))
     out.dump_data(dt.datetime(2017, 7, 3), x, None, kc.blocks_to_sparse(blocks), mask, P)
+    assert not got                                   # overlapped: delivered at the next dump_data / flush
+    out.flush()
     diag = blocks[:, np.arange(P), np.arange(P)].ravel()
     for ii in range(P):
         assert np.array_equal(got["mean"][ii], kc.scatter_param(x, ii, P, mask))
@@ -310,4 +312,43 @@ def test_raster_output_stage_matches_reference_arithmetic():
     # and with the device objects LinearKalman hands over
     out.dump_data(dt.datetime(2017, 7, 4), DeviceVector.from_interleaved(x, P, gu.DEV), None,
                   BlockDiag.from_blocks(blocks, gu.DEV), mask, P)
+    out.flush()
     assert np.array_equal(out.last[1], got["mean"])
+    sync = RasterOutput(syn.S2_PARAMETERS, overlap=False)
+    sync.dump_data(dt.datetime(2017, 7, 4), x, None, kc.blocks_to_sparse(blocks), mask, P)
+    assert np.array_equal(sync.last[1], got["mean"]) and np.array_equal(sync.last[2], got["unc"])
+
+
+def test_run_with_prefetch_and_overlapped_output_matches_plain_run():
+    """run() stages the next observation date while the current one is being
+    solved and RasterOutput reads results back on a side stream: same rasters as
+    the plain path, for a multi-date run with two dates in one grid interval."""
+    from kafka_inferenceengine_b200.output import RasterOutput
+    g = gio.load("run_s2")
+    mask = g["mask"]
+    P = 10
+    N = int(mask.sum())
+    gps = gio.emulators(g, syn.EmulatorData)
+    obs = gio.FixtureObservations(g, gps)
+    res = {}
+    for mode in (True, False):
+        prior = syn.BroadcastPrior(g["x0"][:P], g["prior_inv_block"].astype(np.float64), N,
+                                   lambda blk, n: BlockDiag.from_block(blk, n, gu.DEV),
+                                   (lambda m, n: DeviceVector.broadcast(m, n, gu.DEV)) if mode else None)
+        got = []
+        out = RasterOutput(syn.S2_PARAMETERS, overlap=mode,
+                           sink=lambda t, names, mean, unc: got.append((t, mean.copy(), unc.copy())))
+        kf = kb.LinearKalman(obs, out, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS,
+                             state_propagation=None, prior=prior, linear=False, prefetch_observations=mode)
+        kf.set_trajectory_model()
+        kf.set_trajectory_uncertainty(np.zeros(N * P))
+        x0, Pinv0 = prior.process_prior(None)
+        kf.run(gio.grid(g), x0, None, Pinv0, iter_obs_op=True)
+        res[mode] = (got, list(kf.last_iterations))
+    assert res[True][1] == res[False][1] == _iters_per_date(g["iter_log"])
+    assert len(res[True][0]) == len(res[False][0]) == len(g["out_steps"])
+    for (t1, m1, u1), (t2, m2, u2) in zip(res[True][0], res[False][0]):
+        assert t1 == t2 and np.array_equal(m1, m2) and np.array_equal(u1, u2)
+    # and equal to the reference-checked interleaved output
+    last_x = res[True][0][-1][1]
+    assert np.allclose(last_x[6][mask], g["out_x"][-1][6::P], rtol=2e-3, atol=1e-5)
