@@ -71,33 +71,37 @@ constexpr double kFarShift = 600.0 * kL;                 // beyond this the per-
 constexpr uint32_t kHiUnder = 0x40efeb6cu;               // high word of 708 L
 constexpr uint32_t kHiOver = 0x40eff6f7u;                // high word of 709 L
 
-// exp(a / L).  fp64-pipe cost: 3 adds + 5 FMAs + 1 mul; every range test is an integer
-// compare/select on the high word, so the function is branch-free and the compiler can
-// interleave several evaluations.  |rel err| < 3e-16 for -708 L <= a < 709 L; exactly 0
-// below, +inf above, NaN for NaN.
+// Polynomial coefficients live in constant memory so that the DFMAs take them as
+// c[bank][offset] operands instead of re-materialising 64-bit immediates in the loop.
+__constant__ double c_exp_poly[6] = {1.24178437017169252822e-12, 5.73285168864040188714e-10,
+                                      2.11731371554647762752e-07, 5.86490495505616996649e-05,
+                                      1.08304246962491450973e-02, 6755399441055744.0 /* 1.5 * 2^52 */};
+
+// exp(a / L) for finite a < 709 L.  fp64-pipe cost: 3 adds + 5 FMAs + 1 mul; the only range
+// test is one unsigned compare on the high word (exactly 0 below -708 L), so the function is
+// branch-free and several evaluations interleave.  |rel err| < 3e-16.  NaN / +inf / overflow
+// are NOT handled here: callers check their inputs once per pixel, outside the hot loop.
 __device__ __forceinline__ double exp_scaled(double a, const double* __restrict__ tab64) {
-    const double kMagic = 6755399441055744.0;            // 1.5 * 2^52
-    const double t = a + kMagic;
+    const double t = a + c_exp_poly[5];
     const int k = __double2loint(t);
-    const double r = a - (t - kMagic);                   // exact, |r| <= 1/2
-    double p = fma(r, 1.24178437017169252822e-12, 5.73285168864040188714e-10);
-    p = fma(p, r, 2.11731371554647762752e-07);
-    p = fma(p, r, 5.86490495505616996649e-05);
-    p = fma(p, r, 1.08304246962491450973e-02);
+    const double r = a - (t - c_exp_poly[5]);            // exact, |r| <= 1/2
+    double p = fma(r, c_exp_poly[0], c_exp_poly[1]);
+    p = fma(p, r, c_exp_poly[2]);
+    p = fma(p, r, c_exp_poly[3]);
+    p = fma(p, r, c_exp_poly[4]);
     p = fma(p, r, 1.0);
     const double v = tab64[k & 63] * p;
-    int hi = __double2hiint(v) + ((k >> 6) << 20);
-    int lo = __double2loint(v);
-    const int ha = __double2hiint(a);
-    const uint32_t mag = (uint32_t)ha & 0x7fffffffu;
-    // (uint32)ha >= 0x80000000 + kHiUnder  <=>  a <= -708 L (or -inf / negative NaN)
-    const bool under = (uint32_t)ha >= (0x80000000u + kHiUnder);
-    const bool over = (uint32_t)(ha - (int)kHiOver) < (0x7ff00001u - kHiOver);   // 709 L <= a <= +inf
-    const bool nan = (mag + (uint32_t)(__double2loint(a) != 0)) > 0x7ff00000u;
-    hi = under ? 0 : hi;
-    hi = over ? 0x7ff00000 : hi;
-    hi = nan ? 0x7ff80000 : hi;
-    lo = (mag >= kHiUnder) ? 0 : lo;
+    // (uint32)hi(a) >= 0x80000000 + hi(708 L)  <=>  a <= -708 L (or -inf)
+    const int hi_n = __double2hiint(v) + ((k >> 6) << 20);
+    const int lo_n = __double2loint(v);
+    int hi, lo;
+    // selp keeps this branch-free (the compiler otherwise jumps around the exponent insert)
+    asm("{\n\t.reg .pred p;\n\t"
+        "setp.ge.u32 p, %2, %3;\n\t"
+        "selp.b32 %0, 0, %4, p;\n\t"
+        "selp.b32 %1, 0, %5, p;\n\t}"
+        : "=r"(hi), "=r"(lo)
+        : "r"(__double2hiint(a)), "r"(0x80000000u + kHiUnder), "r"(hi_n), "r"(lo_n));
     return __hiloint2double(hi, lo);
 }
 
@@ -116,6 +120,7 @@ struct GpLinParams {
     int64_t ld;
     int64_t n_pix;
     uint32_t flags;
+    int32_t n_bands;
 };
 
 // tuning knobs (defaults are the measured best; benchmarks/gp_variants.py sweeps them)
@@ -166,14 +171,18 @@ __device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, i
 }
 
 template <int D, int PPT>
-__global__ void __launch_bounds__(kGpThreads, KAFKA_GP_MINBLOCKS)
+__global__ void __launch_bounds__(kGpThreads, (KAFKA_GP_MINBLOCKS == 1 && PPT == 2 && D <= 10 && KAFKA_GP_THREADS == 128) ? 3 : KAFKA_GP_MINBLOCKS)
 gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     extern __shared__ __align__(16) double smem[];
     __shared__ uint64_t bar;
     __shared__ double s_exp[64];
 
-    const GpBandDev& band = prm.bands[blockIdx.y];
+    // band is the FAST grid index: the CTAs of all bands of one pixel tile run together, so
+    // the tile's state is fetched from HBM once and served to the other bands by L2
+    const int band_idx = (int)(blockIdx.x % prm.n_bands);
+    const int64_t tile_idx = blockIdx.x / prm.n_bands;
+    const GpBandDev& band = prm.bands[band_idx];
     const int T = band.n_train;
     const uint32_t bytes = (uint32_t)((HDR + T * RS) * sizeof(double));
 
@@ -189,7 +198,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     }
 
     // pixel states while the table is in flight
-    const int64_t tile0 = (int64_t)blockIdx.x * (kGpThreads * PPT);
+    const int64_t tile0 = tile_idx * (kGpThreads * PPT);
     int64_t pix[PPT];
     bool live[PPT];
     double xr[PPT][D];
@@ -198,7 +207,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     for (int pp = 0; pp < PPT; ++pp) {
         pix[pp] = tile0 + pp * kGpThreads + threadIdx.x;
         bool in = pix[pp] < prm.n_pix;
-        live[pp] = in && (prm.obs_mask == nullptr || prm.obs_mask[(int64_t)blockIdx.y * prm.ld + pix[pp]] != 0);
+        live[pp] = in && (prm.obs_mask == nullptr || prm.obs_mask[(int64_t)band_idx * prm.ld + pix[pp]] != 0);
         any_live |= live[pp];
 #pragma unroll
         for (int d = 0; d < D; ++d)
@@ -212,7 +221,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     const double* rows = smem + HDR;
 
     double sh[PPT], mu[PPT], G[PPT][D];
-    bool far = false;
+    bool far = false, bad[PPT];
 #pragma unroll
     for (int pp = 0; pp < PPT; ++pp) {
         double s = 0.0;
@@ -225,6 +234,9 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
         sh[pp] = (-0.5 * kL) * s;                          // scaled like the table
         mu[pp] = 0.0;
         far |= live[pp] && !(sh[pp] > -kFarShift);         // also true for NaN; padding lanes do not count
+        // a non-finite state (NaN / inf in any input) is caught here, once per pixel, and
+        // turned into NaN outputs below: exp_scaled itself assumes finite arguments
+        bad[pp] = !(fabs(s) <= 1.79769313486231570815e308);
     }
 
     if (__any_sync(0xffffffffu, any_live)) {
@@ -252,13 +264,18 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
 #pragma unroll
     for (int pp = 0; pp < PPT; ++pp) {
         if (pix[pp] >= prm.n_pix) continue;
+        if (bad[pp]) {
+            mu[pp] = CUDART_NAN;
+#pragma unroll
+            for (int d = 0; d < D; ++d) G[pp][d] = CUDART_NAN;
+        }
         double m = live[pp] ? mu[pp] : 0.0;
-        prm.h0[(int64_t)blockIdx.y * prm.ld + pix[pp]] = r32 ? round_f32(m) : m;
+        prm.h0[(int64_t)band_idx * prm.ld + pix[pp]] = r32 ? round_f32(m) : m;
         if (prm.jac) {
 #pragma unroll
             for (int d = 0; d < D; ++d) {
                 double g = live[pp] ? G[pp][d] - theta_e[d] * xr[pp][d] * mu[pp] : 0.0;
-                prm.jac[((int64_t)blockIdx.y * D + d) * prm.ld + pix[pp]] = r32 ? round_f32(g) : g;
+                prm.jac[((int64_t)band_idx * D + d) * prm.ld + pix[pp]] = r32 ? round_f32(g) : g;
             }
         }
     }
@@ -363,8 +380,12 @@ static int launch_linearize(const GpLinParams& prm, int n_bands, int max_T, cuda
     }
     auto kern = gp_linearize_kernel<D, PPT>;
     KAFKA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((unsigned)((prm.n_pix + kGpThreads * PPT - 1) / (kGpThreads * PPT)), (unsigned)n_bands);
-    kern<<<grid, kGpThreads, smem, s>>>(prm);
+    const int64_t tiles = (prm.n_pix + kGpThreads * PPT - 1) / (kGpThreads * PPT);
+    if (tiles * n_bands > 0x7fffffffLL) {
+        set_error("kafka_gp_linearize: %lld pixel tiles x %d bands exceed the grid limit", (long long)tiles, n_bands);
+        return KAFKA_E_TOOLARGE;
+    }
+    kern<<<(unsigned)(tiles * n_bands), kGpThreads, smem, s>>>(prm);
     return launch_status("gp_linearize_kernel");
 }
 
@@ -476,6 +497,7 @@ int kafka_gp_linearize(const double* x, int64_t ld, int64_t n_pix, const kafka_g
     prm.ld = ld;
     prm.n_pix = n_pix;
     prm.flags = flags;
+    prm.n_bands = n_bands;
     int rc = KAFKA_E_UNSUPPORTED;
     KAFKA_DISPATCH_D(D, rc = dispatch_ppt<kD>(prm, n_bands, max_T, (cudaStream_t)stream));
     return rc;
