@@ -453,7 +453,10 @@ def main():
     n_iter_mean = float(np.mean(iters))
     gp_bytes = n_pix * (8 * P + B * (1 + 8 + 8 * P))            # x once, mask, h0, Jacobian out
     gp_flops = n_pix * B * T * (5 * P + 28)
-    sv_bytes = n_pix * (BYTES_PER_PIXEL_DATE + 8 * B * P + 8 * B + 8 * P + 8 * B)   # + J, H0, x_prev in, innovations out
+    # solve launch with per-pixel operators (iteration >= 2): in x_prev, x_f (8P each), per band
+    # w, y, H0, J[P] (8(3+P)); out x (8P), A packed (4P(P+1)), innovations (8B).  The prior block is
+    # ONE block shared by all pixels in this workload (KAFKA_PRIOR_BROADCAST), so it is not counted.
+    sv_bytes = n_pix * (3 * 8 * P + B * 8 * (3 + P) + 4 * P * (P + 1) + 8 * B)
     gp_tf = gp_flops / (gp_ms * 1e-3) / 1e12
     roofline = {
         "kernel": "gp_linearize_kernel<10,2> (GP emulator mean+Jacobian, all bands, one launch per iteration)",

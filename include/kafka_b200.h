@@ -50,6 +50,17 @@ extern "C" {
                                 the reference's "one unique state vector" shortcut      \
                                 (kafka/inference/utils.py:72-74)                        */
 
+#define KAFKA_BAND_WCM 3     /* Water-Cloud SAR backscatter model, closed form:          \
+                                row[0..4] = A,B,C,D,E, row[5] = cos(incidence angle),    \
+                                mapper[0] = state slot of the vegetation descriptor      \
+                                (LAI), mapper[1] = slot of soil moisture                 \
+                                (kafka/observation_operators/sar_forward_model.py:13-113) */
+
+/* raw raster element types for kafka_gather_scaled_band */
+#define KAFKA_RAW_I16 0
+#define KAFKA_RAW_U16 1
+#define KAFKA_RAW_F32 2
+
 /* flags */
 #define KAFKA_ROUND_F32 1u      /* round H0/J to float32 as the reference stores them \
                                    (kafka/inference/utils.py:193-195)                  */
@@ -76,6 +87,19 @@ int kafka_compact_mask(const uint8_t* mask, int64_t n_raster, int32_t* idx, int6
 int kafka_gather_band(const double* obs, const double* inv_var, const uint8_t* obs_mask,
                       const int32_t* idx, int64_t n_pix, double* y, double* w, uint8_t* m_out,
                       void* stream);
+
+/* Observation ingest fused with the gather, replacing the arithmetic of
+ * Sentinel2Observations.get_band_data
+ * (kafka/input_output/Sentinel2_Observations.py:166-179): from the RAW surface
+ * reflectance raster (scaled integers) to compacted rows
+ *   m = raw[idx] > 0 (and ext_mask[idx] != 0 when ext_mask is given)
+ *   y = m ? raw[idx] / divisor      : 0        (divisor = 10000)
+ *   w = m ? 1 / (rel_sigma * y)^2   : 0        (rel_sigma = 0.05)
+ * Only the raw raster (2 or 4 bytes per pixel) has to cross PCIe instead of the
+ * 17 bytes of (float64 reflectance, float64 inverse variance, mask). */
+int kafka_gather_scaled_band(const void* raw, int raw_type, const uint8_t* ext_mask, const int32_t* idx,
+                             int64_t n_pix, double divisor, double rel_sigma, double* y, double* w,
+                             uint8_t* m_out, void* stream);
 
 /* Output stage, replaces KafkaOutput.dump_data's scatter
  * (kafka/input_output/observations.py:374-375,392-393): for parameter p writes
@@ -145,6 +169,19 @@ int kafka_gp_predict(const double* xin, int64_t ld, int64_t n_pts, const double*
                      int n_train, int n_dim, const double* inv_q, double* mean, double* jac,
                      double* var, void* stream);
 
+/* Second-order ("Hessian") correction of the posterior precision, replacing
+ * hessian_correction / hessian_correction_multiband
+ * (kafka/inference/kf_tools.py:26-72):
+ *     corr_i = sum_b  m_bi * w_bi * innovation_bi * E_b^T (d2 h_b / dx2)(x_i) E_b
+ * with E_b the embedding of band b's emulator inputs into the state (its
+ * mapper; the reference hard-codes the TIP selector, kf_tools.py:19-23).
+ * Writes corr (packed, may be NULL) and/or subtracts it from a_inout (packed,
+ * may be NULL): P_analysis_inverse - P_correction (kafka/linear_kf.py:416).
+ * w must be gated to 0 where unobserved. */
+int kafka_gp_hessian_correction(const double* x, int64_t ld, int64_t n_pix, int n_params,
+                                const kafka_gp_band* bands_host, int n_bands, const double* innovations,
+                                const double* w, double* corr, double* a_inout, void* stream);
+
 /* gp.hessian (kafka/inference/kf_tools.py:28): hess[(d*D+e)*ld + i]. */
 int kafka_gp_hessian(const double* xin, int64_t ld, int64_t n_pts, const double* table,
                      int n_train, int n_dim, double* hess, void* stream);
@@ -154,7 +191,7 @@ typedef struct {
     int32_t kind;                      /* KAFKA_BAND_ARRAYS / _LINEAR / _UNIFORM             */
     int32_t n_dim;                     /* ARRAYS, UNIFORM: Jacobian planes of this band      */
     int32_t mapper[KAFKA_MAX_DIM];     /* ARRAYS, UNIFORM: state slot of Jacobian plane d    */
-    double row[KAFKA_MAX_PARAMS];      /* LINEAR: operator row                               */
+    double row[KAFKA_MAX_PARAMS];      /* LINEAR: operator row; WCM: A,B,C,D,E,cos(theta)    */
     double offset;                     /* LINEAR: H0 = row.x_prev + offset                   */
     const double* h0;                  /* ARRAYS: [ld] device; UNIFORM: 1 value              */
     const double* jac;                 /* ARRAYS: [n_dim][ld] device; UNIFORM: [n_dim]       */
@@ -176,7 +213,8 @@ int64_t kafka_solve_scratch_doubles(int64_t n_pix);
  * (solvers.py:142), fwd[b*ld+i] = J_b.(x - x_f) + H0_b (solvers.py:137),
  * n_bad = number of pixels whose block was not positive definite (their x is
  * left at x_f).  `scratch` holds kafka_solve_scratch_doubles(n_pix) doubles.
- * flags: KAFKA_PRIOR_BROADCAST. */
+ * flags: KAFKA_PRIOR_BROADCAST; KAFKA_ROUND_F32 (applies to WCM bands, whose
+ * operator the reference also stores in float32). */
 int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve_band* bands_host,
                       int n_bands, const double* x_prev, const double* x_f, const double* pinv_f,
                       double* x_out, double* a_out, double* innovations, double* fwd,
@@ -209,6 +247,15 @@ int kafka_solve_bands_static(int64_t n_pix, int64_t ld, int n_params, const kafk
                              int n_bands, const double* x_prev, const double* x_f, const double* pinv_f,
                              double* x_out, double* a_out, double* innovations, double* fwd,
                              double* norm2, int32_t* n_bad, uint32_t flags, void* stream);
+
+/* Water-Cloud SAR forward model and gradient, replacing sar_observation_operator
+ * (kafka/observation_operators/sar_forward_model.py:13-113) for inspection and
+ * tests: x[0*ld+i] = vegetation descriptor (LAI), x[1*ld+i] = soil moisture;
+ * params_host = {A, B, C, D, E, cos(incidence angle)}; sigma0[i] (linear units),
+ * grad[0*ld+i], grad[1*ld+i] (may be NULL).  Inside the filter the same maths runs
+ * fused in kafka_solve_bands (band kind KAFKA_BAND_WCM). */
+int kafka_wcm_forward(const double* x, int64_t ld, int64_t n, const double* params_host, double* sigma0,
+                      double* grad, void* stream);
 
 /* ---- a12-a17: advance / propagation ----------------------------------------
  * propagate_information_filter_LAI (kafka/inference/kf_tools.py:292-314),

@@ -17,6 +17,8 @@ MAX_DIM = 16
 BAND_ARRAYS = 0
 BAND_LINEAR = 1
 BAND_UNIFORM = 2
+BAND_WCM = 3
+RAW_I16, RAW_U16, RAW_F32 = 0, 1, 2
 ROUND_F32 = 1
 PRIOR_BROADCAST = 2
 STATIC_SCRATCH_DOUBLES = 262144
@@ -47,6 +49,7 @@ SIGNATURES = {
     "kafka_compact_scratch_elems": (_i64, [_i64]),
     "kafka_compact_mask": (C.c_int, [_p, _i64, _p, _i64, _p, C.POINTER(C.c_int64), _p]),
     "kafka_gather_band": (C.c_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p]),
+    "kafka_gather_scaled_band": (C.c_int, [_p, _i32, _p, _p, _i64, C.c_double, C.c_double, _p, _p, _p, _p]),
     "kafka_scatter_output": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p, _p, _p]),
     "kafka_state_uniform": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
     "kafka_interleaved_to_planar": (C.c_int, [_p, _i64, _i32, _p, _i64, _p]),
@@ -58,12 +61,14 @@ SIGNATURES = {
     "kafka_gp_pack_host": (C.c_int, [_p, _p, _p, _i32, _i32, _p]),
     "kafka_gp_linearize": (C.c_int, [_p, _i64, _i64, C.POINTER(GpBand), _i32, _p, _p, _p, _u32, _p]),
     "kafka_gp_predict": (C.c_int, [_p, _i64, _i64, _p, _i32, _i32, _p, _p, _p, _p, _p]),
+    "kafka_gp_hessian_correction": (C.c_int, [_p, _i64, _i64, _i32, C.POINTER(GpBand), _i32, _p, _p, _p, _p, _p]),
     "kafka_gp_hessian": (C.c_int, [_p, _i64, _i64, _p, _i32, _i32, _p, _p]),
     "kafka_solve_scratch_doubles": (_i64, [_i64]),
     "kafka_solve_bands": (C.c_int, [_i64, _i64, _i32, C.POINTER(SolveBand), _i32, _p, _p, _p, _p, _p, _p, _p,
                                     _p, _p, _p, _u32, _p]),
     "kafka_solve_bands_static": (C.c_int, [_i64, _i64, _i32, C.POINTER(SolveBand), _i32, _p, _p, _p, _p, _p, _p, _p,
                                            _p, _p, _u32, _p]),
+    "kafka_wcm_forward": (C.c_int, [_p, _i64, _i64, _p, _p, _p, _p]),
     "kafka_advance_carry_slot": (C.c_int, [_p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _p, _p, _p]),
     "kafka_advance_approx": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p]),
     "kafka_advance_exact": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p, _p]),

@@ -335,6 +335,97 @@ gp_hessian_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, con
         }
 }
 
+// ---- second-order correction of the posterior precision (kf_tools.py:26-72) ----------
+// One thread per pixel, bands in sequence: the D(D+1)/2 Hessian sums of a band are
+// accumulated in registers, scaled by w * innovation and added into the packed P x P
+// correction block in global memory (coalesced read-modify-write, one plane at a time).
+struct GpHessCorrParams {
+    GpBandDev bands[KAFKA_MAX_BANDS];
+    const double* x;
+    const double* innovations;
+    const double* w;
+    double* corr;
+    double* a_inout;
+    int64_t ld;
+    int64_t n_pix;
+    int32_t n_bands;
+    int32_t n_params;
+};
+
+template <int D>
+__global__ void __launch_bounds__(128)
+gp_hessian_correction_kernel(const __grid_constant__ GpHessCorrParams prm) {
+    constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D), L = tri_count(D);
+    extern __shared__ __align__(16) double smem[];
+    __shared__ double s_exp[64];
+    if (threadIdx.x < 64) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
+    const bool in = i < prm.n_pix;
+    const int LP = tri_count(prm.n_params);
+    // the output block starts from zero (or from a_inout when correcting in place)
+    double* out = prm.corr ? prm.corr : prm.a_inout;
+    const double sign = prm.corr ? 1.0 : -1.0;
+    if (in && prm.corr)
+        for (int c = 0; c < LP; ++c) prm.corr[(int64_t)c * prm.ld + i] = 0.0;
+    for (int b = 0; b < prm.n_bands; ++b) {
+        const GpBandDev& band = prm.bands[b];
+        const int T = band.n_train;
+        __syncthreads();                                   // previous band's table no longer in use
+        for (int k = threadIdx.x; k < HDR + T * RS; k += 128) smem[k] = band.table[k];
+        __syncthreads();
+        if (!in) continue;
+        const double c = prm.w[(int64_t)b * prm.ld + i] * prm.innovations[(int64_t)b * prm.ld + i];
+        if (c == 0.0) continue;                            // masked pixel: zero block (kf_tools.py:49-51)
+        const double* theta_e = smem;
+        const double* centre = smem + DP;
+        const double* rows = smem + HDR;
+        double xr[D], tx[D], acc[L], mu = 0.0, s = 0.0;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            xr[d] = prm.x[(int64_t)band.mapper[d] * prm.ld + i] - centre[d];
+            tx[d] = theta_e[d] * xr[d];
+            s = fma(tx[d], xr[d], s);
+        }
+#pragma unroll
+        for (int k = 0; k < L; ++k) acc[k] = 0.0;
+        const double sh = (-0.5 * kL) * s;
+        for (int j = 0; j < T; ++j) {
+            const double* row = rows + j * RS;
+            double a = row[DP] + sh, u[D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                a = fma(row[d], xr[d], a);
+                u[d] = fma(row[d], kInvL, -tx[d]);
+            }
+            const double wj = exp_scaled(a, s_exp) * row[DP + 1];
+            mu += wj;
+#pragma unroll
+            for (int r = 0; r < D; ++r) {
+                const double wu = wj * u[r];
+#pragma unroll
+                for (int q = 0; q <= r; ++q) acc[tri(r, q)] = fma(wu, u[q], acc[tri(r, q)]);
+            }
+        }
+        const double cs = c * sign;
+#pragma unroll
+        for (int r = 0; r < D; ++r)
+#pragma unroll
+            for (int q = 0; q <= r; ++q) {
+                const double h = acc[tri(r, q)] - (r == q ? theta_e[r] * mu : 0.0);
+                const int sr = band.mapper[r], sq = band.mapper[q];
+                const int cidx = sr >= sq ? tri(sr, sq) : tri(sq, sr);
+                // two emulator inputs mapped to one state slot would hit the same entry twice
+                // per thread; the host rejects such mappers, so this is a plain RMW
+                double* dst = out + (int64_t)cidx * prm.ld + i;
+                *dst = fma(cs, h, *dst);
+            }
+    }
+    // producing corr AND correcting a_inout: second pass a -= corr
+    if (in && prm.corr && prm.a_inout)
+        for (int c = 0; c < LP; ++c)
+            prm.a_inout[(int64_t)c * prm.ld + i] -= prm.corr[(int64_t)c * prm.ld + i];
+}
+
 // ---- predictive variance: s_f - k^T Q^-1 k, one warp per point ---------------------
 __global__ void __launch_bounds__(128)
 gp_variance_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, const double* __restrict__ table, int T,
@@ -521,6 +612,65 @@ int kafka_gp_predict(const double* xin, int64_t ld, int64_t n_pts, const double*
     gp_variance_kernel<<<(unsigned)((n_pts + 3) / 4), 128, smem, (cudaStream_t)stream>>>(xin, ld, n_pts, table, n_train,
                                                                                        n_dim, inv_q, var);
     return launch_status("gp_variance_kernel");
+}
+
+int kafka_gp_hessian_correction(const double* x, int64_t ld, int64_t n_pix, int n_params,
+                                const kafka_gp_band* bands, int n_bands, const double* innovations,
+                                const double* w, double* corr, double* a_inout, void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "kafka_gp_hessian_correction: need 0 <= n_pix <= ld");
+    KAFKA_CHECK_ARG(n_params >= 1 && n_params <= KAFKA_MAX_PARAMS, "kafka_gp_hessian_correction: n_params=%d", n_params);
+    KAFKA_CHECK_ARG(n_bands >= 1 && n_bands <= KAFKA_MAX_BANDS && bands, "kafka_gp_hessian_correction: n_bands=%d", n_bands);
+    KAFKA_CHECK_ARG(corr || a_inout, "kafka_gp_hessian_correction: no output given");
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(x && innovations && w, "kafka_gp_hessian_correction: null pointer");
+    GpHessCorrParams prm;
+    memset(&prm, 0, sizeof(prm));
+    const int D = bands[0].n_dim;
+    KAFKA_CHECK_ARG(D >= 1 && D <= KAFKA_MAX_DIM, "kafka_gp_hessian_correction: n_dim=%d", D);
+    int max_T = 0;
+    for (int b = 0; b < n_bands; ++b) {
+        KAFKA_CHECK_ARG(bands[b].n_dim == D, "kafka_gp_hessian_correction: all bands of one call must share n_dim");
+        KAFKA_CHECK_ARG(bands[b].table && bands[b].n_train >= 1, "kafka_gp_hessian_correction: band %d has no table", b);
+        prm.bands[b].table = bands[b].table;
+        prm.bands[b].n_train = bands[b].n_train;
+        uint32_t seen = 0;
+        for (int d = 0; d < D; ++d) {
+            int slot = bands[b].mapper[d];
+            KAFKA_CHECK_ARG(slot >= 0 && slot < n_params && !(seen & (1u << slot)),
+                            "kafka_gp_hessian_correction: band %d maps input %d to slot %d", b, d, slot);
+            seen |= 1u << slot;
+            prm.bands[b].mapper[d] = slot;
+        }
+        max_T = bands[b].n_train > max_T ? bands[b].n_train : max_T;
+    }
+    prm.x = x;
+    prm.innovations = innovations;
+    prm.w = w;
+    prm.corr = corr;
+    prm.a_inout = a_inout;
+    prm.ld = ld;
+    prm.n_pix = n_pix;
+    prm.n_bands = n_bands;
+    prm.n_params = n_params;
+    size_t smem = (size_t)(tab_hdr(D) + max_T * tab_row(D)) * sizeof(double);
+    if (smem > 200 * 1024) {
+        set_error("kafka_gp_hessian_correction: training table of %zu bytes does not fit shared memory", smem);
+        return KAFKA_E_TOOLARGE;
+    }
+    int rc = KAFKA_E_UNSUPPORTED;
+    unsigned grid = (unsigned)((n_pix + 127) / 128);
+    KAFKA_DISPATCH_D(D, {
+        auto kern = gp_hessian_correction_kernel<kD>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) {
+            set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+            rc = (int)e;
+        } else {
+            kern<<<grid, 128, smem, (cudaStream_t)stream>>>(prm);
+            rc = launch_status("gp_hessian_correction_kernel");
+        }
+    });
+    return rc;
 }
 
 int kafka_gp_hessian(const double* xin, int64_t ld, int64_t n_pts, const double* table, int n_train, int n_dim,

@@ -124,6 +124,24 @@ __global__ void gather_band_kernel(const double* __restrict__ obs, const double*
     if (m_out) m_out[i] = m ? 1 : 0;
 }
 
+template <typename RawT>
+__global__ void gather_scaled_band_kernel(const RawT* __restrict__ raw, const uint8_t* __restrict__ ext_mask,
+                                          const int32_t* __restrict__ idx, int64_t n_pix, double divisor,
+                                          double rel_sigma, double* __restrict__ y, double* __restrict__ w,
+                                          uint8_t* __restrict__ m_out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pix) return;
+    int32_t j = idx[i];
+    const RawT r = raw[j];
+    bool m = r > (RawT)0;                                        // mask = rho_surface > 0   (:168)
+    if (ext_mask) m = m && ext_mask[j] != 0;
+    const double rho = m ? (double)r / divisor : 0.0;            // rho_surface / 10000.     (:169)
+    const double sig = rho * rel_sigma;                          // R_mat = rho_surface*0.05 (:174)
+    y[i] = rho;
+    w[i] = m ? 1.0 / (sig * sig) : 0.0;                          // 1./(R_mat)**2, gated     (:175-178)
+    if (m_out) m_out[i] = m ? 1 : 0;
+}
+
 __global__ void scatter_output_kernel(const double* __restrict__ x, const double* __restrict__ a,
                                       int64_t ld, int64_t n_pix, int n_params,
                                       const int32_t* __restrict__ idx, int64_t n_raster,
@@ -264,6 +282,33 @@ int kafka_gather_band(const double* obs, const double* inv_var, const uint8_t* o
     gather_band_kernel<<<(unsigned)((n_pix + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
         obs, inv_var, obs_mask, idx, n_pix, y, w, m_out);
     return launch_status("gather_band");
+}
+
+int kafka_gather_scaled_band(const void* raw, int raw_type, const uint8_t* ext_mask, const int32_t* idx,
+                             int64_t n_pix, double divisor, double rel_sigma, double* y, double* w,
+                             uint8_t* m_out, void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0, "kafka_gather_scaled_band: n_pix < 0");
+    KAFKA_CHECK_ARG(divisor > 0.0 && rel_sigma > 0.0, "kafka_gather_scaled_band: divisor and rel_sigma must be > 0");
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(raw && idx && y && w, "kafka_gather_scaled_band: null pointer");
+    const int threads = 256;
+    const unsigned grid = (unsigned)((n_pix + threads - 1) / threads);
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (raw_type) {
+        case KAFKA_RAW_I16:
+            gather_scaled_band_kernel<int16_t><<<grid, threads, 0, s>>>((const int16_t*)raw, ext_mask, idx, n_pix, divisor, rel_sigma, y, w, m_out);
+            break;
+        case KAFKA_RAW_U16:
+            gather_scaled_band_kernel<uint16_t><<<grid, threads, 0, s>>>((const uint16_t*)raw, ext_mask, idx, n_pix, divisor, rel_sigma, y, w, m_out);
+            break;
+        case KAFKA_RAW_F32:
+            gather_scaled_band_kernel<float><<<grid, threads, 0, s>>>((const float*)raw, ext_mask, idx, n_pix, divisor, rel_sigma, y, w, m_out);
+            break;
+        default:
+            set_error("kafka_gather_scaled_band: unknown raw_type %d", raw_type);
+            return KAFKA_E_BADARG;
+    }
+    return launch_status("gather_scaled_band_kernel");
 }
 
 int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, int64_t n_pix,

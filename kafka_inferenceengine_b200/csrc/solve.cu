@@ -40,9 +40,41 @@ struct SolveParams {
 
 constexpr int kSolveThreads = 128;
 
+// Water-Cloud model and its gradient (sar_forward_model.py:74-98); prm = A,B,C,D,E,cos(theta)
+__device__ __forceinline__ void wcm_eval(const double* __restrict__ prm, double V, double SM, double& s0, double& g0,
+                                         double& g1) {
+    const double A = prm[0], Bc = prm[1], C = prm[2], Dc = prm[3], E = prm[4], mu = prm[5];
+    const double tau = exp(-2.0 * Bc / mu * V);
+    double z = pow(V, E), z1 = pow(V, E - 1.0);
+    z = (z != z) ? 1.0 : z;                                 // the reference's NaN guards (:87-92)
+    z1 = (z1 != z1) ? 1.0 : z1;
+    const double surf = exp10((C + Dc * SM) / 10.0);
+    s0 = A * z * mu * (1.0 - tau) + tau * surf;
+    g0 = A * E * mu * z1 * (1.0 - tau) + 2.0 * A * Bc * z * tau - 2.0 * surf * Bc * tau / mu;
+    g1 = Dc * 2.302585092994045684 * tau * surf * 0.1;
+}
+
+struct WcmParams {
+    double prm[6];
+};
+
+__global__ void __launch_bounds__(256)
+wcm_forward_kernel(const double* __restrict__ x, int64_t ld, int64_t n, const __grid_constant__ WcmParams wp,
+                   double* __restrict__ sigma0, double* __restrict__ grad) {
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    double s0, g0, g1;
+    wcm_eval(wp.prm, x[i], x[ld + i], s0, g0, g1);
+    sigma0[i] = s0;
+    if (grad) {
+        grad[i] = g0;
+        grad[ld + i] = g1;
+    }
+}
+
 template <int P>
 __device__ __forceinline__ void band_row(const SolveBandDev& bd, int64_t ld, int64_t i, const double (&xp)[P],
-                                         double w, double (&J)[P], double& h0) {
+                                         double w, double (&J)[P], double& h0, bool round32, bool& domain_bad) {
     if (bd.kind == KAFKA_BAND_LINEAR) {
         double s = bd.offset;
 #pragma unroll
@@ -51,6 +83,26 @@ __device__ __forceinline__ void band_row(const SolveBandDev& bd, int64_t ld, int
             s = fma(bd.row[p], xp[p], s);
         }
         h0 = w != 0.0 ? s : 0.0;
+    } else if (bd.kind == KAFKA_BAND_WCM) {
+        // Water-Cloud model (sar_forward_model.py:74-98): V = vegetation descriptor, SM = soil moisture
+        double V = 0.0, SM = 0.0;
+#pragma unroll
+        for (int p = 0; p < P; ++p) {                       // static indexing keeps xp in registers
+            V = bd.src[p] == 0 ? xp[p] : V;
+            SM = bd.src[p] == 1 ? xp[p] : SM;
+        }
+        double s0, g0, g1;
+        wcm_eval(bd.row, V, SM, s0, g0, g1);
+        if (round32) {
+            s0 = round_f32(s0);
+            g0 = round_f32(g0);
+            g1 = round_f32(g1);
+        }
+        const bool on = w != 0.0;
+#pragma unroll
+        for (int p = 0; p < P; ++p) J[p] = !on ? 0.0 : (bd.src[p] == 0 ? g0 : (bd.src[p] == 1 ? g1 : 0.0));
+        h0 = on ? s0 : 0.0;
+        if (on && !(V > 0.0 && SM > 0.0)) domain_bad = true;  // "Negative LAI!" / "Negative SM!" (:66-71)
     } else if (bd.kind == KAFKA_BAND_UNIFORM) {
         // one linearisation point for the whole image: every thread reads the same
         // D+1 values (L1 broadcast); unobserved pixels keep an empty row (utils.py:199-215)
@@ -76,6 +128,8 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm) {
     if (i < prm.n_pix) {
         double A[L], rhs[P], xp[P], xf[P];
         const bool bcast = (prm.flags & KAFKA_PRIOR_BROADCAST) != 0;
+        const bool round32 = (prm.flags & KAFKA_ROUND_F32) != 0;
+        bool domain_bad = false;
 #pragma unroll
         for (int c = 0; c < L; ++c) A[c] = bcast ? prm.pinv_f[c] : ldg_stream(prm.pinv_f + (int64_t)c * ld + i);
 #pragma unroll
@@ -85,12 +139,13 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm) {
         }
         symv<P>(A, xf, rhs);
 
+#pragma unroll 2
         for (int b = 0; b < prm.n_bands; ++b) {
             const SolveBandDev& bd = prm.bands[b];
             const double w = ldg_stream(bd.w + i);
             const double y = ldg_stream(bd.y + i);
             double J[P], h0;
-            band_row<P>(bd, ld, i, xp, w, J, h0);
+            band_row<P>(bd, ld, i, xp, w, J, h0, round32, domain_bad);
             double yp = y - h0;                                   // y' = y + J.x_prev - H0
 #pragma unroll
             for (int p = 0; p < P; ++p) yp = fma(J[p], xp[p], yp);
@@ -109,7 +164,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm) {
         for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A[c]);
 
         double invd[P];
-        const bool ok = chol_factor<P>(A, invd);
+        const bool ok = chol_factor<P>(A, invd) && !domain_bad;
         chol_solve<P>(A, invd, rhs);
 #pragma unroll
         for (int p = 0; p < P; ++p) {
@@ -125,7 +180,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm) {
             for (int b = 0; b < prm.n_bands; ++b) {
                 const SolveBandDev& bd = prm.bands[b];
                 double J[P], h0;
-                band_row<P>(bd, ld, i, xp, bd.w[i], J, h0);
+                band_row<P>(bd, ld, i, xp, bd.w[i], J, h0, round32, domain_bad);
                 double f = h0;
 #pragma unroll
                 for (int p = 0; p < P; ++p) f = fma(J[p], rhs[p] - xf[p], f);
@@ -264,6 +319,15 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         if (h.kind == KAFKA_BAND_LINEAR) {
             for (int p = 0; p < n_params; ++p) d.row[p] = h.row[p];
             d.offset = h.offset;
+        } else if (h.kind == KAFKA_BAND_WCM) {
+            for (int p = 0; p < 6; ++p) d.row[p] = h.row[p];
+            for (int k = 0; k < 2; ++k) {
+                int slot = h.mapper[k];
+                KAFKA_CHECK_ARG(slot >= 0 && slot < n_params && d.src[slot] < 0,
+                                "kafka_solve_bands: band %d maps WCM input %d to slot %d", b, k, slot);
+                d.src[slot] = (int8_t)k;
+            }
+            KAFKA_CHECK_ARG(h.row[5] > 0.0, "kafka_solve_bands: band %d has cos(incidence angle) <= 0", b);
         } else if (h.kind == KAFKA_BAND_ARRAYS || h.kind == KAFKA_BAND_UNIFORM) {
             KAFKA_CHECK_ARG(h.h0 && h.jac, "kafka_solve_bands: band %d lacks h0/jac", b);
             KAFKA_CHECK_ARG(h.n_dim >= 1 && h.n_dim <= KAFKA_MAX_DIM, "kafka_solve_bands: band %d n_dim=%d", b, h.n_dim);
@@ -302,6 +366,19 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
     if (rc != 0) return rc;
     reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
     return launch_status("reduce_partials_kernel");
+}
+
+int kafka_wcm_forward(const double* x, int64_t ld, int64_t n, const double* params_host, double* sigma0, double* grad,
+                      void* stream) {
+    KAFKA_CHECK_ARG(n >= 0 && ld >= n, "kafka_wcm_forward: need 0 <= n <= ld");
+    KAFKA_CHECK_ARG(params_host, "kafka_wcm_forward: params is null");
+    KAFKA_CHECK_ARG(params_host[5] > 0.0, "kafka_wcm_forward: cos(incidence angle) must be > 0");
+    if (n == 0) return 0;
+    KAFKA_CHECK_ARG(x && sigma0, "kafka_wcm_forward: null pointer");
+    WcmParams wp;
+    for (int k = 0; k < 6; ++k) wp.prm[k] = params_host[k];
+    wcm_forward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, ld, n, wp, sigma0, grad);
+    return launch_status("wcm_forward_kernel");
 }
 
 int kafka_blend_prior(const double* prior_mean, const double* prior_inv, const double* x_f, const double* pinv_f,

@@ -23,6 +23,24 @@ class BandBuffers(object):
         self.m = torch.zeros((n_bands, ld), dtype=torch.uint8, device=device)
 
 
+class ScaledReflectance(object):
+    """Marker passed in the ``uncertainty`` field of a band whose ``observations``
+    are the RAW scaled-integer surface reflectance (int16 / uint16 / float32
+    raster as read from the granule).  The arithmetic of
+    ``Sentinel2Observations.get_band_data`` (Sentinel2_Observations.py:166-179:
+    ``mask = raw > 0``, ``rho = raw / 10000``, ``sigma = 0.05 rho``, ``R^-1 =
+    1/sigma^2``) then runs on the device, fused with the compaction gather, and
+    only 2-4 bytes per pixel cross PCIe instead of 17.  ``mask`` of such a band
+    may be None or an extra boolean raster that is AND-ed in."""
+
+    RAW_TYPES = {np.dtype(np.int16): _lib.RAW_I16, np.dtype(np.uint16): _lib.RAW_U16,
+                 np.dtype(np.float32): _lib.RAW_F32}
+
+    def __init__(self, divisor=10000.0, rel_sigma=0.05):
+        self.divisor = float(divisor)
+        self.rel_sigma = float(rel_sigma)
+
+
 class _Slot(object):
     """One set of pinned staging buffers + device rasters."""
 
@@ -34,16 +52,18 @@ class _Slot(object):
         self.d_obs = torch.empty((n_bands, n), dtype=torch.float64, device=device)
         self.d_inv = torch.empty((n_bands, n), dtype=torch.float64, device=device)
         self.d_msk = torch.empty((n_bands, n), dtype=torch.uint8, device=device)
+        self.h_raw = self.d_raw = None        # (n_bands, n) 4-byte cells for raw rasters, allocated on first use
         self.copied = [torch.cuda.Event() for _ in range(n_bands)]   # H2D of band b done
         self.gathered = None                                         # main stream finished reading d_*
 
 
 class StagedDate(object):
     """Hand-over between ``stage`` and ``finish``."""
-    __slots__ = ("slot", "n_bands", "device_data")
+    __slots__ = ("slot", "n_bands", "device_data", "raw")
 
-    def __init__(self, slot, n_bands, device_data=None):
+    def __init__(self, slot, n_bands, device_data=None, raw=None):
         self.slot, self.n_bands, self.device_data = slot, n_bands, device_data
+        self.raw = raw or {}                 # band -> (raw_type, ScaledReflectance, has_mask)
 
 
 class ObservationStager(object):
@@ -99,6 +119,14 @@ class ObservationStager(object):
         np.copyto(slot.h_inv[b].numpy()[lo:hi], d._kafka_inv_var[lo:hi], casting="unsafe")
         np.not_equal(np.asarray(d.mask).reshape(-1)[lo:hi], 0, out=slot.h_msk[b].numpy()[lo:hi].view(np.bool_))
 
+    @staticmethod
+    def _stage_raw(slot, b, d, info, lo, hi):
+        dt_ = info[3]
+        dst = slot.h_raw[b].numpy().view(np.uint8)[:slot.h_raw.shape[1] * dt_.itemsize].view(dt_)
+        np.copyto(dst[lo:hi], np.asarray(d.observations).reshape(-1)[lo:hi])
+        if info[2]:
+            np.not_equal(np.asarray(d.mask).reshape(-1)[lo:hi], 0, out=slot.h_msk[b].numpy()[lo:hi].view(np.bool_))
+
     def stage(self, current_data):
         """Start moving one date's rasters to the device; returns a token for ``finish``."""
         nb = len(current_data)
@@ -110,19 +138,46 @@ class ObservationStager(object):
         if slot.gathered is not None:
             self._copy_stream.wait_event(slot.gathered)           # device rasters no longer being gathered
         parts = max(1, min(self.N_THREADS, n // (1 << 20)))       # split big rasters across the pool
-        holders = [_Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n)) for d in current_data]
-        futures = [[self._pool.submit(self._stage_part, slot, b, holders[b], n * k // parts, n * (k + 1) // parts)
-                    for k in range(parts)] for b in range(nb)]
+        raw = {}
+        for b, d in enumerate(current_data):
+            if isinstance(d.uncertainty, ScaledReflectance):
+                dt_ = np.asarray(d.observations).dtype
+                if dt_ not in ScaledReflectance.RAW_TYPES:
+                    raise TypeError("raw reflectance rasters must be int16, uint16 or float32, not %s" % dt_)
+                raw[b] = (ScaledReflectance.RAW_TYPES[dt_], d.uncertainty, d.mask is not None, dt_)
+        if raw and slot.h_raw is None:
+            slot.h_raw = torch.empty((slot.cap, n), dtype=torch.int32).pin_memory()
+            slot.d_raw = torch.empty((slot.cap, n), dtype=torch.int32, device=self.device)
+        holders = [None if b in raw else _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
+                   for b, d in enumerate(current_data)]
+        futures = []
+        for b, d in enumerate(current_data):
+            if b in raw:
+                futures.append([self._pool.submit(self._stage_raw, slot, b, d, raw[b], n * k // parts,
+                                                  n * (k + 1) // parts) for k in range(parts)])
+            else:
+                futures.append([self._pool.submit(self._stage_part, slot, b, holders[b], n * k // parts,
+                                                  n * (k + 1) // parts) for k in range(parts)])
         for b in range(nb):
             for f in futures[b]:
                 f.result()
             with torch.cuda.stream(self._copy_stream):
-                slot.d_obs[b].copy_(slot.h_obs[b], non_blocking=True)
-                slot.d_inv[b].copy_(slot.h_inv[b], non_blocking=True)
-                slot.d_msk[b].copy_(slot.h_msk[b], non_blocking=True)
+                if b in raw:
+                    item = raw[b][3].itemsize
+                    nbytes = n * item
+                    src = slot.h_raw[b].view(torch.uint8)[:nbytes]
+                    slot.d_raw[b].view(torch.uint8)[:nbytes].copy_(src, non_blocking=True)
+                    self.h2d_bytes += nbytes
+                    if raw[b][2]:
+                        slot.d_msk[b].copy_(slot.h_msk[b], non_blocking=True)
+                        self.h2d_bytes += n
+                else:
+                    slot.d_obs[b].copy_(slot.h_obs[b], non_blocking=True)
+                    slot.d_inv[b].copy_(slot.h_inv[b], non_blocking=True)
+                    slot.d_msk[b].copy_(slot.h_msk[b], non_blocking=True)
+                    self.h2d_bytes += n * 17
                 slot.copied[b].record(self._copy_stream)
-        self.h2d_bytes += nb * n * 17
-        return StagedDate(slot, nb)
+        return StagedDate(slot, nb, raw=raw)
 
     def finish(self, token, out=None):
         """Gather the staged rasters into compacted rows on the compute stream."""
@@ -137,9 +192,19 @@ class ObservationStager(object):
             return out
         slot = token.slot
         main = torch.cuda.current_stream(self.device)
+        lib = _lib.get_lib()
         for b in range(nb):
             main.wait_event(slot.copied[b])
-            pix.gather_band(slot.d_obs[b], slot.d_inv[b], slot.d_msk[b], out.y[b], out.w[b], out.m[b])
+            if b in token.raw:
+                raw_type, sr, has_mask, _ = token.raw[b]
+                with torch.cuda.device(self.device):
+                    _lib.check(lib.kafka_gather_scaled_band(_lib.ptr(slot.d_raw[b]), raw_type,
+                                                            _lib.ptr(slot.d_msk[b]) if has_mask else None,
+                                                            _lib.ptr(pix.idx), pix.n_pix, sr.divisor, sr.rel_sigma,
+                                                            _lib.ptr(out.y[b]), _lib.ptr(out.w[b]), _lib.ptr(out.m[b]),
+                                                            _lib.stream_ptr()), "kafka_gather_scaled_band")
+            else:
+                pix.gather_band(slot.d_obs[b], slot.d_inv[b], slot.d_msk[b], out.y[b], out.w[b], out.m[b])
         slot.gathered = torch.cuda.Event()
         slot.gathered.record(main)
         return out
@@ -178,14 +243,20 @@ def make_solve_bands(descs, bufs):
     """ctypes array of kafka_solve_band from python descriptors.
 
     ``descs[b]`` is ("arrays", h0_row, jac_rows(D, ld), mapper),
-    ("uniform", h0(1), jac(D), mapper) or ("linear", row, offset)."""
+    ("uniform", h0(1), jac(D), mapper), ("linear", row, offset) or
+    ("wcm", (A, B, C, D, E, cos_theta), veg_slot, sm_slot)."""
     nb = len(descs)
     arr = (_lib.SolveBand * max(nb, 1))()
     for b, d in enumerate(descs):
         sb = arr[b]
         sb.y = bufs.y[b].data_ptr()
         sb.w = bufs.w[b].data_ptr()
-        if d[0] == "linear":
+        if d[0] == "wcm":
+            sb.kind = _lib.BAND_WCM
+            for p_, v in enumerate(d[1]):
+                sb.row[p_] = float(v)
+            sb.mapper[0], sb.mapper[1] = int(d[2]), int(d[3])
+        elif d[0] == "linear":
             sb.kind = _lib.BAND_LINEAR
             row = np.asarray(d[1], dtype=np.float64)
             for p in range(row.size):
@@ -202,13 +273,13 @@ def make_solve_bands(descs, bufs):
     return arr
 
 
-def solve_bands(ws, descs, bufs, x_prev, x_f, pinv_f, x_out, a_out, want_fwd=False):
+def solve_bands(ws, descs, bufs, x_prev, x_f, pinv_f, x_out, a_out, want_fwd=False, round_f32=False):
     """One linearised update (kafka_solve_bands).  Results land in ``x_out``,
     ``a_out``, ``ws.innov``, ``ws.fwd``; ``ws.norm2`` / ``ws.n_bad`` stay on the
     device until the caller reads them."""
     lib = _lib.get_lib()
     arr = make_solve_bands(descs, bufs)
-    flags = _lib.PRIOR_BROADCAST if pinv_f.is_broadcast else 0
+    flags = (_lib.PRIOR_BROADCAST if pinv_f.is_broadcast else 0) | (_lib.ROUND_F32 if round_f32 else 0)
     with torch.cuda.device(ws.device):
         _lib.check(lib.kafka_solve_bands(ws.n_pix, ws.ld, ws.n_params, arr, len(descs), _lib.ptr(x_prev.data),
                                          _lib.ptr(x_f.data), _lib.ptr(pinv_f.data), _lib.ptr(x_out.data),

@@ -19,7 +19,8 @@ from ..device import BlockDiag, DeviceVector, default_device, tri_count
 
 LOG = logging.getLogger(__name__)
 
-__all__ = ["NoHessianMethod", "band_selecta", "tip_prior", "tip_prior_full", "blend_prior",
+__all__ = ["NoHessianMethod", "band_selecta", "hessian_correction", "hessian_correction_multiband",
+           "hessian_correction_pixel", "tip_prior", "tip_prior_full", "blend_prior",
            "propagate_and_blend_prior", "propagate_standard_kalman",
            "propagate_information_filter_SLOW", "propagate_information_filter_approx_SLOW",
            "propagate_information_filter_LAI", "propagate_information_filter_carry_slot",
@@ -38,6 +39,99 @@ def band_selecta(band):
     if band == 0:
         return np.array([0, 1, 6, 2])
     return np.array([3, 4, 6, 5])
+
+
+def _hessian_mapper(tab, band, nparams, band_mapper=None):
+    """State slots feeding the emulator of ``band``: the whole state when the
+    emulator takes it all, else ``band_mapper[band]``, else the reference's
+    hard-coded TIP selector (kf_tools.py:19-23)."""
+    if band_mapper is not None:
+        return np.asarray(band_mapper[band], dtype=np.int32)
+    if tab.n_dim == nparams:
+        return np.arange(nparams, dtype=np.int32)
+    return band_selecta(band).astype(np.int32)
+
+
+def _hessian_correction_device(gps, x0, ws, innovations, nparams, mappers, device, a_inout=None, want_corr=True):
+    """kafka_gp_hessian_correction for a list of bands.  ``ws`` / ``innovations``
+    are (n_bands, ld) device tensors (w gated to 0 where unobserved)."""
+    from .utils import emulator_table
+    lib = _lib.get_lib()
+    x = DeviceVector.from_interleaved(x0, nparams, device)
+    nb = len(gps)
+    tabs = [emulator_table(g, device) for g in gps]
+    arr = (_lib.GpBand * nb)()
+    for b, (tab, mp) in enumerate(zip(tabs, mappers)):
+        if len(mp) != tab.n_dim:
+            raise ValueError("band %d: mapper has %d entries for a %d-input emulator" % (b, len(mp), tab.n_dim))
+        arr[b].table, arr[b].n_train, arr[b].n_dim = tab.table.data_ptr(), tab.n_train, tab.n_dim
+        for d, slot in enumerate(mp):
+            arr[b].mapper[d] = int(slot)
+    corr = BlockDiag.empty(x.n_pix, nparams, device) if want_corr else None
+    with torch.cuda.device(device):
+        _lib.check(lib.kafka_gp_hessian_correction(_lib.ptr(x.data), x.ld, x.n_pix, nparams, arr, nb,
+                                                   _lib.ptr(innovations), _lib.ptr(ws),
+                                                   _lib.ptr(corr.data) if corr is not None else None,
+                                                   _lib.ptr(a_inout.data) if a_inout is not None else None,
+                                                   _lib.stream_ptr()), "kafka_gp_hessian_correction")
+    return corr
+
+
+def _compact_rows(rasters_or_vectors, state_mask, n, ld, device, gate=None):
+    out = torch.zeros((len(rasters_or_vectors), ld), dtype=torch.float64, device=device)
+    sm = np.asarray(state_mask, dtype=bool)
+    for b, r in enumerate(rasters_or_vectors):
+        v = r.diagonal()[sm.flatten()] if sp.issparse(r) else np.asarray(r, dtype=np.float64)
+        v = v[sm] if v.shape == sm.shape else v.reshape(-1)
+        if gate is not None:
+            v = np.where(gate[b], v, 0.0)
+        out[b, :n] = torch.from_numpy(np.ascontiguousarray(v, dtype=np.float64)).to(device)
+    return out
+
+
+def hessian_correction_pixel(gp, x0, C_obs_inv, innovation, band, nparams):
+    """kf_tools.py:26-34 for one pixel (through the batched kernel)."""
+    x0 = np.asarray(x0, dtype=np.float64).reshape(-1)
+    m = np.ones((1, 1), dtype=bool)
+    R = sp.diags([float(C_obs_inv)])
+    return hessian_correction(gp, x0, R, np.array([innovation]), m, m, band, nparams).blocks()[0]
+
+
+def hessian_correction(gp, x0, R_mat, innovation, mask, state_mask, band, nparams, band_mapper=None):
+    """kf_tools.py:37-60: block-diagonal second-order correction of one band,
+    ``d2h/dx2 * R^-1 * innovation`` per observed pixel, zero elsewhere."""
+    if not hasattr(gp, "inputs"):
+        return 0.                                        # no Hessian available (kf_tools.py:41-44)
+    from .utils import emulator_table
+    device = default_device()
+    sm = np.asarray(state_mask, dtype=bool)
+    n = int(sm.sum())
+    from ..device import padded
+    ld = padded(n)
+    obs = np.asarray(mask)[sm].astype(bool).reshape(-1)
+    ws = _compact_rows([R_mat], sm, n, ld, device, gate=[obs])
+    innov = _compact_rows([np.asarray(innovation, dtype=np.float64).reshape(-1)], sm, n, ld, device)
+    tab = emulator_table(gp, device)
+    return _hessian_correction_device([gp], x0, ws, innov, nparams, [_hessian_mapper(tab, band, nparams, band_mapper)],
+                                      device)
+
+
+def hessian_correction_multiband(gp, x0, R_mats, innovations, masks, state_mask, n_bands, nparams,
+                                 band_mapper=None):
+    """kf_tools.py:63-72: sum of the per-band corrections.  ``gp`` may be one
+    emulator (what the reference passes, linear_kf.py:314) or one per band."""
+    from .utils import emulator_table
+    device = default_device()
+    sm = np.asarray(state_mask, dtype=bool)
+    n = int(sm.sum())
+    from ..device import padded
+    ld = padded(n)
+    gps = list(gp) if isinstance(gp, (list, tuple)) else [gp] * n_bands
+    obs = [np.asarray(m)[sm].astype(bool).reshape(-1) for m in masks]
+    ws = _compact_rows(list(R_mats), sm, n, ld, device, gate=obs)
+    innov = _compact_rows([np.asarray(v, dtype=np.float64).reshape(-1) for v in innovations], sm, n, ld, device)
+    mappers = [_hessian_mapper(emulator_table(g, device), b, nparams, band_mapper) for b, g in enumerate(gps)]
+    return _hessian_correction_device(gps, x0, ws, innov, nparams, mappers, device)
 
 
 def tip_prior():

@@ -40,7 +40,8 @@ class LinearKalman(object):
                  state_propagation=propagate_information_filter_LAI,
                  band_mapper=None,
                  linear=True, diagnostics=True, prior=None, *, device=None, comm=None,
-                 round_operator_f32=True, dedup_uniform_state=True, prefetch_observations=True):
+                 round_operator_f32=True, dedup_uniform_state=True, prefetch_observations=True,
+                 hessian_correction=False):
         _lib.get_lib()                                   # fail now if the CUDA library is missing
         if not isinstance(create_observation_operator, ObservationOperator):
             raise NotImplementedError(
@@ -68,6 +69,9 @@ class LinearKalman(object):
         self.comm = comm
         self.round_operator_f32 = bool(round_operator_f32)
         self.dedup_uniform_state = bool(dedup_uniform_state)
+        # second-order correction of the posterior precision after convergence; the reference
+        # has it switched off on the run() path (linear_kf.py:313-319) and on in assimilate_band
+        self.hessian_correction = bool(hessian_correction)
         # stage the NEXT observation date (observations.get_band_data + host->device copy)
         # while the kernels of the current date run; calls get_band_data one date early
         self.prefetch_observations = bool(prefetch_observations)
@@ -229,7 +233,12 @@ class LinearKalman(object):
         descs = [None] * len(current_data)
         groups = {}
         for b, data in enumerate(current_data):
-            if op.kind == "linear":
+            if op.kind == "wcm":
+                if self.n_params < 2:
+                    raise ValueError("the SAR operator needs a state of (vegetation descriptor, soil moisture)")
+                slots = (0, 1) if self.band_mapper is None else tuple(int(v) for v in self.band_mapper[b][:2])
+                descs[b] = ("wcm", op.band_parameters(b, data.metadata), slots[0], slots[1])
+            elif op.kind == "linear":
                 em = data.emulator
                 row = np.asarray(em.row, dtype=np.float64)
                 if row.size != self.n_params:
@@ -284,7 +293,7 @@ class LinearKalman(object):
         self._token = None
         bufs = self._stager.finish(token if token is not None else self._stager.stage(current_data))
         groups, descs = self._band_plan(current_data)
-        all_linear = not groups
+        all_linear = not groups and all(d is not None and d[0] == "linear" for d in descs)
         n, P = self.n_state_elems, self.n_params
 
         bufsx = [DeviceVector.empty(n, P, self.device), DeviceVector.empty(n, P, self.device)]
@@ -325,9 +334,9 @@ class LinearKalman(object):
                     for k, g in enumerate(group):
                         descs[g[0]] = ("arrays", hsub[k], jsub[k], g[2])
                 x_new = bufsx[(n_iter - 1) % 2]
-                ev = self._tick("solve_bands")
+                ev = self._tick("solve_bands" if shared is None else "solve_bands_shared_linearisation")
                 engine.solve_bands(ws, descs, bufs, x_prev, x_forecast, P_forecast_inverse, x_new, a_out,
-                                   want_fwd=self.want_forward_modelled)
+                                   want_fwd=self.want_forward_modelled, round_f32=self.round_operator_f32)
                 self._tock(ev)
                 if shared is None or n_iter >= 2:
                     # a full emulator pass is now queued: use the wait to stage the next date
@@ -353,8 +362,21 @@ class LinearKalman(object):
             n_iter += 1
 
         n_bad = int(ws.n_bad.item())
+        if n_bad and self._create_observation_operator.kind == "wcm":
+            # the reference's forward model refuses such states (sar_forward_model.py:66-71)
+            raise ValueError("%d pixels left the Water-Cloud model's domain (LAI <= 0 or SM <= 0) or have a "
+                             "non positive-definite information matrix" % n_bad)
         if n_bad:
             LOG.warning("%d pixels had a non positive-definite information matrix; left at the forecast", n_bad)
+        if (self.hessian_correction or getattr(self, "_force_hessian", False)) and groups:
+            # P_analysis_inverse - P_correction (linear_kf.py:319,416), evaluated at x_analysis
+            for group in groups:
+                idxs = [g[0] for g in group]
+                kf_tools._hessian_correction_device(
+                    [current_data[b].emulator for b in idxs], x_analysis,
+                    bufs.w[idxs].contiguous() if len(idxs) != n_bands else bufs.w,
+                    ws.innov[idxs].contiguous() if len(idxs) != n_bands else ws.innov,
+                    P, [g[2] for g in group], self.device, a_inout=a_out, want_corr=False)
         self.last_iterations.append(n_iter - 1)
         self.last_norms.append(norms)
         innovations = DeviceBands(ws.innov.clone(), n)
@@ -383,8 +405,18 @@ class LinearKalman(object):
     def assimilate_band(self, band, timestep, x_forecast, P_forecast,
                         P_forecast_inverse, convergence_tolerance=1e-3,
                         min_iterations=1):
-        """linear_kf.py:356-425 through the multiband kernels with one band."""
+        """linear_kf.py:356-425 through the multiband kernels with one band,
+        including the Hessian correction the reference applies here (:412-416)."""
         data = self.observations.get_band_data(timestep, band)
+        self._force_hessian = True
+        try:
+            return self._assimilate_band(band, timestep, data, x_forecast, P_forecast, P_forecast_inverse,
+                                         convergence_tolerance, min_iterations)
+        finally:
+            self._force_hessian = False
+
+    def _assimilate_band(self, band, timestep, data, x_forecast, P_forecast, P_forecast_inverse,
+                         convergence_tolerance, min_iterations):
         op = self._create_observation_operator
         if op.kind == "gp" and (op.state_mappers is not None or self.band_mapper is not None):
             # the band index selects the state mapper: keep it by padding the plan

@@ -137,6 +137,84 @@ def sparse_to_blocks(A, n_params):
 
 
 # --------------------------------------------------------------------------
+# next rows: SAR Water-Cloud operator, Hessian correction, S2 ingest
+# --------------------------------------------------------------------------
+WCM_PARAMETERS = {'VV': [0.0846, 0.0615, -14.8465, 15.907, 1.],
+                  'VH': [0.0795, 0.1464, -14.8332, 15.907, 0.]}
+
+
+def sar_forward(x, theta_deg, polarisation):
+    """kafka/observation_operators/sar_forward_model.py:56-98, vectorised: returns
+    sigma_0 and the gradient with respect to (V, SM)."""
+    x = np.atleast_2d(np.asarray(x, dtype=np.float64))
+    A, B, C, D, E = WCM_PARAMETERS[polarisation]
+    mu = np.cos(np.deg2rad(theta_deg))
+    V, SM = x[:, 0], x[:, 1]
+    tau = np.exp(-2. * B / mu * V)
+    sigma_veg = A * np.power(V, E) * mu * (1. - tau)
+    sigma_surf = 10. ** ((C + D * SM) / 10.)
+    sigma_0 = sigma_veg + tau * sigma_surf
+    z = np.power(V, E)
+    z1 = np.power(V, E - 1.)
+    g0 = A * E * mu * z1 * (1. - tau) + 2. * A * B * z * tau - (
+        (2. ** (1 / 10. * (C + D * SM) + 1.)) * (5. ** (1 / 10. * (C + D * SM)) * B * tau)) / mu
+    g1 = D * np.log(10.) * tau * 10. ** (1. / 10. * (C + D * SM) - 1.)
+    return sigma_0, np.stack([g0, g1], axis=1)
+
+
+def sar_operator(x_prev, n_params, obs_mask, band, theta_deg=23.0, slots=(0, 1), round_f32=True):
+    """create_sar_observation_operator (sar_forward_model.py:116-173) as dense rows:
+    band 0 = VV, band 1 = VH, incidence angle 23 degrees (:146-156)."""
+    N = x_prev.shape[0] // n_params
+    xs = x_prev.reshape(N, n_params)
+    obs = np.asarray(obs_mask, dtype=bool)
+    H0 = np.zeros(N)
+    J = np.zeros((N, n_params))
+    if obs.any():
+        s0, g = sar_forward(xs[obs][:, list(slots)], theta_deg, ("VV", "VH")[band])
+        H0[obs] = s0
+        Jo = np.zeros((int(obs.sum()), n_params))
+        Jo[:, slots[0]] = g[:, 0]
+        Jo[:, slots[1]] = g[:, 1]
+        J[obs] = Jo
+    if round_f32:
+        H0 = H0.astype(np.float32).astype(np.float64)
+        J = J.astype(np.float32).astype(np.float64)
+    return H0, J
+
+
+def hessian_correction(gp, x0, inv_var, innovation, obs_mask, n_params, mapper):
+    """kf_tools.py:26-60 for one band on compacted vectors: per observed pixel
+    big_ddH * C_obs_inv * innovation with big_ddH the emulator Hessian embedded
+    through ``mapper``; zero blocks for unobserved pixels."""
+    N = x0.shape[0] // n_params
+    xs = x0.reshape(N, n_params)
+    obs = np.asarray(obs_mask, dtype=bool)
+    out = np.zeros((N, n_params, n_params))
+    if obs.any():
+        mapper = np.asarray(mapper)
+        ddH = gp.hessian(xs[obs][:, mapper])
+        big = np.zeros((int(obs.sum()), n_params, n_params))
+        big[:, mapper[:, None], mapper[None, :]] = ddH
+        out[obs] = big * (np.asarray(inv_var)[obs] * np.asarray(innovation)[obs])[:, None, None]
+    return out
+
+
+def s2_ingest(raw, ext_mask=None, divisor=10000.0, rel_sigma=0.05):
+    """Sentinel2_Observations.py:166-179: mask, reflectance and inverse variance
+    (inf where masked) from the raw scaled-integer raster."""
+    mask = raw > 0
+    if ext_mask is not None:
+        mask = mask & (np.asarray(ext_mask) != 0)
+    rho = np.where(mask, raw / divisor, 0)
+    R = rho * rel_sigma
+    R[np.logical_not(mask)] = 0.
+    with np.errstate(divide="ignore"):
+        inv_var = 1. / (R) ** 2
+    return rho, inv_var, mask
+
+
+# --------------------------------------------------------------------------
 # a8/a9  one linearised solve
 # --------------------------------------------------------------------------
 def solve_sparse32(ys, ws, H0s, Js, x_prev, x_f, Pinv_f_sparse):

@@ -19,6 +19,9 @@ run_s2.npz           LinearKalman.run, S2/PROSAIL style (kafka_test_S2.py:174-19
 run_tip.npz          LinearKalman.run, 2-band TIP with state_mapper operators and
                      propagate_information_filter_LAI (kafka_test.py:156-217)
 run_linear.npz       LinearKalman.run, 1 linear band in (H0,H) tuple form
+kat_sar.npz          sar_observation_operator, VV and VH
+                     (observation_operators/sar_forward_model.py:13-113)
+kat_hessian.npz      hessian_correction(_multiband) on the TIP layout (kf_tools.py:26-72)
 """
 import datetime as dt
 import hashlib
@@ -328,9 +331,59 @@ def run_linear(kafka):
     np.savez_compressed(os.path.join(OUT, "run_linear.npz"), **res)
 
 
+def kat_sar(kafka):
+    """sar_observation_operator (observation_operators/sar_forward_model.py:13-113)."""
+    from kafka.observation_operators.sar_forward_model import sar_observation_operator
+    rng = np.random.default_rng(9)
+    n = 400
+    x = np.stack([rng.uniform(0.05, 7.0, n), rng.uniform(0.02, 0.6, n)], axis=1)
+    res = {"x": x}
+    for pol in ("VV", "VH"):
+        s0, g = sar_observation_operator(x, np.full(n, 23.0), pol)
+        res["sigma0_" + pol] = s0
+        res["grad_" + pol] = g
+    np.savez_compressed(os.path.join(OUT, "kat_sar.npz"), **res)
+
+
+def kat_hessian(kafka):
+    """hessian_correction / hessian_correction_multiband (kf_tools.py:26-72) on the
+    TIP layout, with the oracle GP providing gp.hessian."""
+    kt = kafka.inference.kf_tools
+    rng = np.random.default_rng(31)
+    P = 7
+    mask = _small_mask(rng, 9, 11)
+    N = int(mask.sum())
+    mappers = [np.array([0, 1, 6, 2]), np.array([3, 4, 6, 5])]
+    gps = [syn.make_emulator(rng, syn.TIP_MEAN[m], syn.TIP_SIGMA[m], n_train=80, w_scale=0.15,
+                             cls=GaussianProcess) for m in mappers]
+    x0 = (syn.TIP_MEAN + 0.4 * syn.TIP_SIGMA * rng.standard_normal((N, P))).ravel()
+    res = {"mask": mask, "x0": x0}
+    res.update(_gp_arrays("gp", gps))
+    Rs, innovs, masks = [], [], []
+    for b in range(2):
+        omask = rng.random(mask.shape) < 0.8
+        inv = np.where(omask, rng.uniform(100., 900., mask.shape), np.inf)
+        R = syn.inverse_variance_matrix(inv)
+        innov = 0.05 * rng.standard_normal(N)
+        corr = kt.hessian_correction(gps[b], x0, R, innov, omask, mask, b, P)
+        dense = corr.toarray()
+        res["corr_%d" % b] = np.array([dense[i * P:(i + 1) * P, i * P:(i + 1) * P] for i in range(N)])
+        res["obs_mask_%d" % b], res["inv_var_%d" % b], res["innov_%d" % b] = omask, inv, innov
+        Rs.append(R)
+        innovs.append(innov)
+        masks.append(omask)
+    # the reference passes ONE emulator for every band (linear_kf.py:314)
+    multi = kt.hessian_correction_multiband(gps[0], x0, Rs, innovs, masks, mask, 2, P)
+    dense = multi.toarray()
+    res["corr_multi_gp0"] = np.array([dense[i * P:(i + 1) * P, i * P:(i + 1) * P] for i in range(N)])
+    np.savez_compressed(os.path.join(OUT, "kat_hessian.npz"), **res)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     kafka = ref_shim.load()
+    kat_sar(kafka)
+    kat_hessian(kafka)
     kat_propagators(kafka)
     kat_time_grid(kafka)
     barrax_mask()

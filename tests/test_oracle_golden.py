@@ -242,3 +242,43 @@ def test_run_linear_vs_reference(mode):
     for k, (t, x, Pinv, _) in enumerate(rows):
         assert np.allclose(Pinv[:, idx, idx].ravel(), g["out_diag"][k], rtol=5e-6)
         assert np.allclose(x, g["out_x"][k], rtol=1e-4, atol=1e-6)
+
+
+# ---- "next" rows: SAR Water-Cloud operator, Hessian correction, S2 ingest ---
+def test_sar_forward_vs_reference():
+    g = gio.load("kat_sar")
+    for pol in ("VV", "VH"):
+        s0, grad = kc.sar_forward(g["x"], 23.0, pol)
+        assert np.allclose(s0, g["sigma0_" + pol], rtol=1e-13)
+        assert np.allclose(grad, g["grad_" + pol], rtol=1e-12, atol=1e-18)
+
+
+def test_hessian_correction_vs_reference():
+    g = gio.load("kat_hessian")
+    mask = g["mask"]
+    gps = gio.emulators(g, GaussianProcess)
+    mappers = [np.array([0, 1, 6, 2]), np.array([3, 4, 6, 5])]
+    total = 0
+    for b in range(2):
+        obs = g["obs_mask_%d" % b][mask]
+        inv = g["inv_var_%d" % b][mask]
+        c = kc.hessian_correction(gps[b], g["x0"], inv, g["innov_%d" % b], obs, 7, mappers[b])
+        assert np.allclose(c, g["corr_%d" % b], rtol=1e-10, atol=1e-12)
+        assert not c[~obs].any()
+        total = total + kc.hessian_correction(gps[0], g["x0"], inv, g["innov_%d" % b], obs, 7, mappers[b])
+    assert np.allclose(total, g["corr_multi_gp0"], rtol=1e-9, atol=1e-10)
+
+
+def test_s2_ingest_matches_reader_arithmetic():
+    # Sentinel2_Observations.py:166-179 restated; checked against the literal numpy expressions
+    rng = np.random.default_rng(0)
+    raw = rng.integers(-50, 9000, size=(40, 50)).astype(np.int16)
+    rho, inv, m = kc.s2_ingest(raw)
+    mask = raw > 0
+    want = np.where(mask, raw / 10000., 0)
+    R = want * 0.05
+    R[~mask] = 0.
+    with np.errstate(divide="ignore"):
+        want_inv = 1. / R ** 2
+    assert np.array_equal(m, mask) and np.array_equal(rho, want) and np.array_equal(inv, want_inv)
+    assert np.isinf(inv[~mask]).all()
