@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "libkafka_b200.so")
+LIB_PATH = os.environ.get("KAFKA_B200_LIB") or os.path.join(HERE, "csrc", "libkafka_b200.so")
 
 MAX_PARAMS = 16
 MAX_BANDS = 16

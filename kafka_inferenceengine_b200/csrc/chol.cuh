@@ -7,6 +7,10 @@ namespace kafka {
 
 // In place A -> L (A = L L^T), diagonal stored as 1/L_jj in invd.  Returns false
 // when the block is not positive definite.
+// All loops run over the full compile-time range 0..P-1 with a guard instead of a
+// data-dependent bound: after unrolling every guard folds away and every index is a
+// literal (with triangular bounds the compiler refuses to unroll some sizes and drops the
+// block into local memory).
 template <int P>
 __device__ __forceinline__ bool chol_factor(double (&A)[tri_count(P)], double (&invd)[P]) {
     bool ok = true;
@@ -14,17 +18,21 @@ __device__ __forceinline__ bool chol_factor(double (&A)[tri_count(P)], double (&
     for (int j = 0; j < P; ++j) {
         double d = A[tri(j, j)];
 #pragma unroll
-        for (int k = 0; k < j; ++k) d = fma(-A[tri(j, k)], A[tri(j, k)], d);
+        for (int k = 0; k < P; ++k)
+            if (k < j) d = fma(-A[tri(j, k)], A[tri(j, k)], d);
         ok = ok && (d > 0.0);
         double inv = rsqrt(d);   // <= 1 ulp in fp64
         invd[j] = inv;
         A[tri(j, j)] = d * inv;
 #pragma unroll
-        for (int i = j + 1; i < P; ++i) {
-            double s = A[tri(i, j)];
+        for (int i = 0; i < P; ++i) {
+            if (i > j) {
+                double s = A[tri(i, j)];
 #pragma unroll
-            for (int k = 0; k < j; ++k) s = fma(-A[tri(i, k)], A[tri(j, k)], s);
-            A[tri(i, j)] = s * inv;
+                for (int k = 0; k < P; ++k)
+                    if (k < j) s = fma(-A[tri(i, k)], A[tri(j, k)], s);
+                A[tri(i, j)] = s * inv;
+            }
         }
     }
     return ok;
@@ -37,14 +45,17 @@ __device__ __forceinline__ void chol_solve(const double (&Lm)[tri_count(P)], con
     for (int i = 0; i < P; ++i) {
         double s = b[i];
 #pragma unroll
-        for (int k = 0; k < i; ++k) s = fma(-Lm[tri(i, k)], b[k], s);
+        for (int k = 0; k < P; ++k)
+            if (k < i) s = fma(-Lm[tri(i, k)], b[k], s);
         b[i] = s * invd[i];
     }
 #pragma unroll
-    for (int i = P - 1; i >= 0; --i) {
+    for (int ii = 0; ii < P; ++ii) {
+        const int i = P - 1 - ii;
         double s = b[i];
 #pragma unroll
-        for (int k = i + 1; k < P; ++k) s = fma(-Lm[tri(k, i)], b[k], s);
+        for (int k = 0; k < P; ++k)
+            if (k > i) s = fma(-Lm[tri(k, i)], b[k], s);
         b[i] = s * invd[i];
     }
 }

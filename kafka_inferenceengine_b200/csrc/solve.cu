@@ -7,6 +7,8 @@
 // right-hand side live in registers, every global access is a coalesced planar
 // load/store (consecutive threads = consecutive pixels), nothing is re-read.
 // This kernel is HBM-bound; algorithmic bytes per pixel are in DESIGN.md.
+#include <stdlib.h>
+
 #include "chol.cuh"
 
 namespace kafka {
@@ -19,6 +21,7 @@ struct SolveBandDev {
     double row[KAFKA_MAX_PARAMS];
     double offset;
     int32_t kind;
+    int32_t n_planes;               // ARRAYS: Jacobian planes of this band
     int8_t src[KAFKA_MAX_PARAMS];   // Jacobian plane feeding state slot p, -1 = none
 };
 
@@ -38,7 +41,10 @@ struct SolveParams {
     uint32_t flags;
 };
 
-constexpr int kSolveThreads = 128;
+#ifndef KAFKA_SOLVE_THREADS
+#define KAFKA_SOLVE_THREADS 128
+#endif
+constexpr int kSolveThreads = KAFKA_SOLVE_THREADS;
 
 // Water-Cloud model and its gradient (sar_forward_model.py:74-98); prm = A,B,C,D,E,cos(theta)
 __device__ __forceinline__ void wcm_eval(const double* __restrict__ prm, double V, double SM, double& s0, double& g0,
@@ -208,6 +214,155 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm) {
     }
 }
 
+// ---------------------------------------------------------------------------
+// TMA-pipelined variant (the fast path).  The band loop of the kernel above is
+// latency bound: 238 registers leave 8 warps per SM and every band's 3+D loads
+// are consumed immediately.  Here one elected thread streams each band's rows
+// (w, y, H0, J planes: 1 KB each for the CTA's 128 pixels) into a 3-stage
+// shared-memory ring with cp.async.bulk + mbarrier, two bands ahead of the
+// arithmetic, so ~40 KB per CTA are in flight without costing a register.
+// ---------------------------------------------------------------------------
+constexpr int kSolveStages = 3;
+
+template <int P>
+__device__ __forceinline__ void band_row_staged(const SolveBandDev& bd, const double* __restrict__ st, int n_dim_max,
+                                                const double (&xp)[P], double w, double (&J)[P], double& h0,
+                                                bool round32, bool& domain_bad) {
+    // stage layout: [w | y | h0 | jac plane 0 .. n_dim-1], kSolveThreads doubles each
+    if (bd.kind == KAFKA_BAND_ARRAYS) {
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+            J[p] = bd.src[p] >= 0 ? st[(3 + bd.src[p]) * kSolveThreads + threadIdx.x] : 0.0;
+        h0 = st[2 * kSolveThreads + threadIdx.x];
+    } else {
+        band_row<P>(bd, 0, 0, xp, w, J, h0, round32, domain_bad);     // LINEAR / UNIFORM / WCM: nothing per pixel to load
+    }
+}
+
+template <int P>
+__global__ void __launch_bounds__(kSolveThreads)
+solve_bands_tma_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
+    constexpr int L = tri_count(P);
+    extern __shared__ __align__(16) double stages[];               // kSolveStages x (3 + n_dim_max) x 128
+    __shared__ uint64_t bars[kSolveStages];
+    __shared__ double s_part[2][kSolveThreads / 32];
+    const int64_t tile0 = (int64_t)blockIdx.x * kSolveThreads;
+    const int64_t i = tile0 + threadIdx.x;
+    const int64_t ld = prm.ld;
+    const uint32_t row_bytes = (uint32_t)(min((int64_t)kSolveThreads, ld - tile0) * sizeof(double));
+    const int stage_doubles = (3 + n_dim_max) * kSolveThreads;
+    double ssq = 0.0, bad = 0.0;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < kSolveStages; ++s) mbar_init(&bars[s], 1);
+    }
+    __syncthreads();
+
+    auto issue = [&](int b) {                                       // one thread: queue band b's rows
+        const SolveBandDev& bd = prm.bands[b];
+        double* st = stages + (b % kSolveStages) * stage_doubles;
+        uint64_t* bar = &bars[b % kSolveStages];
+        const int planes = bd.kind == KAFKA_BAND_ARRAYS ? 3 + bd.n_planes : 2;
+        mbar_expect_tx(bar, row_bytes * planes);
+        tma_bulk_g2s(st, bd.w + tile0, row_bytes, bar);
+        tma_bulk_g2s(st + kSolveThreads, bd.y + tile0, row_bytes, bar);
+        if (bd.kind == KAFKA_BAND_ARRAYS) {
+            tma_bulk_g2s(st + 2 * kSolveThreads, bd.h0 + tile0, row_bytes, bar);
+            for (int d = 0; d < bd.n_planes; ++d)
+                tma_bulk_g2s(st + (3 + d) * kSolveThreads, bd.jac + (int64_t)d * ld + tile0, row_bytes, bar);
+        }
+    };
+    if (threadIdx.x == 0)
+        for (int b = 0; b < min(kSolveStages, prm.n_bands); ++b) issue(b);
+
+    const bool live = i < prm.n_pix;
+    const int64_t il = live ? i : tile0;                            // padding lanes read a valid pixel, write nothing
+    double A[L], rhs[P], xp[P], xf[P];
+    const bool bcast = (prm.flags & KAFKA_PRIOR_BROADCAST) != 0;
+    const bool round32 = (prm.flags & KAFKA_ROUND_F32) != 0;
+    bool domain_bad = false;
+#pragma unroll
+    for (int c = 0; c < L; ++c) A[c] = bcast ? prm.pinv_f[c] : ldg_stream(prm.pinv_f + (int64_t)c * ld + il);
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        xp[p] = ldg_stream(prm.x_prev + (int64_t)p * ld + il);
+        xf[p] = ldg_stream(prm.x_f + (int64_t)p * ld + il);
+    }
+    symv<P>(A, xf, rhs);
+
+    for (int b = 0; b < prm.n_bands; ++b) {
+        const SolveBandDev& bd = prm.bands[b];
+        const double* st = stages + (b % kSolveStages) * stage_doubles;
+        mbar_wait(&bars[b % kSolveStages], (uint32_t)((b / kSolveStages) & 1));
+        const double w = st[threadIdx.x];
+        const double y = st[kSolveThreads + threadIdx.x];
+        double J[P], h0;
+        band_row_staged<P>(bd, st, n_dim_max, xp, w, J, h0, round32, domain_bad);
+        double yp = y - h0;
+#pragma unroll
+        for (int p = 0; p < P; ++p) yp = fma(J[p], xp[p], yp);
+        const double wy = w * yp;
+#pragma unroll
+        for (int r = 0; r < P; ++r) {
+            const double wj = w * J[r];
+            rhs[r] = fma(wy, J[r], rhs[r]);
+#pragma unroll
+            for (int q = 0; q <= r; ++q) A[tri(r, q)] = fma(wj, J[q], A[tri(r, q)]);
+        }
+        if (prm.innovations && live) stg_stream(prm.innovations + (int64_t)b * ld + i, y - h0);
+        __syncthreads();                                            // every thread has consumed this stage
+        if (threadIdx.x == 0 && b + kSolveStages < prm.n_bands) issue(b + kSolveStages);
+    }
+
+    if (live) {
+#pragma unroll
+        for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A[c]);
+        double invd[P];
+        const bool ok = chol_factor<P>(A, invd) && !domain_bad;
+        chol_solve<P>(A, invd, rhs);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const double xn = ok ? rhs[p] : xf[p];
+            rhs[p] = xn;
+            stg_stream(prm.x_out + (int64_t)p * ld + i, xn);
+            const double d = xn - xp[p];
+            ssq = fma(d, d, ssq);
+        }
+        bad = ok ? 0.0 : 1.0;
+        if (prm.fwd) {
+            for (int b = 0; b < prm.n_bands; ++b) {
+                const SolveBandDev& bd = prm.bands[b];
+                double J[P], h0;
+                bool dummy = false;
+                band_row<P>(bd, ld, i, xp, bd.w[i], J, h0, round32, dummy);
+                double f = h0;
+#pragma unroll
+                for (int p = 0; p < P; ++p) f = fma(J[p], rhs[p] - xf[p], f);
+                stg_stream(prm.fwd + (int64_t)b * ld + i, f);
+            }
+        }
+    }
+
+    ssq = warp_sum(ssq);
+    bad = warp_sum(bad);
+    if ((threadIdx.x & 31) == 0) {
+        s_part[0][threadIdx.x >> 5] = ssq;
+        s_part[1][threadIdx.x >> 5] = bad;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < kSolveThreads / 32; ++k) {
+            s0 += s_part[0][k];
+            s1 += s_part[1][k];
+        }
+        prm.partials[blockIdx.x] = s0;
+        prm.partials[gridDim.x + blockIdx.x] = s1;
+    }
+}
+
 // Fixed-order second stage: same bits every run, whatever the launch order.
 __global__ void __launch_bounds__(256)
 reduce_partials_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ norm2,
@@ -333,6 +488,7 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
             KAFKA_CHECK_ARG(h.n_dim >= 1 && h.n_dim <= KAFKA_MAX_DIM, "kafka_solve_bands: band %d n_dim=%d", b, h.n_dim);
             d.h0 = h.h0;
             d.jac = h.jac;
+            d.n_planes = h.n_dim;
             for (int k = 0; k < h.n_dim; ++k) {
                 int slot = h.mapper[k];
                 KAFKA_CHECK_ARG(slot >= 0 && slot < n_params, "kafka_solve_bands: band %d maps plane %d to slot %d", b, k,
@@ -358,11 +514,39 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
     prm.n_bands = n_bands;
     prm.flags = flags;
     const unsigned grid = (unsigned)((n_pix + kSolveThreads - 1) / kSolveThreads);
+    // TMA bulk copies need 16-byte aligned rows whose padded tail stays inside the arrays
+    bool tma_ok = n_bands > 0 && (ld % 2) == 0;
+    int n_dim_max = 0;
+    for (int b = 0; b < n_bands && tma_ok; ++b) {
+        const SolveBandDev& d = prm.bands[b];
+        auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+        tma_ok = al(d.w) && al(d.y);
+        if (d.kind == KAFKA_BAND_ARRAYS) {
+            tma_ok = tma_ok && al(d.h0) && al(d.jac);
+            n_dim_max = d.n_planes > n_dim_max ? d.n_planes : n_dim_max;
+        }
+    }
+    if (getenv("KAFKA_SOLVE_NO_TMA")) tma_ok = false;
     int rc = KAFKA_E_UNSUPPORTED;
-    KAFKA_DISPATCH_P(n_params, {
-        solve_bands_kernel<kP><<<grid, kSolveThreads, 0, s>>>(prm);
-        rc = launch_status("solve_bands_kernel");
-    });
+    if (tma_ok) {
+        const size_t smem = (size_t)kSolveStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
+        KAFKA_DISPATCH_P(n_params, {
+            auto kern = solve_bands_tma_kernel<kP>;
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) {
+                set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+                rc = (int)e;
+            } else {
+                kern<<<grid, kSolveThreads, smem, s>>>(prm, n_dim_max);
+                rc = launch_status("solve_bands_tma_kernel");
+            }
+        });
+    } else {
+        KAFKA_DISPATCH_P(n_params, {
+            solve_bands_kernel<kP><<<grid, kSolveThreads, 0, s>>>(prm);
+            rc = launch_status("solve_bands_kernel");
+        });
+    }
     if (rc != 0) return rc;
     reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
     return launch_status("reduce_partials_kernel");
