@@ -491,6 +491,15 @@ def main():
         fp64_peak = float(probe.kafka_probe_fp64_tflops(5))
     except OSError:
         pass
+    # DRAM traffic per pixel of each kernel from the committed ncu --set full capture
+    # (profiles/r01_ncu_kernels.json, written by profiles/summarize_ncu.py)
+    ncu_bpp = {}
+    try:
+        for k in json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_kernels.json")))["kernels"]:
+            if "dram_bytes_per_pixel" in k:
+                ncu_bpp[k["kernel"].split("<")[0].replace("void ", "")] = k["dram_bytes_per_pixel"]
+    except Exception:
+        pass
     gp_ms = float(np.mean(prof.get("gp_linearize", [float("nan")])))
     sv_ms = float(np.mean(prof.get("solve_bands", [float("nan")])))
     n_iter_mean = float(np.mean(iters))
@@ -505,7 +514,11 @@ def main():
         "kernel": "gp_linearize_kernel<10,2> (GP emulator mean+Jacobian, all bands, one launch per iteration)",
         "bound": "hbm",
         "achieved": gp_bytes / (gp_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-        "frac": gp_bytes / (gp_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
+        "frac": gp_bytes / (gp_ms * 1e-3) / 1e9 / hbm_peak,
+        "traffic": (ncu_bpp["gp_linearize_kernel"] * n_pix) if "gp_linearize_kernel" in ncu_bpp else None,
+        "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per pixel from profiles/r01_ncu_kernels.json "
+                          "(ncu --set full, 2.196 M px launch) x pixels of this launch",
+        "peak_source": peak_src,
         "algorithmic_bytes_per_launch": gp_bytes, "ms_per_launch": gp_ms,
         "share_of_step": float(np.sum(prof.get("gp_linearize", [0.0]))) / args.steps / ms_step,
         "note": "this kernel is fp64-pipe bound, not HBM bound (SURVEY 8d: ~195 kflop vs ~1 kB per pixel-iteration); "
@@ -513,10 +526,13 @@ def main():
         "fp64": {"achieved": gp_tf, "peak": fp64_peak, "unit": "TFLOP/s (algorithmic: B*T*(5D+28) per pixel)",
                  "frac": (gp_tf / fp64_peak) if fp64_peak else None,
                  "peak_source": "DFMA probe measured in this run (benchmarks/probe.cu)"},
-        "solve_kernel": {"kernel": "solve_bands_kernel<10> (normal equations + Cholesky + partial norm)",
+        "solve_kernel": {"kernel": "solve_bands_tma_kernel<10> (normal equations + Cholesky + partial norm; per-pixel "
+                                   "operators, i.e. the launches of iteration >= 2) + reduce_partials_kernel",
                          "bound": "hbm", "achieved": sv_bytes / (sv_ms * 1e-3) / 1e9, "peak": hbm_peak,
                          "unit": "GB/s", "frac": sv_bytes / (sv_ms * 1e-3) / 1e9 / hbm_peak,
-                         "algorithmic_bytes_per_launch": sv_bytes, "ms_per_launch": sv_ms},
+                         "algorithmic_bytes_per_launch": sv_bytes, "ms_per_launch": sv_ms,
+                         "traffic": (ncu_bpp["solve_bands_tma_kernel"] * n_pix)
+                         if "solve_bands_tma_kernel" in ncu_bpp else None},
         "step": {"bytes_per_pixel_date": BYTES_PER_PIXEL_DATE,
                  "achieved": n_pix * BYTES_PER_PIXEL_DATE / (ms_step * 1e-3) / 1e9, "unit": "GB/s",
                  "frac": n_pix * BYTES_PER_PIXEL_DATE / (ms_step * 1e-3) / 1e9 / hbm_peak},

@@ -18,15 +18,15 @@ CSRC = os.path.join(ROOT, "kafka_inferenceengine_b200", "csrc")
 OUT = os.path.join(HERE, "variants")
 VARIANTS = {
     "default": [],
-    "ppt1": ["-DKAFKA_GP_FORCE_PPT=1"],
+    "u1": ["-DKAFKA_GP_UNROLL=1"],
+    "u3": ["-DKAFKA_GP_UNROLL=3"],
+    "u4": ["-DKAFKA_GP_UNROLL=4"],
+    "u4_mb2": ["-DKAFKA_GP_UNROLL=4", "-DKAFKA_GP_MINBLOCKS=2"],
+    "u2_mb2": ["-DKAFKA_GP_MINBLOCKS=2"],
+    "u2_mb4": ["-DKAFKA_GP_MINBLOCKS=4"],
     "ppt1_u4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_UNROLL=4"],
-    "ppt2_u1": ["-DKAFKA_GP_UNROLL=1"],
-    "ppt2_u4": ["-DKAFKA_GP_UNROLL=4"],
-    "ppt2_t256": ["-DKAFKA_GP_THREADS=256"],
-    "ppt2_t64": ["-DKAFKA_GP_THREADS=64"],
-    "ppt2_mb4": ["-DKAFKA_GP_MINBLOCKS=4"],
-    "ppt1_t256": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_THREADS=256"],
-    "ppt1_mb5": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=5"],
+    "ppt1_u4_mb5": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_UNROLL=4", "-DKAFKA_GP_MINBLOCKS=5"],
+    "t256_mb1": ["-DKAFKA_GP_THREADS=256"],
 }
 
 
