@@ -2,6 +2,7 @@
 observation upload + compaction gather, band descriptors and the call into the
 fused build+solve kernel.  No arithmetic happens here."""
 import ctypes as C
+import os
 
 import numpy as np
 import scipy.sparse as sp
@@ -79,7 +80,8 @@ class ObservationStager(object):
     of the current date are still running (``LinearKalman`` does that from its
     iteration loop).  Buffers are allocated once and reused across dates."""
 
-    N_THREADS = 8
+    # staging threads: up to 8, but never more than this rank's share of the host cores
+    N_THREADS = max(2, min(8, (os.cpu_count() or 8) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))))
     N_SLOTS = 2
 
     def __init__(self, pix):
