@@ -526,13 +526,13 @@ def main():
         "fp64": {"achieved": gp_tf, "peak": fp64_peak, "unit": "TFLOP/s (algorithmic: B*T*(5D+28) per pixel)",
                  "frac": (gp_tf / fp64_peak) if fp64_peak else None,
                  "peak_source": "DFMA probe measured in this run (benchmarks/probe.cu)"},
-        "solve_kernel": {"kernel": "solve_bands_tma_kernel<10> (normal equations + Cholesky + partial norm; per-pixel "
+        "solve_kernel": {"kernel": "solve_bands_kernel<10> (normal equations + Cholesky + partial norm; per-pixel "
                                    "operators, i.e. the launches of iteration >= 2) + reduce_partials_kernel",
                          "bound": "hbm", "achieved": sv_bytes / (sv_ms * 1e-3) / 1e9, "peak": hbm_peak,
                          "unit": "GB/s", "frac": sv_bytes / (sv_ms * 1e-3) / 1e9 / hbm_peak,
                          "algorithmic_bytes_per_launch": sv_bytes, "ms_per_launch": sv_ms,
-                         "traffic": (ncu_bpp["solve_bands_tma_kernel"] * n_pix)
-                         if "solve_bands_tma_kernel" in ncu_bpp else None},
+                         "traffic": (ncu_bpp["solve_bands_kernel"] * n_pix)
+                         if "solve_bands_kernel" in ncu_bpp else None},
         "step": {"bytes_per_pixel_date": BYTES_PER_PIXEL_DATE,
                  "achieved": n_pix * BYTES_PER_PIXEL_DATE / (ms_step * 1e-3) / 1e9, "unit": "GB/s",
                  "frac": n_pix * BYTES_PER_PIXEL_DATE / (ms_step * 1e-3) / 1e9 / hbm_peak},

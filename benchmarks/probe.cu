@@ -38,7 +38,52 @@ __global__ void __launch_bounds__(256) fp64_dmma_probe(double* out, int iters, d
     if (s == 123.456) out[0] = s;
 }
 
+// Planar streaming pattern of the solve kernel: every thread reads R planes and writes W planes
+// (plane stride ld doubles), nothing else.  Tells how much of the copy bandwidth this access
+// pattern can reach, independent of the arithmetic.
+__global__ void __launch_bounds__(128) planar_stream_probe(const double* __restrict__ in, double* __restrict__ out,
+                                                           long long n, long long ld, int R, int W) {
+    long long i = (long long)blockIdx.x * 128 + threadIdx.x;
+    if (i >= n) return;
+    double acc = 0.0;
+    for (int r = 0; r < R; r += 4) {
+        double a = __ldcs(in + (long long)r * ld + i);
+        double b = r + 1 < R ? __ldcs(in + (long long)(r + 1) * ld + i) : 0.0;
+        double c = r + 2 < R ? __ldcs(in + (long long)(r + 2) * ld + i) : 0.0;
+        double d = r + 3 < R ? __ldcs(in + (long long)(r + 3) * ld + i) : 0.0;
+        acc += (a + b) + (c + d);
+    }
+    for (int w = 0; w < W; ++w) __stcs(out + (long long)w * ld + i, acc + w);
+}
+
 extern "C" {
+double kafka_probe_planar_stream_gbs(long long n, int R, int W, int reps) {
+    double *in = nullptr, *out = nullptr;
+    long long ld = n;
+    if (cudaMalloc(&in, (size_t)R * ld * 8) != cudaSuccess) return -1.0;
+    if (cudaMalloc(&out, (size_t)W * ld * 8) != cudaSuccess) { cudaFree(in); return -1.0; }
+    cudaMemset(in, 0, (size_t)R * ld * 8);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0.0;
+    for (int r = 0; r < reps + 1; ++r) {
+        cudaEventRecord(e0);
+        planar_stream_probe<<<(unsigned)((n + 127) / 128), 128>>>(in, out, n, ld, R, W);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double gbs = (double)(R + W) * n * 8 / (ms * 1e-3) / 1e9;
+        if (r > 0 && gbs > best) best = gbs;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(in);
+    cudaFree(out);
+    return best;
+}
+
 double kafka_probe_dmma_tflops(int reps) {
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);

@@ -7,56 +7,53 @@ namespace kafka {
 
 // In place A -> L (A = L L^T), diagonal stored as 1/L_jj in invd.  Returns false
 // when the block is not positive definite.
+// Right-looking (outer-product) form: once column j is known, the whole trailing block is
+// updated with INDEPENDENT FMAs, so the dependent chain per column is rsqrt -> scale -> one
+// FMA instead of a j-term dot product.  With 8 warps per SM the solve kernels are bound by
+// instruction latency, and this halves the critical path of the factorisation.
 // All loops run over the full compile-time range 0..P-1 with a guard instead of a
-// data-dependent bound: after unrolling every guard folds away and every index is a
-// literal (with triangular bounds the compiler refuses to unroll some sizes and drops the
-// block into local memory).
+// data-dependent bound: after unrolling every guard folds away and every index is a literal
+// (with triangular bounds the compiler refuses to unroll some sizes and drops the block into
+// local memory).
 template <int P>
 __device__ __forceinline__ bool chol_factor(double (&A)[tri_count(P)], double (&invd)[P]) {
     bool ok = true;
 #pragma unroll
     for (int j = 0; j < P; ++j) {
-        double d = A[tri(j, j)];
-#pragma unroll
-        for (int k = 0; k < P; ++k)
-            if (k < j) d = fma(-A[tri(j, k)], A[tri(j, k)], d);
+        const double d = A[tri(j, j)];
         ok = ok && (d > 0.0);
-        double inv = rsqrt(d);   // <= 1 ulp in fp64
+        const double inv = rsqrt(d);   // <= 1 ulp in fp64
         invd[j] = inv;
         A[tri(j, j)] = d * inv;
 #pragma unroll
-        for (int i = 0; i < P; ++i) {
-            if (i > j) {
-                double s = A[tri(i, j)];
+        for (int i = 0; i < P; ++i)
+            if (i > j) A[tri(i, j)] *= inv;
 #pragma unroll
-                for (int k = 0; k < P; ++k)
-                    if (k < j) s = fma(-A[tri(i, k)], A[tri(j, k)], s);
-                A[tri(i, j)] = s * inv;
-            }
-        }
+        for (int i = 0; i < P; ++i)
+#pragma unroll
+            for (int k = 0; k < P; ++k)
+                if (i > j && k > j && k <= i) A[tri(i, k)] = fma(-A[tri(i, j)], A[tri(k, j)], A[tri(i, k)]);
     }
     return ok;
 }
 
-// Solve L L^T x = b in place.
+// Solve L L^T x = b in place (column-oriented substitutions, same reasoning).
 template <int P>
 __device__ __forceinline__ void chol_solve(const double (&Lm)[tri_count(P)], const double (&invd)[P], double (&b)[P]) {
 #pragma unroll
-    for (int i = 0; i < P; ++i) {
-        double s = b[i];
+    for (int k = 0; k < P; ++k) {
+        b[k] *= invd[k];
 #pragma unroll
-        for (int k = 0; k < P; ++k)
-            if (k < i) s = fma(-Lm[tri(i, k)], b[k], s);
-        b[i] = s * invd[i];
+        for (int i = 0; i < P; ++i)
+            if (i > k) b[i] = fma(-Lm[tri(i, k)], b[k], b[i]);
     }
 #pragma unroll
-    for (int ii = 0; ii < P; ++ii) {
-        const int i = P - 1 - ii;
-        double s = b[i];
+    for (int kk = 0; kk < P; ++kk) {
+        const int k = P - 1 - kk;
+        b[k] *= invd[k];
 #pragma unroll
-        for (int k = 0; k < P; ++k)
-            if (k > i) s = fma(-Lm[tri(k, i)], b[k], s);
-        b[i] = s * invd[i];
+        for (int i = 0; i < P; ++i)
+            if (i < k) b[i] = fma(-Lm[tri(k, i)], b[k], b[i]);
     }
 }
 

@@ -5,8 +5,9 @@
 //
 // One thread owns one pixel: the packed P x P block (P(P+1)/2 fp64) and the
 // right-hand side live in registers, every global access is a coalesced planar
-// load/store (consecutive threads = consecutive pixels), nothing is re-read.
-// This kernel is HBM-bound; algorithmic bytes per pixel are in DESIGN.md.
+// access (consecutive threads = consecutive pixels), nothing is re-read.  The
+// band rows are prefetched through a thread-private cp.async ring (see the
+// kernel).  This kernel is HBM-bound; algorithmic bytes per pixel are in DESIGN.md.
 #include <stdlib.h>
 
 #include "chol.cuh"
@@ -123,108 +124,6 @@ __device__ __forceinline__ void band_row(const SolveBandDev& bd, int64_t ld, int
 }
 
 template <int P>
-__global__ void __launch_bounds__(kSolveThreads)
-solve_bands_kernel(const __grid_constant__ SolveParams prm) {
-    constexpr int L = tri_count(P);
-    __shared__ double s_part[2][kSolveThreads / 32];
-    const int64_t i = (int64_t)blockIdx.x * kSolveThreads + threadIdx.x;
-    const int64_t ld = prm.ld;
-    double ssq = 0.0, bad = 0.0;
-
-    if (i < prm.n_pix) {
-        double A[L], rhs[P], xp[P], xf[P];
-        const bool bcast = (prm.flags & KAFKA_PRIOR_BROADCAST) != 0;
-        const bool round32 = (prm.flags & KAFKA_ROUND_F32) != 0;
-        bool domain_bad = false;
-#pragma unroll
-        for (int c = 0; c < L; ++c) A[c] = bcast ? prm.pinv_f[c] : ldg_stream(prm.pinv_f + (int64_t)c * ld + i);
-#pragma unroll
-        for (int p = 0; p < P; ++p) {
-            xp[p] = ldg_stream(prm.x_prev + (int64_t)p * ld + i);
-            xf[p] = ldg_stream(prm.x_f + (int64_t)p * ld + i);
-        }
-        symv<P>(A, xf, rhs);
-
-#pragma unroll 2
-        for (int b = 0; b < prm.n_bands; ++b) {
-            const SolveBandDev& bd = prm.bands[b];
-            const double w = ldg_stream(bd.w + i);
-            const double y = ldg_stream(bd.y + i);
-            double J[P], h0;
-            band_row<P>(bd, ld, i, xp, w, J, h0, round32, domain_bad);
-            double yp = y - h0;                                   // y' = y + J.x_prev - H0
-#pragma unroll
-            for (int p = 0; p < P; ++p) yp = fma(J[p], xp[p], yp);
-            const double wy = w * yp;
-#pragma unroll
-            for (int r = 0; r < P; ++r) {
-                const double wj = w * J[r];
-                rhs[r] = fma(wy, J[r], rhs[r]);
-#pragma unroll
-                for (int q = 0; q <= r; ++q) A[tri(r, q)] = fma(wj, J[q], A[tri(r, q)]);
-            }
-            if (prm.innovations) stg_stream(prm.innovations + (int64_t)b * ld + i, y - h0);
-        }
-
-#pragma unroll
-        for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A[c]);
-
-        double invd[P];
-        const bool ok = chol_factor<P>(A, invd) && !domain_bad;
-        chol_solve<P>(A, invd, rhs);
-#pragma unroll
-        for (int p = 0; p < P; ++p) {
-            const double xn = ok ? rhs[p] : xf[p];
-            rhs[p] = xn;
-            stg_stream(prm.x_out + (int64_t)p * ld + i, xn);
-            const double d = xn - xp[p];
-            ssq = fma(d, d, ssq);
-        }
-        bad = ok ? 0.0 : 1.0;
-
-        if (prm.fwd) {
-            for (int b = 0; b < prm.n_bands; ++b) {
-                const SolveBandDev& bd = prm.bands[b];
-                double J[P], h0;
-                band_row<P>(bd, ld, i, xp, bd.w[i], J, h0, round32, domain_bad);
-                double f = h0;
-#pragma unroll
-                for (int p = 0; p < P; ++p) f = fma(J[p], rhs[p] - xf[p], f);
-                stg_stream(prm.fwd + (int64_t)b * ld + i, f);
-            }
-        }
-    }
-
-    ssq = warp_sum(ssq);
-    bad = warp_sum(bad);
-    if ((threadIdx.x & 31) == 0) {
-        s_part[0][threadIdx.x >> 5] = ssq;
-        s_part[1][threadIdx.x >> 5] = bad;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-        for (int k = 0; k < kSolveThreads / 32; ++k) {
-            s0 += s_part[0][k];
-            s1 += s_part[1][k];
-        }
-        prm.partials[blockIdx.x] = s0;
-        prm.partials[gridDim.x + blockIdx.x] = s1;
-    }
-}
-
-// ---------------------------------------------------------------------------
-// TMA-pipelined variant (the fast path).  The band loop of the kernel above is
-// latency bound: 238 registers leave 8 warps per SM and every band's 3+D loads
-// are consumed immediately.  Here one elected thread streams each band's rows
-// (w, y, H0, J planes: 1 KB each for the CTA's 128 pixels) into a 3-stage
-// shared-memory ring with cp.async.bulk + mbarrier, two bands ahead of the
-// arithmetic, so ~40 KB per CTA are in flight without costing a register.
-// ---------------------------------------------------------------------------
-constexpr int kSolveStages = 3;
-
-template <int P>
 __device__ __forceinline__ void band_row_staged(const SolveBandDev& bd, const double* __restrict__ st, int n_dim_max,
                                                 const double (&xp)[P], double w, double (&J)[P], double& h0,
                                                 bool round32, bool& domain_bad) {
@@ -239,45 +138,49 @@ __device__ __forceinline__ void band_row_staged(const SolveBandDev& bd, const do
     }
 }
 
+// ---------------------------------------------------------------------------
+// Thread-private asynchronous pipeline.  Every thread copies ITS OWN pixel's band
+// values (w, y, H0, J planes: 3+D doubles) into its own shared-memory slots with
+// cp.async (LDGSTS, no registers held while in flight), kAsyncStages-1 bands ahead of the
+// arithmetic, and reads them back after cp.async.wait_group: no thread ever reads
+// what another thread copied, so the band loop needs no barrier of any kind.
+// ---------------------------------------------------------------------------
+#ifndef KAFKA_ASYNC_STAGES
+#define KAFKA_ASYNC_STAGES 3
+#endif
+constexpr int kAsyncStages = KAFKA_ASYNC_STAGES;
+
 template <int P>
 __global__ void __launch_bounds__(kSolveThreads)
-solve_bands_tma_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
+solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     constexpr int L = tri_count(P);
-    extern __shared__ __align__(16) double stages[];               // kSolveStages x (3 + n_dim_max) x 128
-    __shared__ uint64_t bars[kSolveStages];
+    extern __shared__ __align__(16) double stages[];               // kAsyncStages x (3 + n_dim_max) x 128
     __shared__ double s_part[2][kSolveThreads / 32];
     const int64_t tile0 = (int64_t)blockIdx.x * kSolveThreads;
     const int64_t i = tile0 + threadIdx.x;
     const int64_t ld = prm.ld;
-    const uint32_t row_bytes = (uint32_t)(min((int64_t)kSolveThreads, ld - tile0) * sizeof(double));
     const int stage_doubles = (3 + n_dim_max) * kSolveThreads;
+    const bool live = i < prm.n_pix;
+    const bool in_ld = i < ld;                                      // padding lanes inside the arrays still copy
     double ssq = 0.0, bad = 0.0;
 
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int s = 0; s < kSolveStages; ++s) mbar_init(&bars[s], 1);
-    }
-    __syncthreads();
-
-    auto issue = [&](int b) {                                       // one thread: queue band b's rows
-        const SolveBandDev& bd = prm.bands[b];
-        double* st = stages + (b % kSolveStages) * stage_doubles;
-        uint64_t* bar = &bars[b % kSolveStages];
-        const int planes = bd.kind == KAFKA_BAND_ARRAYS ? 3 + bd.n_planes : 2;
-        mbar_expect_tx(bar, row_bytes * planes);
-        tma_bulk_g2s(st, bd.w + tile0, row_bytes, bar);
-        tma_bulk_g2s(st + kSolveThreads, bd.y + tile0, row_bytes, bar);
-        if (bd.kind == KAFKA_BAND_ARRAYS) {
-            tma_bulk_g2s(st + 2 * kSolveThreads, bd.h0 + tile0, row_bytes, bar);
-            for (int d = 0; d < bd.n_planes; ++d)
-                tma_bulk_g2s(st + (3 + d) * kSolveThreads, bd.jac + (int64_t)d * ld + tile0, row_bytes, bar);
+    auto issue = [&](int b) {
+        if (b < prm.n_bands && in_ld) {
+            const SolveBandDev& bd = prm.bands[b];
+            double* st = stages + (b % kAsyncStages) * stage_doubles + threadIdx.x;
+            cp_async8(st, bd.w + i);
+            cp_async8(st + kSolveThreads, bd.y + i);
+            if (bd.kind == KAFKA_BAND_ARRAYS) {
+                cp_async8(st + 2 * kSolveThreads, bd.h0 + i);
+                for (int d = 0; d < bd.n_planes; ++d) cp_async8(st + (3 + d) * kSolveThreads, bd.jac + (int64_t)d * ld + i);
+            }
         }
+        cp_async_commit();                                          // one group per band, even when empty
     };
-    if (threadIdx.x == 0)
-        for (int b = 0; b < min(kSolveStages, prm.n_bands); ++b) issue(b);
+#pragma unroll
+    for (int b = 0; b < kAsyncStages - 1; ++b) issue(b);
 
-    const bool live = i < prm.n_pix;
-    const int64_t il = live ? i : tile0;                            // padding lanes read a valid pixel, write nothing
+    const int64_t il = live ? i : tile0;
     double A[L], rhs[P], xp[P], xf[P];
     const bool bcast = (prm.flags & KAFKA_PRIOR_BROADCAST) != 0;
     const bool round32 = (prm.flags & KAFKA_ROUND_F32) != 0;
@@ -292,11 +195,12 @@ solve_bands_tma_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     symv<P>(A, xf, rhs);
 
     for (int b = 0; b < prm.n_bands; ++b) {
+        issue(b + kAsyncStages - 1);
+        cp_async_wait<kAsyncStages - 1>();                          // this thread's copies of band b have landed
         const SolveBandDev& bd = prm.bands[b];
-        const double* st = stages + (b % kSolveStages) * stage_doubles;
-        mbar_wait(&bars[b % kSolveStages], (uint32_t)((b / kSolveStages) & 1));
-        const double w = st[threadIdx.x];
-        const double y = st[kSolveThreads + threadIdx.x];
+        const double* st = stages + (b % kAsyncStages) * stage_doubles;
+        const double w = in_ld ? st[threadIdx.x] : 0.0;
+        const double y = in_ld ? st[kSolveThreads + threadIdx.x] : 0.0;
         double J[P], h0;
         band_row_staged<P>(bd, st, n_dim_max, xp, w, J, h0, round32, domain_bad);
         double yp = y - h0;
@@ -311,9 +215,8 @@ solve_bands_tma_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
             for (int q = 0; q <= r; ++q) A[tri(r, q)] = fma(wj, J[q], A[tri(r, q)]);
         }
         if (prm.innovations && live) stg_stream(prm.innovations + (int64_t)b * ld + i, y - h0);
-        __syncthreads();                                            // every thread has consumed this stage
-        if (threadIdx.x == 0 && b + kSolveStages < prm.n_bands) issue(b + kSolveStages);
     }
+    cp_async_wait<0>();
 
     if (live) {
 #pragma unroll
@@ -514,39 +417,22 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
     prm.n_bands = n_bands;
     prm.flags = flags;
     const unsigned grid = (unsigned)((n_pix + kSolveThreads - 1) / kSolveThreads);
-    // TMA bulk copies need 16-byte aligned rows whose padded tail stays inside the arrays
-    bool tma_ok = n_bands > 0 && (ld % 2) == 0;
     int n_dim_max = 0;
-    for (int b = 0; b < n_bands && tma_ok; ++b) {
-        const SolveBandDev& d = prm.bands[b];
-        auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
-        tma_ok = al(d.w) && al(d.y);
-        if (d.kind == KAFKA_BAND_ARRAYS) {
-            tma_ok = tma_ok && al(d.h0) && al(d.jac);
-            n_dim_max = d.n_planes > n_dim_max ? d.n_planes : n_dim_max;
-        }
-    }
-    if (getenv("KAFKA_SOLVE_NO_TMA")) tma_ok = false;
+    for (int b = 0; b < n_bands; ++b)
+        if (prm.bands[b].kind == KAFKA_BAND_ARRAYS && prm.bands[b].n_planes > n_dim_max) n_dim_max = prm.bands[b].n_planes;
+    const size_t smem = (size_t)kAsyncStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
     int rc = KAFKA_E_UNSUPPORTED;
-    if (tma_ok) {
-        const size_t smem = (size_t)kSolveStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
-        KAFKA_DISPATCH_P(n_params, {
-            auto kern = solve_bands_tma_kernel<kP>;
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) {
-                set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
-                rc = (int)e;
-            } else {
-                kern<<<grid, kSolveThreads, smem, s>>>(prm, n_dim_max);
-                rc = launch_status("solve_bands_tma_kernel");
-            }
-        });
-    } else {
-        KAFKA_DISPATCH_P(n_params, {
-            solve_bands_kernel<kP><<<grid, kSolveThreads, 0, s>>>(prm);
+    KAFKA_DISPATCH_P(n_params, {
+        auto kern = solve_bands_kernel<kP>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) {
+            set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+            rc = (int)e;
+        } else {
+            kern<<<grid, kSolveThreads, smem, s>>>(prm, n_dim_max);
             rc = launch_status("solve_bands_kernel");
-        });
-    }
+        }
+    });
     if (rc != 0) return rc;
     reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
     return launch_status("reduce_partials_kernel");
