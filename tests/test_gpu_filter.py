@@ -352,3 +352,80 @@ def test_run_with_prefetch_and_overlapped_output_matches_plain_run():
     # and equal to the reference-checked interleaved output
     last_x = res[True][0][-1][1]
     assert np.allclose(last_x[6][mask], g["out_x"][-1][6::P], rtol=2e-3, atol=1e-5)
+
+
+def test_edge_cases_empty_mask_all_unobserved_and_maximum_sizes():
+    """Empty state mask; a date where no pixel is observed; and the largest
+    supported problem (16 parameters, 16 bands, 16-input emulators)."""
+    # --- empty state mask: nothing to do, nothing breaks
+    mask = np.zeros((5, 6), dtype=bool)
+    kf = kb.LinearKalman(None, None, mask, kb.create_linear_observation_operator, syn.TIP_PARAMETERS, prior=None)
+    assert kf.n_state_elems == 0
+    band = syn.BandData(np.zeros(mask.shape), np.ones(mask.shape), np.ones(mask.shape, dtype=bool), None,
+                        kb.LinearBandOperator(np.eye(7)[6]))
+    x, _, A, innov = kf.do_all_bands(None, [band], np.zeros(0), None, BlockDiag.from_blocks(np.zeros((0, 7, 7)), gu.DEV))
+    assert len(x) == 0 and np.asarray(x).size == 0 and kf.last_iterations[-1] == 2
+    # --- nobody observed: analysis == forecast, A == P_f^-1, two iterations (min_iterations)
+    rng = np.random.default_rng(2)
+    mask = rng.random((9, 13)) < 0.7
+    N = int(mask.sum())
+    P = 7
+    _, _, inv = kb.tip_prior()
+    kf = kb.LinearKalman(None, None, mask, kb.create_linear_observation_operator, syn.TIP_PARAMETERS, prior=None)
+    none_obs = np.zeros(mask.shape, dtype=bool)
+    band = syn.BandData(np.zeros(mask.shape), syn.inverse_variance_matrix(np.full(mask.shape, np.inf)), none_obs, None,
+                        kb.LinearBandOperator(np.eye(7)[6]))
+    x0 = np.tile(syn.TIP_MEAN, N) + 0.01 * rng.standard_normal(N * P)
+    x, _, A, innov = kf.do_all_bands(None, [band], x0, None, BlockDiag.from_block(inv.astype(np.float64), N, gu.DEV))
+    assert np.allclose(np.asarray(x), x0, rtol=1e-12) and kf.last_iterations[-1] == 2
+    assert np.array_equal(A.blocks()[3], inv.astype(np.float64)) and not np.asarray(innov).any()
+    # --- maximum sizes
+    P = B = D = 16
+    mean = rng.uniform(0.5, 1.5, P)
+    sigma = rng.uniform(0.05, 0.2, P)
+    gps = [syn.make_emulator(rng, mean, sigma, n_train=40, cls=GaussianProcess) for _ in range(B)]
+    N = int(mask.sum())
+    x_true = mean + sigma * rng.standard_normal((N, P))
+    date = dt.datetime(2017, 7, 3)
+    obs = syn.SyntheticObservations(mask, [date], gps, x_true, lambda gp, X: gp.predict(X, do_unc=False)[0], rng)
+    names = ["p%d" % k for k in range(P)]
+    kf = kb.LinearKalman(obs, None, mask, kb.create_prosail_observation_operator, names, prior=None)
+    blocks = np.repeat(np.diag(1.0 / sigma ** 2)[None], N, axis=0)
+    data = [obs.get_band_data(date, b) for b in range(B)]
+    x, _, A, _ = kf.do_all_bands(date, data, np.tile(mean, N), None, BlockDiag.from_blocks(blocks, gu.DEV))
+    bands = gio.compacted_bands(obs, mask)[date]
+    ops = [(lambda xp, gp=gp, m=bands[b][2]: kc.emulator_operator(gp, xp, P, m)) for b, gp in enumerate(gps)]
+    xo, Ao, _, n, _ = kc.do_all_bands(ops, [b_[0] for b_ in bands], [b_[1] for b_ in bands], [b_[2] for b_ in bands],
+                                      np.tile(mean, N), blocks, P)
+    assert kf.last_iterations[-1] == n
+    assert np.max(np.abs(np.asarray(x) - xo) / np.maximum(np.abs(xo), 1e-3)) < TOL
+    idx = np.arange(P)
+    assert np.max(gu.rel(A.blocks()[:, idx, idx], Ao[:, idx, idx])) < TOL            # posterior precision diagonal
+    assert np.max(np.abs(A.blocks() - Ao)) < TOL * np.abs(Ao).max()                  # whole block, on its own scale
+
+
+def test_legacy_band_by_band_assimilate():
+    """assimilate (linear_kf.py:325-354): bands one after the other, each band's
+    analysis the next band's forecast, Hessian correction applied per band."""
+    g = gio.load("run_tip")
+    mask = g["mask"]
+    P = 7
+    N = int(mask.sum())
+    gps = gio.emulators(g, syn.EmulatorData)
+    ogps = gio.emulators(g, GaussianProcess)
+    obs = gio.FixtureObservations(g, gps)
+    date = obs.dates[0]
+    bands = gio.compacted_bands(obs, mask)[date]
+    mappers = [g["mapper_0"], g["mapper_1"]]
+    blocks = np.repeat(g["prior_inv_block"][None].astype(np.float64), N, axis=0)
+    kf = kb.LinearKalman(obs, None, mask, kb.create_nonlinear_observation_operator, syn.TIP_PARAMETERS, prior=None)
+    x, _, A = kf.assimilate([date], g["x0"], None, BlockDiag.from_blocks(blocks, gu.DEV))
+    assert kf.previous_state.timestamp == date
+    xo, Ao = g["x0"], blocks
+    for b in range(2):
+        op = [lambda xp, b=b: kc.emulator_operator(ogps[b], xp, P, bands[b][2], state_mapper=mappers[b])]
+        xn, An, innov, n, _ = kc.do_all_bands(op, [bands[b][0]], [bands[b][1]], [bands[b][2]], xo, Ao, P, min_iterations=1)
+        corr = kc.hessian_correction(ogps[b], xn, bands[b][1], innov, bands[b][2], P, mappers[b])
+        xo, Ao = xn, An - corr
+    assert np.max(np.abs(np.asarray(x) - xo) / np.maximum(np.abs(xo), 1e-3)) < TOL
+    assert np.max(np.abs(A.blocks() - Ao)) < TOL * np.abs(Ao).max()
