@@ -18,15 +18,12 @@ CSRC = os.path.join(ROOT, "kafka_inferenceengine_b200", "csrc")
 OUT = os.path.join(HERE, "variants")
 VARIANTS = {
     "default": [],
+    "tab64": ["-DKAFKA_EXP_LOG2N=6"],
+    "f2i": ["-DKAFKA_EXP_F2I=1"],
     "u1": ["-DKAFKA_GP_UNROLL=1"],
-    "u3": ["-DKAFKA_GP_UNROLL=3"],
     "u4": ["-DKAFKA_GP_UNROLL=4"],
-    "u4_mb2": ["-DKAFKA_GP_UNROLL=4", "-DKAFKA_GP_MINBLOCKS=2"],
-    "u2_mb2": ["-DKAFKA_GP_MINBLOCKS=2"],
-    "u2_mb4": ["-DKAFKA_GP_MINBLOCKS=4"],
     "ppt1_u4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_UNROLL=4"],
-    "ppt1_u4_mb5": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_UNROLL=4", "-DKAFKA_GP_MINBLOCKS=5"],
-    "t256_mb1": ["-DKAFKA_GP_THREADS=256"],
+    "t256": ["-DKAFKA_GP_THREADS=256"],
 }
 
 
@@ -53,7 +50,6 @@ def run():
     n = 4_000_000
     rng = np.random.default_rng(1)
     gps = [syn.make_emulator(rng, syn.SAIL_MEAN, syn.SAIL_SIGMA, n_train=250) for _ in range(B)]
-    tabs = [torch.from_numpy(_lib.gp_pack(g.inputs, g.theta, g.invQt)).to(dev) for g in gps]
     gen = torch.Generator(device=dev).manual_seed(5)
     x = torch.from_numpy(syn.SAIL_MEAN).to(dev)[:, None] + torch.from_numpy(syn.SAIL_SIGMA).to(dev)[:, None] * \
         torch.randn((P, n), generator=gen, dtype=torch.float64, device=dev)
@@ -65,6 +61,15 @@ def run():
         if not os.path.exists(path):
             continue
         lib = C.CDLL(path)
+        # every variant packs its own tables (the exponent scale is a compile-time constant)
+        lib.kafka_gp_table_doubles.restype = C.c_int64
+        tabs = []
+        for g in gps:
+            host = np.empty(lib.kafka_gp_table_doubles(250, P), dtype=np.float64)
+            rc = lib.kafka_gp_pack_host(C.c_void_p(g.inputs.ctypes.data), C.c_void_p(g.theta.ctypes.data),
+                                        C.c_void_p(g.invQt.ctypes.data), 250, P, C.c_void_p(host.ctypes.data))
+            assert rc == 0
+            tabs.append(torch.from_numpy(host).to(dev))
         fn = lib.kafka_gp_linearize
         fn.restype = C.c_int
         fn.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.POINTER(_lib.GpBand), C.c_int, C.c_void_p, C.c_void_p,

@@ -9,13 +9,13 @@
 //             e_j = ln s_f - 0.5 sum_d theta_d X'_jd^2
 //     w_j   = k_j alpha_j,   mean = sum_j w_j,   G_d = sum_j w_j zh_jd
 //     dmean/dx_d = G_d - theta_d x'_d mean
-// The table stores zh and e pre-multiplied by L = 64/ln2, so the dot product IS the
-// base-2^(1/64) exponent: k = rint(a), r = a - k is exact, 2^(k/64) comes from a
-// 64-entry table and exp(r ln2/64) from a degree-5 polynomial (|r| <= 1/2, truncation
-// 3.5e-17).  The per-pixel factor exp(-0.5 sum theta x'^2) is pulled out of the loop and
+// The table stores zh and e pre-multiplied by L = 256/ln2, so the dot product IS the
+// base-2^(1/256) exponent: k = rint(a), r = a - k is exact, 2^(k/256) comes from a
+// 256-entry table and exp(r ln2/256) from a degree-4 polynomial (|r| <= 1/2, truncation
+// 3.8e-17).  The per-pixel factor exp(-0.5 sum theta x'^2) is pulled out of the loop and
 // applied once at the end (a warp keeps it inside the exponent when one of its pixels is so
 // far from the centre that the un-shifted exponent could overflow).  Per (pixel, band,
-// training point): 2D FMAs + ~11 fp64 ops, i.e. 31 fp64-pipe instructions at D=10 against
+// training point): 2D FMAs + ~10 fp64 ops, i.e. 30 fp64-pipe instructions at D=10 against
 // the 5D+28 = 78 flops of the textbook form.  The training table (T rows of {zh[D], e,
 // alpha}) is staged once per CTA in shared memory by a TMA bulk copy and then read as
 // warp-wide broadcasts.  The kernel is bound by the fp64 pipe, not by HBM.
@@ -26,8 +26,22 @@
 
 namespace kafka {
 
-__constant__ double c_exp2_tab[64] = {
+// exponent granularity: 2^(1/64) (64-entry table + degree-5 polynomial) or 2^(1/256)
+// (256-entry table + degree-4 polynomial, one DFMA fewer per evaluation)
+#ifndef KAFKA_EXP_LOG2N
+#define KAFKA_EXP_LOG2N 8   // measured 4.5 % faster than 6 on B200 (benchmarks/gp_variants.py)
+#endif
+#ifndef KAFKA_EXP_F2I
+#define KAFKA_EXP_F2I 0
+#endif
+constexpr int kExpLog2N = KAFKA_EXP_LOG2N;
+constexpr int kExpN = 1 << kExpLog2N;
+__constant__ double c_exp2_tab[kExpN] = {
+#if KAFKA_EXP_LOG2N == 6
 #include "exp_table.inc"
+#else
+#include "exp_table256.inc"
+#endif
 };
 
 // ---- table layout -----------------------------------------------------------
@@ -35,35 +49,50 @@ __host__ __device__ constexpr int dpad(int D) { return (D + 1) & ~1; }
 __host__ __device__ constexpr int tab_hdr(int D) { return 2 * dpad(D) + 2; }   // theta_e, centre, s_f, nugget
 __host__ __device__ constexpr int tab_row(int D) { return dpad(D) + 2; }       // zh[DP], e, alpha
 
-// ---- exp in base 2^(1/64): argument already scaled by L = 64/ln2 ------------------
+// ---- exp in base 2^(1/N): argument already scaled by L = N/ln2 ----------------------
+#if KAFKA_EXP_LOG2N == 6
 constexpr double kL = 9.23324826168936567683e+01;        // 64/ln2
 constexpr double kInvL = 1.08304246962491450973e-02;     // ln2/64
-constexpr double kFarShift = 600.0 * kL;                 // beyond this the per-pixel factor stays in the exponent
 constexpr uint32_t kHiUnder = 0x40efeb6cu;               // high word of 708 L
-constexpr uint32_t kHiOver = 0x40eff6f7u;                // high word of 709 L
-
 // Polynomial coefficients live in constant memory so that the DFMAs take them as
 // c[bank][offset] operands instead of re-materialising 64-bit immediates in the loop.
 __constant__ double c_exp_poly[6] = {1.24178437017169252822e-12, 5.73285168864040188714e-10,
                                       2.11731371554647762752e-07, 5.86490495505616996649e-05,
                                       1.08304246962491450973e-02, 6755399441055744.0 /* 1.5 * 2^52 */};
+#else
+constexpr double kL = 3.69329930467574627073e+02;        // 256/ln2
+constexpr double kInvL = 2.70760617406228627432e-03;     // ln2/256
+constexpr uint32_t kHiUnder = 0x410feb6cu;               // high word of 708 L
+__constant__ double c_exp_poly[6] = {0.0, 2.23939519087515698716e-12, 3.30830268054137129301e-09,
+                                      3.66556559691010622906e-06, 2.70760617406228627432e-03,
+                                      6755399441055744.0 /* 1.5 * 2^52 */};
+#endif
+constexpr double kFarShift = 600.0 * kL;                 // beyond this the per-pixel factor stays in the exponent
 
-// exp(a / L) for finite a < 709 L.  fp64-pipe cost: 3 adds + 5 FMAs + 1 mul; the only range
+// exp(a / L) for finite a < 709 L.  fp64-pipe cost: 3 adds + 5 (4) FMAs + 1 mul; the only range
 // test is one unsigned compare on the high word (exactly 0 below -708 L), so the function is
 // branch-free and several evaluations interleave.  |rel err| < 3e-16.  NaN / +inf / overflow
 // are NOT handled here: callers check their inputs once per pixel, outside the hot loop.
-__device__ __forceinline__ double exp_scaled(double a, const double* __restrict__ tab64) {
+__device__ __forceinline__ double exp_scaled(double a, const double* __restrict__ tab) {
+#if KAFKA_EXP_F2I
+    const int k = __double2int_rn(a);
+    const double r = a - (double)k;                      // exact, |r| <= 1/2
+#else
     const double t = a + c_exp_poly[5];
     const int k = __double2loint(t);
     const double r = a - (t - c_exp_poly[5]);            // exact, |r| <= 1/2
+#endif
+#if KAFKA_EXP_LOG2N == 6
     double p = fma(r, c_exp_poly[0], c_exp_poly[1]);
     p = fma(p, r, c_exp_poly[2]);
+#else
+    double p = fma(r, c_exp_poly[1], c_exp_poly[2]);
+#endif
     p = fma(p, r, c_exp_poly[3]);
     p = fma(p, r, c_exp_poly[4]);
     p = fma(p, r, 1.0);
-    const double v = tab64[k & 63] * p;
-    // (uint32)hi(a) >= 0x80000000 + hi(708 L)  <=>  a <= -708 L (or -inf)
-    const int hi_n = __double2hiint(v) + ((k >> 6) << 20);
+    const double v = tab[k & (kExpN - 1)] * p;
+    const int hi_n = __double2hiint(v) + ((k >> kExpLog2N) << 20);
     const int lo_n = __double2loint(v);
     int hi, lo;
     // selp keeps this branch-free (the compiler otherwise jumps around the exponent insert)
@@ -147,7 +176,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     extern __shared__ __align__(16) double smem[];
     __shared__ uint64_t bar;
-    __shared__ double s_exp[64];
+    __shared__ double s_exp[kExpN];
 
     // band is the FAST grid index: the CTAs of all bands of one pixel tile run together, so
     // the tile's state is fetched from HBM once and served to the other bands by L2
@@ -158,7 +187,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     const uint32_t bytes = (uint32_t)((HDR + T * RS) * sizeof(double));
 
     if (threadIdx.x == 0) mbar_init(&bar, 1);
-    for (int k = threadIdx.x; k < 64; k += kGpThreads) s_exp[k] = c_exp2_tab[k];
+    for (int k = threadIdx.x; k < kExpN; k += kGpThreads) s_exp[k] = c_exp2_tab[k];
     __syncthreads();
     if (threadIdx.x == 0) {
         mbar_expect_tx(&bar, bytes);
@@ -259,10 +288,10 @@ gp_hessian_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, con
                   double* __restrict__ hess) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D), L = tri_count(D);
     extern __shared__ __align__(16) double smem[];
-    __shared__ double s_exp[64];
+    __shared__ double s_exp[kExpN];
     const int total = HDR + T * RS;
     for (int k = threadIdx.x; k < total; k += kGpThreads) smem[k] = table[k];
-    if (threadIdx.x < 64) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = c_exp2_tab[k];
     __syncthreads();
     int64_t i = (int64_t)blockIdx.x * kGpThreads + threadIdx.x;
     if (i >= n_pts) return;
@@ -328,8 +357,8 @@ __global__ void __launch_bounds__(128)
 gp_hessian_correction_kernel(const __grid_constant__ GpHessCorrParams prm) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D), L = tri_count(D);
     extern __shared__ __align__(16) double smem[];
-    __shared__ double s_exp[64];
-    if (threadIdx.x < 64) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    __shared__ double s_exp[kExpN];
+    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = c_exp2_tab[k];
     const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
     const bool in = i < prm.n_pix;
     const int LP = tri_count(prm.n_params);
@@ -402,8 +431,8 @@ __global__ void __launch_bounds__(128)
 gp_variance_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, const double* __restrict__ table, int T,
                    int D, const double* __restrict__ inv_q, double* __restrict__ var) {
     extern __shared__ double kbuf[];             // [4 warps][T]
-    __shared__ double s_exp[64];
-    if (threadIdx.x < 64) s_exp[threadIdx.x] = c_exp2_tab[threadIdx.x];
+    __shared__ double s_exp[kExpN];
+    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = c_exp2_tab[k];
     __syncthreads();
     const int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;

@@ -79,7 +79,7 @@ def test_gp_pack_host_matches_numpy():
         assert tab[2 * DP] == pytest.approx(e[D], rel=1e-15)
         rows = tab[2 * DP + 2:].reshape(T, DP + 2)
         Xc = X - tab[DP:DP + D]
-        L = 64.0 / np.log(2.0)                       # rows are in units of ln2/64
+        L = 256.0 / np.log(2.0)                      # rows are in units of ln2/256
         assert np.allclose(rows[:, :D], L * e[:D] * Xc, rtol=4e-16, atol=0)
         assert np.allclose(rows[:, DP], L * (theta[D] - 0.5 * (e[:D] * Xc * Xc).sum(axis=1)), rtol=1e-14)
         assert np.array_equal(rows[:, DP + 1], alpha)
