@@ -51,6 +51,9 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=131072, help="pixels of the workload timed on the host")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="c4shard", choices=["c4shard", "c2", "c3", "c5"],
+                    help="c4shard (default, the bench line): 1/8 of the full S2 tile per GPU; the others are the "
+                         "remaining BASELINE.json configs, run on request for the record (single GPU)")
     return ap.parse_args()
 
 
@@ -312,10 +315,177 @@ def workload_config(args, note=None):
 
 
 # --------------------------------------------------------------------------
+# --------------------------------------------------------------------------
+# the other BASELINE.json configurations (on request; the default bench line is c4shard)
+# --------------------------------------------------------------------------
+def run_other_workload(args):
+    import torch
+    import kafka_inferenceengine_b200 as kb
+    from kafka_inferenceengine_b200 import _lib
+    from kafka_inferenceengine_b200 import synthetic as syn
+    from kafka_inferenceengine_b200.device import BlockDiag, DeviceVector, padded, tri_count
+    torch.cuda.set_device(0)
+    device = torch.device("cuda", 0)
+    base = dt.datetime(2017, 1, 1)
+
+    def timed(fn, reps, warm):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    if args.workload == "c2":
+        # configs[1]: Barrax mask (13 027 px), 10-band PROSAIL emulators, 20 dates, one run() call
+        import zlib  # noqa: F401
+        g = np.load(os.path.join(ROOT, "tests", "golden", "barrax_mask.npz"))
+        ny, nx = g["shape"]
+        mask = np.unpackbits(g["bits"])[:ny * nx].astype(bool).reshape(ny, nx)
+        N = int(mask.sum())
+        gps = make_emulators()
+        rho, inv, msk = synth_on_device(gps, ny * nx, 7, device)
+        n_dates = 20
+        dates = [base + dt.timedelta(days=2 * d, hours=12) for d in range(n_dates)]
+        obs = HostObservations(dates, gps, rho, inv, msk, (ny, nx))
+        inv_block = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
+        prior = syn.BroadcastPrior(syn.SAIL_MEAN, inv_block, N, lambda blk, n: BlockDiag.from_block(blk, n, device),
+                                   lambda m, n: DeviceVector.broadcast(m, n, device))
+        from kafka_inferenceengine_b200.output import RasterOutput
+        out = RasterOutput(syn.S2_PARAMETERS)
+        kf = kb.LinearKalman(obs, out, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS,
+                             state_propagation=None, prior=prior, linear=False, device=device)
+        out.pixels = kf.pixels
+        kf.set_trajectory_model()
+        kf.set_trajectory_uncertainty(0.0)
+        x0, P0 = prior.process_prior(None)
+        grid = [base + dt.timedelta(days=2 * d) for d in range(n_dates + 1)]
+        kf.run(grid, x0, None, P0, iter_obs_op=True)            # warm-up
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            kf.run(grid, x0, None, P0, iter_obs_op=True)
+        torch.cuda.synchronize()
+        ms = 1e3 * (time.perf_counter() - t0) / args.steps
+        print(json.dumps({"workload": "c2: Barrax mask 13027 px, P=10, B=10, T=250, 20 dates, LinearKalman.run with host "
+                                      "rasters, end to end", "metric": "pixel-dates/sec",
+                          "value": N * n_dates / (ms * 1e-3), "ms_per_run": ms, "ms_per_date": ms / n_dates,
+                          "iterations": kf.last_iterations[-n_dates:], "n_gpus": 1}))
+    elif args.workload == "c3":
+        # configs[2]: MODIS tile 2400 x 2400, 7-param TIP state, 2 bands through state mappers (D=4, T=500),
+        # daily steps, an observation every 8th day, propagate_information_filter_LAI with Q[6::7] = 0.04
+        ny = nx = 2400
+        N = ny * nx
+        rng = np.random.default_rng(3)
+        mappers = [np.array([0, 1, 6, 2]), np.array([3, 4, 6, 5])]
+        gps = [syn.make_emulator(rng, syn.TIP_MEAN[m], syn.TIP_SIGMA[m], n_train=500, w_scale=0.15) for m in mappers]
+        from kafka_inferenceengine_b200.inference.utils import emulator_table, linearize_bands
+        gen = torch.Generator(device=device).manual_seed(11)
+        xt = DeviceVector.empty(N, 7, device)
+        xt.data.copy_(torch.from_numpy(syn.TIP_MEAN).to(device)[:, None] + 0.5 * torch.from_numpy(syn.TIP_SIGMA).to(device)[:, None]
+                      * torch.randn(xt.data.shape, generator=gen, dtype=torch.float64, device=device))
+        rho = torch.empty((2, xt.ld), dtype=torch.float64, device=device)
+        linearize_bands(xt, [(emulator_table(g_, device), m) for g_, m in zip(gps, mappers)], None, False, h0=rho,
+                        want_jac=False)
+        rho = rho[:, :N].contiguous()
+        sig = torch.clamp(0.05 * rho.abs(), min=2.5e-3)
+        rho = rho + sig * torch.randn(rho.shape, generator=gen, dtype=torch.float64, device=device)
+        msk = torch.rand(rho.shape, generator=gen, device=device) < 0.9
+        inv = torch.where(msk, 1.0 / sig ** 2, torch.full_like(rho, float("inf")))
+        n_steps = 32
+        dates = [base + dt.timedelta(days=d, hours=12) for d in range(0, n_steps, 8)]
+        obs = DeviceObservationsGeneric(dates, gps, rho, inv, msk.to(torch.uint8), (ny, nx))
+        kf = kb.LinearKalman(obs, NullOutput(), np.ones((ny, nx), dtype=bool), kb.create_nonlinear_observation_operator,
+                             syn.TIP_PARAMETERS, state_propagation=kb.propagate_information_filter_LAI, prior=None,
+                             device=device)
+        kf.set_trajectory_model()
+        q = DeviceVector.empty(N, 7, device)
+        q.data.zero_()
+        q.data[6] = 0.04
+        kf.trajectory_uncertainty = kb.DiagonalMatrix(q, 7, device)
+        mean, prior_inv = kb.tip_prior_full({"n_pixels": N})
+        grid = [base + dt.timedelta(days=d) for d in range(n_steps + 1)]
+        kf.run(grid[:9], mean, None, prior_inv, iter_obs_op=True)          # warm-up
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        kf.last_iterations = []
+        kf.run(grid, mean, None, prior_inv, iter_obs_op=True)
+        torch.cuda.synchronize()
+        ms = 1e3 * (time.perf_counter() - t0)
+        print(json.dumps({"workload": "c3: MODIS tile 2400x2400 (5.76 M px), TIP P=7, B=2 (D=4, T=500), %d daily steps, "
+                                      "observations every 8th day, LAI propagator; device-resident rasters" % n_steps,
+                          "metric": "pixel-steps/sec", "value": N * n_steps / (ms * 1e-3), "ms_per_step": ms / n_steps,
+                          "pixel_dates_per_s": N * len(dates) / (ms * 1e-3), "iterations": kf.last_iterations,
+                          "n_gpus": 1}))
+    else:
+        # configs[4]: batched update with SUPPLIED Jacobians, n_params x bands sweep at 4 M pixels
+        lib = _lib.get_lib()
+        n = 4_000_000
+        ld = padded(n)
+        gen = torch.Generator(device=device).manual_seed(3)
+        rows = []
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
+            os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        hbm = float(peaks.get("hbm_gbs", 6650.0))
+        for Pn in (2, 4, 7, 10, 12, 16):
+            for Bn in (1, 4, 10, 13):
+                Lp = tri_count(Pn)
+                rnd = lambda r: torch.randn((r, ld), generator=gen, dtype=torch.float64, device=device)
+                J, h0, y = [rnd(Pn) for _ in range(Bn)], [rnd(1) for _ in range(Bn)], [rnd(1) for _ in range(Bn)]
+                w = [torch.full((1, ld), 400.0, dtype=torch.float64, device=device) for _ in range(Bn)]
+                xp, xf = rnd(Pn), rnd(Pn)
+                pinv = torch.zeros((Lp, ld), dtype=torch.float64, device=device)
+                r_, c_ = np.tril_indices(Pn)
+                for k in range(Lp):
+                    if r_[k] == c_[k]:
+                        pinv[k] = 4.0
+                arr = (_lib.SolveBand * Bn)()
+                for b in range(Bn):
+                    arr[b].kind, arr[b].n_dim = _lib.BAND_ARRAYS, Pn
+                    for k in range(Pn):
+                        arr[b].mapper[k] = k
+                    arr[b].jac, arr[b].h0, arr[b].y, arr[b].w = J[b].data_ptr(), h0[b].data_ptr(), y[b].data_ptr(), w[b].data_ptr()
+                xo, ao = torch.empty_like(xp), torch.empty_like(pinv)
+                n2 = torch.zeros(1, dtype=torch.float64, device=device)
+                nb = torch.zeros(1, dtype=torch.int32, device=device)
+                scratch = torch.empty(int(lib.kafka_solve_scratch_doubles(n)), dtype=torch.float64, device=device)
+
+                def call():
+                    _lib.check(lib.kafka_solve_bands(n, ld, Pn, arr, Bn, _lib.ptr(xp), _lib.ptr(xf), _lib.ptr(pinv),
+                                                     _lib.ptr(xo), _lib.ptr(ao), None, None, _lib.ptr(n2), _lib.ptr(nb),
+                                                     _lib.ptr(scratch), 0, _lib.stream_ptr()), "kafka_solve_bands")
+                ms = timed(call, 5, 2)
+                bytes_pp = 16 * Pn + 8 * Pn * (Pn + 1) + 8 * Pn + Bn * 8 * (3 + Pn)     # x_f,x_prev,x ; Pinv in + A out ; bands
+                rows.append({"n_params": Pn, "n_bands": Bn, "ms": ms, "Mpx_per_s": n / ms / 1e3,
+                             "GBs": n * bytes_pp / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": n * bytes_pp / (ms * 1e-3) / 1e9 / hbm})
+                del J, h0, y, w, xp, xf, pinv, xo, ao
+        print(json.dumps({"workload": "c5: batched update with supplied Jacobians, 4 M px, per-pixel prior blocks",
+                          "metric": "pixels/sec", "rows": rows, "n_gpus": 1}))
+
+
+class DeviceObservationsGeneric(object):
+    def __init__(self, dates, gps, rho, inv, mask, shape):
+        from kafka_inferenceengine_b200 import synthetic as syn
+        self.dates = list(dates)
+        nb = len(gps)
+        self.bands_per_observation = {d: nb for d in self.dates}
+        self._bands = [syn.BandData(rho[b].view(shape), inv[b].view(shape), mask[b].view(shape), {"band": b}, gps[b])
+                       for b in range(nb)]
+
+    def get_band_data(self, date, band):
+        return self._bands[band]
+
+
 def main():
     args = parse()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload != "c4shard":
+        return run_other_workload(args)
 
     import torch
     import torch.distributed as dist

@@ -153,14 +153,22 @@ class ObservationStager(object):
         holders = [None if b in raw else _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
                    for b, d in enumerate(current_data)]
         futures = []
+        small = n < (1 << 18)                          # tiny rasters: the pool's hand-over costs more than the copy
         for b, d in enumerate(current_data):
-            if b in raw:
+            if small:
+                futures.append([])
+            elif b in raw:
                 futures.append([self._pool.submit(self._stage_raw, slot, b, d, raw[b], n * k // parts,
                                                   n * (k + 1) // parts) for k in range(parts)])
             else:
                 futures.append([self._pool.submit(self._stage_part, slot, b, holders[b], n * k // parts,
                                                   n * (k + 1) // parts) for k in range(parts)])
         for b in range(nb):
+            if small:
+                if b in raw:
+                    self._stage_raw(slot, b, current_data[b], raw[b], 0, n)
+                else:
+                    self._stage_part(slot, b, holders[b], 0, n)
             for f in futures[b]:
                 f.result()
             with torch.cuda.stream(self._copy_stream):
