@@ -268,7 +268,8 @@ def run_reference(args):
     procs = max(1, min(cores, 32))
     gps = make_emulators()
     dev = torch.device("cuda", 0) if torch.cuda.is_available() else None
-    n_sample = procs * 4 * 8192
+    n_sample = procs * 4 * 8192 if args.cpu_sample == 131072 else max(8192, args.cpu_sample // 8192 * 8192)
+    procs = min(procs, n_sample // 8192)
     if dev is not None:
         rho, inv, mask = synth_on_device(gps, n_sample, 99, dev)
     else:                                   # no GPU: numpy forward model from the oracle

@@ -1,7 +1,6 @@
 """Device-side plumbing shared by ``LinearKalman`` and the solver functions:
 observation upload + compaction gather, band descriptors and the call into the
 fused build+solve kernel.  No arithmetic happens here."""
-import ctypes as C
 import os
 
 import numpy as np
@@ -9,7 +8,7 @@ import scipy.sparse as sp
 import torch
 
 from . import _lib
-from .device import BlockDiag, DeviceBands, DeviceVector, PixelIndex, padded, tri_count
+from .device import padded
 
 
 class BandBuffers(object):

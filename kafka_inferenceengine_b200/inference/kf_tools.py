@@ -7,7 +7,6 @@ matrices) or the device containers this package returns (``DeviceVector``,
 ``BlockDiag``); outputs are always device containers, which quack like the
 reference's return values (``np.asarray``, ``.diagonal()``, ``.dot``, ``+``, ``*1.``).
 """
-import ctypes as C
 import logging
 
 import numpy as np
@@ -15,7 +14,7 @@ import scipy.sparse as sp
 import torch
 
 from .. import _lib
-from ..device import BlockDiag, DeviceVector, default_device, tri_count
+from ..device import BlockDiag, DeviceVector, default_device
 
 LOG = logging.getLogger(__name__)
 

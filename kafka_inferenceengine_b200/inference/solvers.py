@@ -12,9 +12,8 @@ import numpy as np
 import scipy.sparse as sp
 import torch
 
-from .. import _lib
 from .. import engine
-from ..device import BlockDiag, DeviceBands, DeviceVector, PixelIndex, default_device, padded
+from ..device import BlockDiag, DeviceBands, DeviceVector, PixelIndex, default_device
 
 LOG = logging.getLogger(__name__ + ".solvers")
 

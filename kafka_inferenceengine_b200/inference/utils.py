@@ -19,7 +19,7 @@ import scipy.sparse as sp
 import torch
 
 from .. import _lib
-from ..device import BlockDiag, DeviceVector, PixelIndex, default_device, padded
+from ..device import BlockDiag, DeviceVector, default_device, padded
 
 LOG = logging.getLogger(__name__)
 

@@ -4,7 +4,7 @@ import numpy as np
 import torch
 
 from kafka_inferenceengine_b200 import _lib
-from kafka_inferenceengine_b200.device import padded, tri_count
+from kafka_inferenceengine_b200.device import padded
 
 DEV = "cuda:0"
 

@@ -10,7 +10,6 @@ import datetime as dt
 
 import numpy as np
 import pytest
-import torch
 
 import golden_io as gio
 import gpu_util as gu

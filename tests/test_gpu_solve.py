@@ -8,9 +8,9 @@ import torch
 import golden_io as gio
 import gpu_util as gu
 import kafka_inferenceengine_b200 as kb
-from kafka_inferenceengine_b200 import _lib, engine
+from kafka_inferenceengine_b200 import _lib
 from kafka_inferenceengine_b200 import synthetic as syn
-from kafka_inferenceengine_b200.device import BlockDiag, DeviceVector, padded, tri_count
+from kafka_inferenceengine_b200.device import padded, tri_count
 from oracle import kafka_cpu as kc
 
 pytestmark = pytest.mark.gpu
