@@ -417,10 +417,24 @@ def run_other_workload(args):
         kf.run(grid, mean, None, prior_inv, iter_obs_op=True)
         torch.cuda.synchronize()
         ms = 1e3 * (time.perf_counter() - t0)
+        # the advance kernel on its own (propagate_information_filter_LAI, SURVEY 8d: 24 B in, 8P + 4P(P+1) out)
+        xa = DeviceVector.broadcast(syn.TIP_MEAN, N, device)
+        Aa = prior_inv.materialise()
+        adv_ms = timed(lambda: kb.propagate_information_filter_LAI(xa, None, Aa, None, q), 10, 3)
+        adv_bytes = N * (24 + 8 * 7 + 4 * 7 * 8)
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
+            os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        hbm = float(peaks.get("hbm_gbs", 6650.0))
         print(json.dumps({"workload": "c3: MODIS tile 2400x2400 (5.76 M px), TIP P=7, B=2 (D=4, T=500), %d daily steps, "
                                       "observations every 8th day, LAI propagator; device-resident rasters" % n_steps,
                           "metric": "pixel-steps/sec", "value": N * n_steps / (ms * 1e-3), "ms_per_step": ms / n_steps,
                           "pixel_dates_per_s": N * len(dates) / (ms * 1e-3), "iterations": kf.last_iterations,
+                          "advance_kernel": {"kernel": "advance_carry_kernel (propagate_information_filter_LAI)",
+                                             "ms_per_call": adv_ms, "algorithmic_bytes": adv_bytes,
+                                             "GBs": adv_bytes / (adv_ms * 1e-3) / 1e9,
+                                             "frac_of_hbm_peak": adv_bytes / (adv_ms * 1e-3) / 1e9 / hbm,
+                                             "note": "CUDA events around the python call: includes two output "
+                                                     "allocations and the launch"},
                           "n_gpus": 1}))
     else:
         # configs[4]: batched update with SUPPLIED Jacobians, n_params x bands sweep at 4 M pixels
@@ -432,7 +446,7 @@ def run_other_workload(args):
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
             os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm = float(peaks.get("hbm_gbs", 6650.0))
-        for Pn in (2, 4, 7, 10, 12, 16):
+        for Pn in [int(v) for v in os.environ.get("KAFKA_C5_PARAMS", "2,4,7,10,12,16").split(",")]:
             for Bn in (1, 4, 10, 13):
                 Lp = tri_count(Pn)
                 rnd = lambda r: torch.randn((r, ld), generator=gen, dtype=torch.float64, device=device)

@@ -10,6 +10,8 @@
 // kernel).  This kernel is HBM-bound; algorithmic bytes per pixel are in DESIGN.md.
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "chol.cuh"
 
 namespace kafka {
@@ -150,11 +152,24 @@ __device__ __forceinline__ void band_row_staged(const SolveBandDev& bd, const do
 #endif
 constexpr int kAsyncStages = KAFKA_ASYNC_STAGES;
 
+// Packed entries kept in registers: all of them up to n_params 12 (78 entries).  For 13..15
+// the first 124 - 4 n_params stay in registers and the remaining rows live in the thread's
+// own shared-memory column (measured: 13 -> 74 %, 14 -> 61 %, 15 -> 46 % of the HBM peak,
+// against 70 / 55 / 37 % with everything in registers and spilling).  At 16 the column would
+// leave one 4-warp CTA per SM, which is slower than spilling; it stays in registers.
+template <int P>
+struct SolveBlock {
+    static constexpr int L = tri_count(P);
+    static constexpr int R = (P >= 13 && P <= 15) ? 124 - 4 * P : L;
+    using type = typename std::conditional<R == L, RegBlock<L>, SplitBlock<L, R, kSolveThreads>>::type;
+};
+
 template <int P>
 __global__ void __launch_bounds__(kSolveThreads)
 solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     constexpr int L = tri_count(P);
-    extern __shared__ __align__(16) double stages[];               // kAsyncStages x (3 + n_dim_max) x 128
+    constexpr int R = SolveBlock<P>::R;
+    extern __shared__ __align__(16) double stages[];               // kAsyncStages x (3 + n_dim_max) x 128 [+ (L-R) x 128]
     __shared__ double s_part[2][kSolveThreads / 32];
     const int64_t tile0 = (int64_t)blockIdx.x * kSolveThreads;
     const int64_t i = tile0 + threadIdx.x;
@@ -181,18 +196,28 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     for (int b = 0; b < kAsyncStages - 1; ++b) issue(b);
 
     const int64_t il = live ? i : tile0;
-    double A[L], rhs[P], xp[P], xf[P];
+    typename SolveBlock<P>::type A;
+    if constexpr (R < L) A.sm = stages + kAsyncStages * stage_doubles + threadIdx.x;
+    double rhs[P], xp[P];
     const bool bcast = (prm.flags & KAFKA_PRIOR_BROADCAST) != 0;
     const bool round32 = (prm.flags & KAFKA_ROUND_F32) != 0;
     bool domain_bad = false;
 #pragma unroll
-    for (int c = 0; c < L; ++c) A[c] = bcast ? prm.pinv_f[c] : ldg_stream(prm.pinv_f + (int64_t)c * ld + il);
+    for (int c = 0; c < L; ++c) A.set(c, bcast ? prm.pinv_f[c] : ldg_stream(prm.pinv_f + (int64_t)c * ld + il));
 #pragma unroll
     for (int p = 0; p < P; ++p) {
         xp[p] = ldg_stream(prm.x_prev + (int64_t)p * ld + il);
-        xf[p] = ldg_stream(prm.x_f + (int64_t)p * ld + il);
+        rhs[p] = 0.0;
     }
-    symv<P>(A, xf, rhs);
+    {   // rhs = P_f^-1 x_f, one column at a time: x_f is not kept (it is re-read, from L2 at
+        // best, only by the rare failed pixel and by the optional forward output)
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+            const double xq = __ldg(prm.x_f + (int64_t)q * ld + il);
+#pragma unroll
+            for (int r = 0; r < P; ++r) rhs[r] = fma(A.get(r >= q ? tri(r, q) : tri(q, r)), xq, rhs[r]);
+        }
+    }
 
     for (int b = 0; b < prm.n_bands; ++b) {
         issue(b + kAsyncStages - 1);
@@ -212,7 +237,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
             const double wj = w * J[r];
             rhs[r] = fma(wy, J[r], rhs[r]);
 #pragma unroll
-            for (int q = 0; q <= r; ++q) A[tri(r, q)] = fma(wj, J[q], A[tri(r, q)]);
+            for (int q = 0; q <= r; ++q) A.set(tri(r, q), fma(wj, J[q], A.get(tri(r, q))));
         }
         if (prm.innovations && live) stg_stream(prm.innovations + (int64_t)b * ld + i, y - h0);
     }
@@ -220,13 +245,13 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
 
     if (live) {
 #pragma unroll
-        for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A[c]);
+        for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A.get(c));
         double invd[P];
-        const bool ok = chol_factor<P>(A, invd) && !domain_bad;
-        chol_solve<P>(A, invd, rhs);
+        const bool ok = chol_factor_blk<P>(A, invd) && !domain_bad;
+        chol_solve_blk<P>(A, invd, rhs);
 #pragma unroll
         for (int p = 0; p < P; ++p) {
-            const double xn = ok ? rhs[p] : xf[p];
+            const double xn = ok ? rhs[p] : __ldg(prm.x_f + (int64_t)p * ld + i);
             rhs[p] = xn;
             stg_stream(prm.x_out + (int64_t)p * ld + i, xn);
             const double d = xn - xp[p];
@@ -241,7 +266,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
                 band_row<P>(bd, ld, i, xp, bd.w[i], J, h0, round32, dummy);
                 double f = h0;
 #pragma unroll
-                for (int p = 0; p < P; ++p) f = fma(J[p], rhs[p] - xf[p], f);
+                for (int p = 0; p < P; ++p) f = fma(J[p], rhs[p] - __ldg(prm.x_f + (int64_t)p * ld + i), f);
                 stg_stream(prm.fwd + (int64_t)b * ld + i, f);
             }
         }
@@ -420,10 +445,11 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
     int n_dim_max = 0;
     for (int b = 0; b < n_bands; ++b)
         if (prm.bands[b].kind == KAFKA_BAND_ARRAYS && prm.bands[b].n_planes > n_dim_max) n_dim_max = prm.bands[b].n_planes;
-    const size_t smem = (size_t)kAsyncStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
+    const size_t ring = (size_t)kAsyncStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
     int rc = KAFKA_E_UNSUPPORTED;
     KAFKA_DISPATCH_P(n_params, {
         auto kern = solve_bands_kernel<kP>;
+        const size_t smem = ring + (size_t)(SolveBlock<kP>::L - SolveBlock<kP>::R) * kSolveThreads * sizeof(double);
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
             set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
