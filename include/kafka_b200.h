@@ -221,6 +221,21 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
                       double* norm2, int32_t* n_bad, double* scratch, uint32_t flags,
                       void* stream);
 
+/* One whole iteration of LinearKalman.do_all_bands (kafka/linear_kf.py:258-296)
+ * when every band is a GP emulator: relinearise all bands at x_prev
+ * (create_prosail/nonlinear_observation_operator, kafka/inference/utils.py:130-219)
+ * into the caller's workspaces h0_work[n_bands*ld], jac_work[n_bands*D*ld], then
+ * run the update of kafka_solve_bands on them.  y, w: [b*ld+i] planes (w gated to
+ * 0 where unobserved); obs_mask as in kafka_gp_linearize (may be NULL).  Same
+ * results as kafka_gp_linearize followed by kafka_solve_bands on one stream.
+ * The caller loops: swap x_prev/x_out, read *norm2, stop as linear_kf.py:288-305. */
+int kafka_assimilate_iter(int64_t n_pix, int64_t ld, int n_params, const kafka_gp_band* gp_bands_host,
+                          int n_bands, const double* y, const double* w, const uint8_t* obs_mask,
+                          const double* x_prev, const double* x_f, const double* pinv_f,
+                          double* h0_work, double* jac_work, double* x_out, double* a_out,
+                          double* innovations, double* fwd, double* norm2, int32_t* n_bad,
+                          double* scratch, uint32_t flags, void* stream);
+
 /* Same update as kafka_solve_bands for callers that cannot allocate device memory
  * and therefore cannot pass `scratch`.  It has no counterpart in the reference
  * (pure Python, no device memory at all).  Typical callers: a plug-in inside a

@@ -68,6 +68,8 @@ SIGNATURES = {
                                     _p, _p, _p, _u32, _p]),
     "kafka_solve_bands_static": (C.c_int, [_i64, _i64, _i32, C.POINTER(SolveBand), _i32, _p, _p, _p, _p, _p, _p, _p,
                                            _p, _p, _u32, _p]),
+    "kafka_assimilate_iter": (C.c_int, [_i64, _i64, _i32, C.POINTER(GpBand), _i32, _p, _p, _p, _p, _p, _p, _p, _p,
+                                        _p, _p, _p, _p, _p, _p, _p, _u32, _p]),
     "kafka_wcm_forward": (C.c_int, [_p, _i64, _i64, _p, _p, _p, _p]),
     "kafka_advance_carry_slot": (C.c_int, [_p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _p, _p, _p]),
     "kafka_advance_approx": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p]),
@@ -99,7 +101,8 @@ def get_lib():
 
 # kernels launched by one successful call of each entry point (for bench.py's
 # gpu_launches count; the set of kernels is in csrc/*.cu)
-KERNELS_PER_CALL = {"kafka_compact_mask": 3, "kafka_solve_bands": 2, "kafka_solve_bands_static": 3}
+KERNELS_PER_CALL = {"kafka_compact_mask": 3, "kafka_solve_bands": 2, "kafka_solve_bands_static": 3,
+                    "kafka_assimilate_iter": 3}
 launch_count = 0
 
 

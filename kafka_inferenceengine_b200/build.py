@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libkafka_b200.so")
-SOURCES = ["layout.cu", "gp.cu", "solve.cu", "advance.cu", "noalloc.cu"]
+SOURCES = ["layout.cu", "gp.cu", "solve.cu", "advance.cu", "assimilate.cu", "noalloc.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
