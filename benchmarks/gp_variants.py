@@ -24,7 +24,12 @@ VARIANTS = {
     "u4": ["-DKAFKA_GP_UNROLL=4"],
     "ppt1_u4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_UNROLL=4"],
     "t256": ["-DKAFKA_GP_THREADS=256"],
+    "tab256_checked": ["-DKAFKA_EXP_CLAMP=0", "-DKAFKA_EXP_LOG2N=8"],
+    "tab256": ["-DKAFKA_EXP_LOG2N=8"],
+    "checked": ["-DKAFKA_EXP_CLAMP=0"],
 }
+if os.environ.get("KAFKA_GP_VARIANTS"):
+    VARIANTS = {k: v for k, v in VARIANTS.items() if k in os.environ["KAFKA_GP_VARIANTS"].split(",")}
 
 
 def build():

@@ -9,13 +9,13 @@
 //             e_j = ln s_f - 0.5 sum_d theta_d X'_jd^2
 //     w_j   = k_j alpha_j,   mean = sum_j w_j,   G_d = sum_j w_j zh_jd
 //     dmean/dx_d = G_d - theta_d x'_d mean
-// The table stores zh and e pre-multiplied by L = 256/ln2, so the dot product IS the
-// base-2^(1/256) exponent: k = rint(a), r = a - k is exact, 2^(k/256) comes from a
-// 256-entry table and exp(r ln2/256) from a degree-4 polynomial (|r| <= 1/2, truncation
-// 3.8e-17).  The per-pixel factor exp(-0.5 sum theta x'^2) is pulled out of the loop and
+// The table stores zh and e pre-multiplied by L = 1024/ln2, so the dot product IS the
+// base-2^(1/1024) exponent: k = rint(a), r = a - k is exact, 2^(k/1024) comes from a
+// 1024-entry table and exp(r ln2/1024) from a degree-3 polynomial (|r| <= 1/2, truncation
+// 5.4e-16).  The per-pixel factor exp(-0.5 sum theta x'^2) is pulled out of the loop and
 // applied once at the end (a warp keeps it inside the exponent when one of its pixels is so
 // far from the centre that the un-shifted exponent could overflow).  Per (pixel, band,
-// training point): 2D FMAs + ~10 fp64 ops, i.e. 30 fp64-pipe instructions at D=10 against
+// training point): 2D FMAs + ~9 fp64 ops, i.e. 29 fp64-pipe instructions at D=10 against
 // the 5D+28 = 78 flops of the textbook form.  The training table (T rows of {zh[D], e,
 // alpha}) is staged once per CTA in shared memory by a TMA bulk copy and then read as
 // warp-wide broadcasts.  The kernel is bound by the fp64 pipe, not by HBM.
@@ -26,27 +26,36 @@
 
 namespace kafka {
 
-// exponent granularity: 2^(1/64) (64-entry table + degree-5 polynomial) or 2^(1/256)
-// (256-entry table + degree-4 polynomial, one DFMA fewer per evaluation)
+// exponent granularity: 2^(1/64) (64-entry table + degree-5 polynomial), 2^(1/256)
+// (256 entries + degree 4) or 2^(1/1024) (1024 entries + degree 3): one DFMA fewer per
+// evaluation with every step
 #ifndef KAFKA_EXP_LOG2N
-#define KAFKA_EXP_LOG2N 8   // measured 4.5 % faster than 6 on B200 (benchmarks/gp_variants.py)
+#define KAFKA_EXP_LOG2N 10  // B200, benchmarks/gp_variants.py: 8 is 4.5 % faster than 6, 10 another 1.6 %
+#endif
+// unchecked exponent insert in the hot loop (see exp_scaled); with LOG2N 10: 5.3 % faster than 8 + checked
+#ifndef KAFKA_EXP_CLAMP
+#define KAFKA_EXP_CLAMP 1
 #endif
 #ifndef KAFKA_EXP_F2I
 #define KAFKA_EXP_F2I 0
 #endif
 constexpr int kExpLog2N = KAFKA_EXP_LOG2N;
 constexpr int kExpN = 1 << kExpLog2N;
-__constant__ double c_exp2_tab[kExpN] = {
+// in global memory (not __constant__): every CTA copies it to shared memory, and constant
+// loads at 32 different addresses per warp would serialise
+__device__ __align__(16) const double g_exp2_tab[kExpN] = {
 #if KAFKA_EXP_LOG2N == 6
 #include "exp_table.inc"
-#else
+#elif KAFKA_EXP_LOG2N == 8
 #include "exp_table256.inc"
+#else
+#include "exp_table1024.inc"
 #endif
 };
 
 // ---- table layout -----------------------------------------------------------
 __host__ __device__ constexpr int dpad(int D) { return (D + 1) & ~1; }
-__host__ __device__ constexpr int tab_hdr(int D) { return 2 * dpad(D) + 2; }   // theta_e, centre, s_f, nugget
+__host__ __device__ constexpr int tab_hdr(int D) { return 2 * dpad(D) + 4; }   // theta_e, centre, s_f, nugget, wide, 0
 __host__ __device__ constexpr int tab_row(int D) { return dpad(D) + 2; }       // zh[DP], e, alpha
 
 // ---- exp in base 2^(1/N): argument already scaled by L = N/ln2 ----------------------
@@ -59,20 +68,31 @@ constexpr uint32_t kHiUnder = 0x40efeb6cu;               // high word of 708 L
 __constant__ double c_exp_poly[6] = {1.24178437017169252822e-12, 5.73285168864040188714e-10,
                                       2.11731371554647762752e-07, 5.86490495505616996649e-05,
                                       1.08304246962491450973e-02, 6755399441055744.0 /* 1.5 * 2^52 */};
-#else
+#elif KAFKA_EXP_LOG2N == 8
 constexpr double kL = 3.69329930467574627073e+02;        // 256/ln2
 constexpr double kInvL = 2.70760617406228627432e-03;     // ln2/256
 constexpr uint32_t kHiUnder = 0x410feb6cu;               // high word of 708 L
 __constant__ double c_exp_poly[6] = {0.0, 2.23939519087515698716e-12, 3.30830268054137129301e-09,
                                       3.66556559691010622906e-06, 2.70760617406228627432e-03,
                                       6755399441055744.0 /* 1.5 * 2^52 */};
+#else
+constexpr double kL = 1.47731972187029850829e+03;        // 1024/ln2
+constexpr double kInvL = 6.76901543515571568581e-04;     // ln2/1024
+constexpr uint32_t kHiUnder = 0x412feb6cu;               // high word of 708 L
+__constant__ double c_exp_poly[6] = {0.0, 0.0, 5.16922293834589264532e-11, 2.29097849806881639316e-07,
+                                      6.76901543515571568581e-04, 6755399441055744.0 /* 1.5 * 2^52 */};
 #endif
 constexpr double kFarShift = 600.0 * kL;                 // beyond this the per-pixel factor stays in the exponent
 
-// exp(a / L) for finite a < 709 L.  fp64-pipe cost: 3 adds + 5 (4) FMAs + 1 mul; the only range
-// test is one unsigned compare on the high word (exactly 0 below -708 L), so the function is
-// branch-free and several evaluations interleave.  |rel err| < 3e-16.  NaN / +inf / overflow
-// are NOT handled here: callers check their inputs once per pixel, outside the hot loop.
+// exp(a / L) for finite a < 709 L.  fp64-pipe cost: 3 adds + 5 / 4 / 3 FMAs + 1 mul.
+// kChecked: the only range test is one unsigned compare on the high word (exactly 0 below
+// -708 L), so the function is branch-free and several evaluations interleave.
+// !kChecked: for callers that guarantee |a| < 2^30 (then k below is exact): the binary exponent
+// is clamped with one integer max instead, and what would underflow comes out as a number of
+// the order of 2^-1021 instead of 0 -- three integer instructions fewer per evaluation.
+// |rel err| < 6e-16.  NaN / +inf / overflow are NOT handled here: callers check their inputs
+// once per pixel, outside the hot loop.
+template <bool kChecked = true>
 __device__ __forceinline__ double exp_scaled(double a, const double* __restrict__ tab) {
 #if KAFKA_EXP_F2I
     const int k = __double2int_rn(a);
@@ -85,24 +105,32 @@ __device__ __forceinline__ double exp_scaled(double a, const double* __restrict_
 #if KAFKA_EXP_LOG2N == 6
     double p = fma(r, c_exp_poly[0], c_exp_poly[1]);
     p = fma(p, r, c_exp_poly[2]);
-#else
-    double p = fma(r, c_exp_poly[1], c_exp_poly[2]);
-#endif
     p = fma(p, r, c_exp_poly[3]);
+#elif KAFKA_EXP_LOG2N == 8
+    double p = fma(r, c_exp_poly[1], c_exp_poly[2]);
+    p = fma(p, r, c_exp_poly[3]);
+#else
+    double p = fma(r, c_exp_poly[2], c_exp_poly[3]);
+#endif
     p = fma(p, r, c_exp_poly[4]);
     p = fma(p, r, 1.0);
-    const double v = tab[k & (kExpN - 1)] * p;
-    const int hi_n = __double2hiint(v) + ((k >> kExpLog2N) << 20);
-    const int lo_n = __double2loint(v);
-    int hi, lo;
-    // selp keeps this branch-free (the compiler otherwise jumps around the exponent insert)
-    asm("{\n\t.reg .pred p;\n\t"
-        "setp.ge.u32 p, %2, %3;\n\t"
-        "selp.b32 %0, 0, %4, p;\n\t"
-        "selp.b32 %1, 0, %5, p;\n\t}"
-        : "=r"(hi), "=r"(lo)
-        : "r"(__double2hiint(a)), "r"(0x80000000u + kHiUnder), "r"(hi_n), "r"(lo_n));
-    return __hiloint2double(hi, lo);
+    const double v = tab[k & (kExpN - 1)] * p;           // in (0.99, 2.01)
+    if constexpr (!kChecked) {
+        const int e = max(k >> kExpLog2N, -1021);
+        return __hiloint2double(__double2hiint(v) + (e << 20), __double2loint(v));
+    } else {
+        const int hi_n = __double2hiint(v) + ((k >> kExpLog2N) << 20);
+        const int lo_n = __double2loint(v);
+        int hi, lo;
+        // selp keeps this branch-free (the compiler otherwise jumps around the exponent insert)
+        asm("{\n\t.reg .pred p;\n\t"
+            "setp.ge.u32 p, %2, %3;\n\t"
+            "selp.b32 %0, 0, %4, p;\n\t"
+            "selp.b32 %1, 0, %5, p;\n\t}"
+            : "=r"(hi), "=r"(lo)
+            : "r"(__double2hiint(a)), "r"(0x80000000u + kHiUnder), "r"(hi_n), "r"(lo_n));
+        return __hiloint2double(hi, lo);
+    }
 }
 
 // ---- linearise: mean + Jacobian for every (pixel, band) -------------------------
@@ -162,7 +190,7 @@ __device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, i
             double a = kShiftInside ? ea.x + sh[pp] : ea.x;
 #pragma unroll
             for (int d = 0; d < D; ++d) a = fma(zh[d], xr[pp][d], a);
-            const double w = exp_scaled(a, tab64) * ea.y;
+            const double w = exp_scaled<kShiftInside || !KAFKA_EXP_CLAMP>(a, tab64) * ea.y;
             mu[pp] += w;
 #pragma unroll
             for (int d = 0; d < D; ++d) G[pp][d] = fma(w, zh[d], G[pp][d]);
@@ -176,7 +204,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     extern __shared__ __align__(16) double smem[];
     __shared__ uint64_t bar;
-    __shared__ double s_exp[kExpN];
+    __shared__ __align__(16) double s_exp[kExpN];
 
     // band is the FAST grid index: the CTAs of all bands of one pixel tile run together, so
     // the tile's state is fetched from HBM once and served to the other bands by L2
@@ -187,10 +215,10 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     const uint32_t bytes = (uint32_t)((HDR + T * RS) * sizeof(double));
 
     if (threadIdx.x == 0) mbar_init(&bar, 1);
-    for (int k = threadIdx.x; k < kExpN; k += kGpThreads) s_exp[k] = c_exp2_tab[k];
     __syncthreads();
     if (threadIdx.x == 0) {
-        mbar_expect_tx(&bar, bytes);
+        mbar_expect_tx(&bar, bytes + (uint32_t)sizeof(s_exp));
+        tma_bulk_g2s(s_exp, g_exp2_tab, (uint32_t)sizeof(s_exp), &bar);
         constexpr uint32_t kChunk = 16384;
         for (uint32_t off = 0; off < bytes; off += kChunk)
             tma_bulk_g2s(reinterpret_cast<char*>(smem) + off, reinterpret_cast<const char*>(band.table) + off,
@@ -221,7 +249,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     const double* rows = smem + HDR;
 
     double sh[PPT], mu[PPT], G[PPT][D];
-    bool far = false, bad[PPT];
+    bool far = smem[2 * DP + 2] != 0.0, bad[PPT];             // a "wide" table takes the checked path
 #pragma unroll
     for (int pp = 0; pp < PPT; ++pp) {
         double s = 0.0;
@@ -291,7 +319,7 @@ gp_hessian_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, con
     __shared__ double s_exp[kExpN];
     const int total = HDR + T * RS;
     for (int k = threadIdx.x; k < total; k += kGpThreads) smem[k] = table[k];
-    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = c_exp2_tab[k];
+    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = g_exp2_tab[k];
     __syncthreads();
     int64_t i = (int64_t)blockIdx.x * kGpThreads + threadIdx.x;
     if (i >= n_pts) return;
@@ -358,7 +386,7 @@ gp_hessian_correction_kernel(const __grid_constant__ GpHessCorrParams prm) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D), L = tri_count(D);
     extern __shared__ __align__(16) double smem[];
     __shared__ double s_exp[kExpN];
-    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = c_exp2_tab[k];
+    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = g_exp2_tab[k];
     const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
     const bool in = i < prm.n_pix;
     const int LP = tri_count(prm.n_params);
@@ -432,7 +460,7 @@ gp_variance_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, co
                    int D, const double* __restrict__ inv_q, double* __restrict__ var) {
     extern __shared__ double kbuf[];             // [4 warps][T]
     __shared__ double s_exp[kExpN];
-    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = c_exp2_tab[k];
+    for (int k = threadIdx.x; k < kExpN; k += blockDim.x) s_exp[k] = g_exp2_tab[k];
     __syncthreads();
     const int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -540,6 +568,7 @@ int kafka_gp_pack_host(const double* inputs, const double* theta, const double* 
     }
     table[2 * DP] = exp(theta[D]);
     table[2 * DP + 1] = exp(theta[D + 1]);
+    double wide = 0.0;
     for (int j = 0; j < T; ++j) {
         double* row = table + HDR + (size_t)j * RS;
         double c = 0.0;
@@ -547,11 +576,16 @@ int kafka_gp_pack_host(const double* inputs, const double* theta, const double* 
             double xc = inputs[(size_t)j * D + d] - centre[d];
             double zh = theta_e[d] * xc;
             c = fma(zh, xc, c);
-            row[d] = kL * zh;                         // rows are stored in units of ln2/64
+            row[d] = kL * zh;                         // rows are stored in units of 1/L
         }
         row[DP] = kL * (theta[D] - 0.5 * c);
         row[DP + 1] = invqt[j];
+        // exponent of this row at any pixel the kernel does not treat as far (sum theta x'^2 < 1200):
+        // |a| <= L (|ln s_f| + c/2 + sqrt(1200 c)).  The unchecked exp needs |a| < 2^30.
+        const double bound = kL * (fabs(theta[D]) + 0.5 * c + sqrt(1200.0 * c));
+        if (!(bound < 1073741824.0)) wide = 1.0;
     }
+    table[2 * DP + 2] = wide;
     return 0;
 }
 
