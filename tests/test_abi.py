@@ -46,7 +46,7 @@ def test_bad_arguments_are_rejected_without_a_gpu():
     lib = _lib.get_lib()
     assert lib.kafka_gp_table_doubles(250, 17) == -1
     assert lib.kafka_gp_table_doubles(250, 10) == 2 * 10 + 4 + 250 * 12
-    assert lib.kafka_gp_table_doubles(250, 7) == 2 * 8 + 2 + 250 * 10
+    assert lib.kafka_gp_table_doubles(250, 7) == 2 * 8 + 4 + 250 * 10
     assert lib.kafka_solve_scratch_doubles(-1) == -1
     assert lib.kafka_compact_scratch_elems(4097) == 4
     st = lib.kafka_interleaved_to_planar(None, 10, 0, None, 32, None)
