@@ -71,15 +71,16 @@ def test_gp_pack_host_matches_numpy():
         alpha = rng.standard_normal(T)
         tab = _lib.gp_pack(X, theta, alpha)
         DP = (D + 1) & ~1
-        assert tab.size == 2 * DP + 2 + T * (DP + 2)
+        assert tab.size == 2 * DP + 4 + T * (DP + 2)
         e = np.exp(theta)
         c = X.mean(axis=0)
         assert np.allclose(tab[:D], e[:D], rtol=1e-15)
         assert np.allclose(tab[DP:DP + D], c, rtol=1e-14, atol=1e-16)
         assert tab[2 * DP] == pytest.approx(e[D], rel=1e-15)
-        rows = tab[2 * DP + 2:].reshape(T, DP + 2)
+        assert tab[2 * DP + 2] == 0.0 and tab[2 * DP + 3] == 0.0     # not a "wide" training set
+        rows = tab[2 * DP + 4:].reshape(T, DP + 2)
         Xc = X - tab[DP:DP + D]
-        L = 256.0 / np.log(2.0)                      # rows are in units of ln2/256
+        L = 1024.0 / np.log(2.0)                     # rows are in units of ln2/1024
         assert np.allclose(rows[:, :D], L * e[:D] * Xc, rtol=4e-16, atol=0)
         assert np.allclose(rows[:, DP], L * (theta[D] - 0.5 * (e[:D] * Xc * Xc).sum(axis=1)), rtol=1e-14)
         assert np.array_equal(rows[:, DP + 1], alpha)
@@ -87,3 +88,9 @@ def test_gp_pack_host_matches_numpy():
             assert np.all(rows[:, D] == 0.0)
     with pytest.raises(ValueError):
         _lib.gp_pack(np.zeros((3, 17)), np.zeros(19), np.zeros(3))
+    # a training point ~2000 length scales from the centre: flagged, the kernels then keep the
+    # range-checked exponential
+    X = np.zeros((4, 2))
+    X[0] = 6000.0
+    tab = _lib.gp_pack(X, np.zeros(4), np.ones(4))
+    assert tab[2 * 2 + 2] == 1.0
