@@ -84,6 +84,31 @@ def test_exp_underflow_and_far_points():
     assert np.allclose(jac, jac_o, rtol=1e-8, atol=1e-300)
 
 
+@pytest.mark.parametrize("outlier", [30.0, 45.0, 8000.0])
+def test_outlier_training_point(outlier):
+    """One training point ``outlier`` length scales from the rest.  Near the centre its kernel
+    value underflows (30: not quite; 45: yes, inside the unchecked exponent of the hot loop;
+    8000: the packer flags the table as wide and the checked exponent runs); near the outlier
+    it is the only point that counts (far-pixel path)."""
+    rng = np.random.default_rng(13)
+    D, T = 4, 40
+    gp0, mean, sigma = _gp(rng, D, T)
+    X = gp0.inputs.copy()
+    ls = 4.0 * sigma                                        # length scales of make_emulator
+    X[7] = mean + outlier * ls / np.sqrt(D)
+    gp = GaussianProcess(X, gp0.targets, gp0.theta)
+    tab = _lib.gp_pack(gp.inputs, gp.theta, gp.invQt)
+    assert (tab[2 * D + 2] != 0.0) == (outlier > 1000.0)
+    pts = np.vstack([mean + 0.5 * sigma * rng.standard_normal((64, D)),
+                     X[7] + 0.5 * sigma * rng.standard_normal((64, D)),
+                     mean + 0.5 * (X[7] - mean)[None, :] + sigma * rng.standard_normal((64, D))])
+    mu_o, jac_o = gp.predict_direct(pts)
+    mu, jac = kb.run_emulator(gp, pts)
+    assert np.isfinite(mu).all() and np.isfinite(jac).all()
+    assert np.allclose(mu, mu_o, rtol=1e-8, atol=1e-12 * np.abs(mu_o).max())
+    assert np.allclose(jac, jac_o, rtol=1e-8, atol=1e-12 * np.abs(jac_o).max())
+
+
 @pytest.mark.parametrize("n", [1, 127, 129, 4095, 40000])
 def test_linearize_bands_mask_mapper_rounding(n):
     """kafka_gp_linearize on the TIP layout: two bands, per-band state mappers
