@@ -723,6 +723,7 @@ def main():
                          "algorithmic_bytes_per_launch": sv_bytes, "ms_per_launch": sv_ms,
                          "traffic": (ncu_bpp["solve_bands_kernel"] * n_pix)
                          if "solve_bands_kernel" in ncu_bpp else None},
+        "step_breakdown_ms": {k: float(np.sum(v)) / args.steps for k, v in prof.items()},
         "step": {"bytes_per_pixel_date": BYTES_PER_PIXEL_DATE,
                  "achieved": n_pix * BYTES_PER_PIXEL_DATE / (ms_step * 1e-3) / 1e9, "unit": "GB/s",
                  "frac": n_pix * BYTES_PER_PIXEL_DATE / (ms_step * 1e-3) / 1e9 / hbm_peak},

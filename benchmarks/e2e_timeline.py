@@ -1,0 +1,98 @@
+"""Where does the host thread of the end-to-end run spend its time?
+
+    python benchmarks/e2e_timeline.py [raw|host] [rows]
+
+Wraps the phases of LinearKalman.run (read bands, stage, finish, norm wait, output, advance)
+with wall-clock timers -- no extra synchronisation, so the overlap is the one bench.py sees --
+and prints milliseconds per date.  A phase that waits for the GPU (norm) shows the GPU time
+the host could not hide behind."""
+import collections
+import datetime as dt
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+import kafka_inferenceengine_b200 as kb  # noqa: E402
+from kafka_inferenceengine_b200 import engine, synthetic as syn  # noqa: E402
+from kafka_inferenceengine_b200.device import BlockDiag, DeviceVector  # noqa: E402
+from kafka_inferenceengine_b200.output import RasterOutput  # noqa: E402
+
+ACC = collections.defaultdict(float)
+
+
+def timed(cls, name, tag):
+    fn = getattr(cls, name)
+
+    def wrap(*a, **k):
+        t0 = time.perf_counter()
+        try:
+            return fn(*a, **k)
+        finally:
+            ACC[tag] += time.perf_counter() - t0
+    setattr(cls, name, wrap)
+
+
+def main():
+    mode = sys.argv[1] if len(sys.argv) > 1 else "raw"
+    rows = int(sys.argv[2]) if len(sys.argv) > 2 else bench.SHARD_ROWS
+    device = torch.device("cuda", 0)
+    shape = (rows, bench.TILE)
+    n_pix = rows * bench.TILE
+    gps = bench.make_emulators()
+    rho, inv, mask = bench.synth_on_device(gps, n_pix, 1234, device)
+    base = dt.datetime(2017, 7, 3)
+    n_warm, steps = 2, 5
+    dates = [base + dt.timedelta(days=d, hours=12) for d in range(n_warm + steps)]
+    obs = (bench.RawObservations(dates, gps, rho, mask, shape) if mode == "raw"
+           else bench.HostObservations(dates, gps, rho, inv, mask, shape))
+    out = RasterOutput(syn.S2_PARAMETERS)
+    inv_block = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
+    prior = syn.BroadcastPrior(syn.SAIL_MEAN, inv_block, n_pix, lambda blk, n: BlockDiag.from_block(blk, n, device),
+                               lambda m, n: DeviceVector.broadcast(m, n, device))
+    kf = kb.LinearKalman(obs, out, np.ones(shape, dtype=bool), kb.create_prosail_observation_operator,
+                         syn.S2_PARAMETERS, state_propagation=None, prior=prior, linear=False, device=device)
+    kf.set_trajectory_model()
+    kf.set_trajectory_uncertainty(0.0)
+    out.pixels = kf.pixels
+    x0, Pinv0 = prior.process_prior(None)
+    kf.run([base + dt.timedelta(days=d) for d in range(n_warm + 1)], x0, None, Pinv0, iter_obs_op=True)
+    torch.cuda.synchronize()
+
+    timed(kb.LinearKalman, "_read_bands", "read_bands")
+    timed(engine.ObservationStager, "stage", "stage (host copies + queue H2D)")
+    timed(engine.ObservationStager, "finish", "finish (queue gathers)")
+    timed(kb.LinearKalman, "_global_norm", "norm (.item(): waits for the GPU)")
+    timed(kb.LinearKalman, "advance", "advance")
+    timed(RasterOutput, "dump_data", "dump_data (incl. wait for previous D2H)")
+    timed(RasterOutput, "_deliver", "  of which _deliver")
+    timed(kb.LinearKalman, "do_all_bands", "do_all_bands (total)")
+    kf.profile = {}
+    prof = None
+    if os.environ.get("KAFKA_CPROFILE"):
+        import cProfile
+        prof = cProfile.Profile()
+        prof.enable()
+    t0 = time.perf_counter()
+    kf.run([base + dt.timedelta(days=n_warm + d) for d in range(steps + 1)], x0, None, Pinv0, iter_obs_op=True)
+    torch.cuda.synchronize()
+    total = time.perf_counter() - t0
+    if prof is not None:
+        import pstats
+        prof.disable()
+        pstats.Stats(prof).sort_stats("tottime").print_stats(18)
+    print("mode %s, %d px: %.1f ms per date" % (mode, n_pix, 1e3 * total / steps))
+    for k, v in ACC.items():
+        print("  %-44s %8.2f ms/date" % (k, 1e3 * v / steps))
+    print("  iterations", kf.last_iterations[-steps:])
+    for k, v in kf.profile.items():
+        print("  GPU %-40s %8.2f ms/date (CUDA events)" % (k, sum(a.elapsed_time(b) for a, b in v) / steps))
+
+
+if __name__ == "__main__":
+    main()

@@ -117,6 +117,15 @@ int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, in
 int kafka_state_uniform(const double* x, int64_t ld, int64_t n_pix, int n_params, int32_t* n_diff,
                         void* stream);
 
+/* Scalar read-back without the copy engine (no counterpart in the reference, which
+ * has no device): n_bytes (multiple of 8, <= 64 KiB) from device memory are written
+ * by a kernel into PINNED host memory (cudaHostAlloc / cudaHostRegister'ed; pageable
+ * memory is refused).  The convergence norm of every iteration (linear_kf.py:293)
+ * comes back this way: queued as a memcpy it would wait behind the previous date's
+ * output rasters on the device->host engine.  The host may read dst once the work
+ * queued on `stream` up to this call has completed (record an event and wait). */
+int kafka_read_small(const void* src_dev, void* dst_pinned_host, int64_t n_bytes, void* stream);
+
 /* ---- layout conversion at the boundary -----------------------------------
  * interleaved x[n_params*i+p] (kafka/inference/utils.py:201) <-> planar. */
 int kafka_interleaved_to_planar(const double* x_il, int64_t n_pix, int n_params, double* x_pl,

@@ -52,6 +52,7 @@ SIGNATURES = {
     "kafka_gather_scaled_band": (C.c_int, [_p, _i32, _p, _p, _i64, C.c_double, C.c_double, _p, _p, _p, _p]),
     "kafka_scatter_output": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p, _p, _p]),
     "kafka_state_uniform": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
+    "kafka_read_small": (C.c_int, [_p, _p, _i64, _p]),
     "kafka_interleaved_to_planar": (C.c_int, [_p, _i64, _i32, _p, _i64, _p]),
     "kafka_planar_to_interleaved": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
     "kafka_blocks_to_packed": (C.c_int, [_p, _i64, _i32, _p, _i64, _p]),
@@ -131,6 +132,28 @@ def np_ptr(a):
 def stream_ptr():
     import torch
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+_small = {}          # device index -> (pinned uint8 tensor, event)
+
+
+def read_small(t):
+    """Host copy (numpy, same dtype) of a SMALL contiguous CUDA tensor whose byte size is a
+    multiple of 8, through kafka_read_small: one tiny kernel on the current stream + an event
+    wait, no device->host memcpy (which would queue behind large transfers in flight)."""
+    import torch
+    nbytes = t.numel() * t.element_size()
+    if not (t.is_cuda and t.is_contiguous() and nbytes % 8 == 0 and 0 < nbytes <= 4096):
+        raise ValueError("read_small needs a contiguous CUDA tensor of 8..4096 bytes (multiple of 8)")
+    key = t.device.index
+    if key not in _small:
+        _small[key] = (torch.empty(4096, dtype=torch.uint8).pin_memory(), torch.cuda.Event())
+    host, event = _small[key]
+    with torch.cuda.device(t.device):
+        check(get_lib().kafka_read_small(ptr(t), C.c_void_p(host.data_ptr()), nbytes, stream_ptr()), "kafka_read_small")
+        event.record(torch.cuda.current_stream())
+    event.synchronize()
+    return host[:nbytes].numpy().view(np.dtype(str(t.dtype).replace("torch.", ""))).copy().reshape(tuple(t.shape))
 
 
 def gp_pack(inputs, theta, invqt):

@@ -24,6 +24,7 @@ void set_error(const char* fmt, ...);
         if (e_ != cudaSuccess) {                                                      \
             kafka::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
                              __FILE__, __LINE__);                                     \
+            (void)cudaGetLastError(); /* reported through the status: leave none behind */ \
             return (int)e_;                                                           \
         }                                                                             \
     } while (0)

@@ -335,6 +335,27 @@ int kafka_state_uniform(const double* x, int64_t ld, int64_t n_pix, int n_params
     return launch_status("state_uniform_kernel");
 }
 
+// A few words from device memory straight into pinned host memory, written by the SMs over
+// PCIe instead of by a copy engine: a scalar read-back queued as a memcpy would wait behind
+// whatever large device->host transfer (the previous date's output rasters) occupies the engine.
+__global__ void store_host_words_kernel(const uint64_t* __restrict__ src, uint64_t* __restrict__ dst, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
+    __threadfence_system();
+}
+
+int kafka_read_small(const void* src_dev, void* dst_pinned_host, int64_t n_bytes, void* stream) {
+    KAFKA_CHECK_ARG(src_dev && dst_pinned_host, "kafka_read_small: null pointer");
+    KAFKA_CHECK_ARG(n_bytes > 0 && n_bytes <= 65536 && n_bytes % 8 == 0,
+                    "kafka_read_small: n_bytes=%lld must be a multiple of 8 in 8..65536", (long long)n_bytes);
+    KAFKA_CHECK_ARG(((uintptr_t)src_dev | (uintptr_t)dst_pinned_host) % 8 == 0, "kafka_read_small: pointers must be 8-byte aligned");
+    void* dst_dev = nullptr;
+    KAFKA_CUDA(cudaHostGetDevicePointer(&dst_dev, dst_pinned_host, 0));     // fails for pageable memory
+    const int n = (int)(n_bytes / 8);
+    store_host_words_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const uint64_t*)src_dev, (uint64_t*)dst_dev, n);
+    return launch_status("store_host_words_kernel");
+}
+
 static int check_layout(const char* who, int64_t n_pix, int n_params, int64_t ld) {
     KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "%s: need 0 <= n_pix <= ld (n_pix=%lld ld=%lld)", who,
                     (long long)n_pix, (long long)ld);

@@ -127,14 +127,22 @@ __device__ __forceinline__ void band_row(const SolveBandDev& bd, int64_t ld, int
 
 template <int P>
 __device__ __forceinline__ void band_row_staged(const SolveBandDev& bd, const double* __restrict__ st, int n_dim_max,
-                                                const double (&xp)[P], double w, double (&J)[P], double& h0,
-                                                bool round32, bool& domain_bad) {
+                                                const double* __restrict__ uni, const double (&xp)[P], double w,
+                                                double (&J)[P], double& h0, bool round32, bool& domain_bad) {
     // stage layout: [w | y | h0 | jac plane 0 .. n_dim-1], kSolveThreads doubles each
     if (bd.kind == KAFKA_BAND_ARRAYS) {
 #pragma unroll
         for (int p = 0; p < P; ++p)
             J[p] = bd.src[p] >= 0 ? st[(3 + bd.src[p]) * kSolveThreads + threadIdx.x] : 0.0;
         h0 = st[2 * kSolveThreads + threadIdx.x];
+    } else if (bd.kind == KAFKA_BAND_UNIFORM) {
+        // one linearisation for the whole image, already laid out by state slot in shared memory
+        // (uni = {J[0..P-1], h0}): warp-wide broadcast reads, no branch; unobserved pixels keep
+        // an empty row (utils.py:199-215)
+        const bool on = w != 0.0;
+#pragma unroll
+        for (int p = 0; p < P; ++p) J[p] = on ? uni[p] : 0.0;
+        h0 = on ? uni[P] : 0.0;
     } else {
         band_row<P>(bd, 0, 0, xp, w, J, h0, round32, domain_bad);     // LINEAR / UNIFORM / WCM: nothing per pixel to load
     }
@@ -171,6 +179,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     constexpr int R = SolveBlock<P>::R;
     extern __shared__ __align__(16) double stages[];               // kAsyncStages x (3 + n_dim_max) x 128 [+ (L-R) x 128]
     __shared__ double s_part[2][kSolveThreads / 32];
+    __shared__ __align__(16) double s_uni[KAFKA_MAX_BANDS][P + 2];   // UNIFORM bands: Jacobian by state slot, then H0
     const int64_t tile0 = (int64_t)blockIdx.x * kSolveThreads;
     const int64_t i = tile0 + threadIdx.x;
     const int64_t ld = prm.ld;
@@ -194,6 +203,19 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     };
 #pragma unroll
     for (int b = 0; b < kAsyncStages - 1; ++b) issue(b);
+
+    bool any_uniform = false;
+    for (int b = 0; b < prm.n_bands; ++b) any_uniform |= prm.bands[b].kind == KAFKA_BAND_UNIFORM;
+    if (any_uniform) {                                              // same decision in every thread
+        for (int k = threadIdx.x; k < prm.n_bands * (P + 1); k += kSolveThreads) {
+            const int b = k / (P + 1), p = k - b * (P + 1);
+            const SolveBandDev& bd = prm.bands[b];
+            double v = 0.0;
+            if (bd.kind == KAFKA_BAND_UNIFORM) v = p == P ? bd.h0[0] : (bd.src[p] >= 0 ? bd.jac[bd.src[p]] : 0.0);
+            s_uni[b][p] = v;
+        }
+        __syncthreads();
+    }
 
     const int64_t il = live ? i : tile0;
     typename SolveBlock<P>::type A;
@@ -227,7 +249,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
         const double w = in_ld ? st[threadIdx.x] : 0.0;
         const double y = in_ld ? st[kSolveThreads + threadIdx.x] : 0.0;
         double J[P], h0;
-        band_row_staged<P>(bd, st, n_dim_max, xp, w, J, h0, round32, domain_bad);
+        band_row_staged<P>(bd, st, n_dim_max, s_uni[b], xp, w, J, h0, round32, domain_bad);
         double yp = y - h0;
 #pragma unroll
         for (int p = 0; p < P; ++p) yp = fma(J[p], xp[p], yp);

@@ -116,12 +116,17 @@ class DeviceVector(object):
             if self.n_pix == 0:
                 self._uniform = False
             else:
-                n_diff = torch.zeros(1, dtype=torch.int32, device=self.device)
+                # [pixel 0's vector | n_diff (i32) + padding], read back in one kafka_read_small
+                tmp = torch.zeros(self.n_params + 1, dtype=torch.float64, device=self.device)
+                n_diff = tmp[self.n_params:].view(torch.int32)[0:1]
                 with torch.cuda.device(self.device):
                     _lib.check(_lib.get_lib().kafka_state_uniform(_lib.ptr(self.data), self.ld, self.n_pix,
                                                                   self.n_params, _lib.ptr(n_diff), _lib.stream_ptr()),
                                "kafka_state_uniform")
-                self._uniform = self.data[:, 0].cpu().numpy() if int(n_diff.item()) == 0 else False
+                    tmp[:self.n_params].copy_(self.data[:, 0])
+                    host = _lib.read_small(tmp)
+                self._uniform = host[:self.n_params].copy() if int(host[self.n_params:].view(np.int32)[0]) == 0 \
+                    else False
         return None if self._uniform is False else self._uniform
 
     @classmethod
@@ -146,10 +151,12 @@ class DeviceVector(object):
     @classmethod
     def broadcast(cls, mean, n_pix, device=None):
         device = device or default_device()
-        mean = torch.as_tensor(np.asarray(mean, dtype=np.float64), device=device)
+        host = np.array(mean.detach().cpu().numpy() if isinstance(mean, torch.Tensor) else mean,
+                        dtype=np.float64).ravel()
+        mean = torch.as_tensor(host, device=device)
         out = cls.empty(n_pix, mean.numel(), device)
         out.data.copy_(mean[:, None].expand(-1, out.ld))
-        out._uniform = mean.cpu().numpy()
+        out._uniform = host                      # known without asking the device
         return out
 
     # -- properties ---------------------------------------------------------

@@ -62,8 +62,13 @@ def global_norm(sum_sq_local, n_elems_local, comm=None):
     if backend == "gloo" and buf.is_cuda:
         buf = buf.cpu()
     dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=comm)
-    buf = buf.cpu()
-    return float(np.sqrt(buf[0].item()) / buf[1].item()), float(buf[1].item())
+    if buf.is_cuda:
+        from . import _lib
+        with torch.cuda.stream(torch.cuda.current_stream(buf.device)):
+            tot = _lib.read_small(buf)           # no device->host memcpy: see kafka_read_small
+    else:
+        tot = buf.numpy()
+    return float(np.sqrt(tot[0]) / tot[1]), float(tot[1])
 
 
 def gather_interleaved(x_local, comm=None, dst=None):

@@ -243,9 +243,17 @@ class SolveWorkspace(object):
         self.ld = ld
         self.innov = torch.zeros((max(n_bands, 1), ld), dtype=torch.float64, device=device)
         self.fwd = torch.zeros((max(n_bands, 1), ld), dtype=torch.float64, device=device) if want_fwd else None
-        self.norm2 = torch.zeros(1, dtype=torch.float64, device=device)
-        self.n_bad = torch.zeros(1, dtype=torch.int32, device=device)
+        # the two scalars every solve leaves behind, side by side so that one kafka_read_small
+        # brings both to the host: [sum of squares (f64) | bad-pixel count (i32) + padding]
+        self.scalars = torch.zeros(2, dtype=torch.float64, device=device)
+        self.norm2 = self.scalars[0:1]
+        self.n_bad = self.scalars[1:2].view(torch.int32)[0:1]
         self.scratch = torch.empty(int(lib.kafka_solve_scratch_doubles(n_pix)), dtype=torch.float64, device=device)
+
+    def read_scalars(self):
+        """(sum of squares, bad-pixel count) of the last solve, waiting for it."""
+        host = _lib.read_small(self.scalars)
+        return float(host[0]), int(host[1:2].view(np.int32)[0])
 
 
 def make_solve_bands(descs, bufs):

@@ -273,8 +273,10 @@ class LinearKalman(object):
         """Convergence norm over ALL pixels (all ranks): linear_kf.py:293."""
         n_elems = self.n_state_elems * self.n_params
         if self.comm is None:
-            return float(np.sqrt(ws.norm2.item()) / float(n_elems)), float(n_elems)
+            ssq, self._n_bad_last = ws.read_scalars()
+            return float(np.sqrt(ssq) / float(n_elems)), float(n_elems)
         from .dist import global_norm
+        self._n_bad_last = None
         return global_norm(ws.norm2, n_elems, self.comm)
 
     def do_all_bands(self, timestep, current_data, x_forecast, P_forecast,
@@ -361,7 +363,7 @@ class LinearKalman(object):
             x_prev = x_analysis
             n_iter += 1
 
-        n_bad = int(ws.n_bad.item())
+        n_bad = self._n_bad_last if self._n_bad_last is not None else ws.read_scalars()[1]
         if n_bad and self._create_observation_operator.kind == "wcm":
             # the reference's forward model refuses such states (sar_forward_model.py:66-71)
             raise ValueError("%d pixels left the Water-Cloud model's domain (LAI <= 0 or SM <= 0) or have a "

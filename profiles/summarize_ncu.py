@@ -67,5 +67,35 @@ def main(rep, out, n_pix):
     print(open(out + ".txt").read())
 
 
+def launches(csv_path, out, command):
+    """Launch list of `ncu --metrics gpu__time_duration.sum --csv --log-file X <command>` -> per-kernel
+    count / total / mean / share table (python profiles/summarize_ncu.py launches X.csv out.txt "<command>")."""
+    rows = [r for r in csv.reader(open(csv_path)) if len(r) > 5]
+    hdr = rows[0]
+    ik, iv, iu = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Unit")
+    agg = {}
+    for r in rows[1:]:
+        try:
+            ms = float(r[iv].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(r[iu].strip(), 1e-6)
+        except ValueError:
+            continue
+        a = agg.setdefault(r[ik], [0, 0.0])
+        a[0] += 1
+        a[1] += ms
+    ours = {k: v for k, v in agg.items() if "kafka::" in k and "probe" not in k}
+    tot = sum(v[1] for v in ours.values())
+    with open(out, "w") as f:
+        f.write(command + "\n(per-launch times are cold-cache and serialised: compare SHARES)\n")
+        for k, (n, ms) in sorted(ours.items(), key=lambda kv: -kv[1][1]):
+            f.write("%-78s n=%3d total=%9.3f ms mean=%8.4f ms share_of_kafka_kernels=%5.1f%%\n"
+                    % (k[:78], n, ms, ms / n, 100.0 * ms / tot))
+        other = sum(v[1] for k, v in agg.items() if k not in ours)
+        f.write("everything else (torch elementwise kernels for synthetic data, peak probes): %.3f ms\n" % other)
+    print(open(out).read())
+
+
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2], int(sys.argv[3]) if len(sys.argv) > 3 else 0)
+    if sys.argv[1] == "launches":
+        launches(sys.argv[2], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "")
+    else:
+        main(sys.argv[1], sys.argv[2], int(sys.argv[3]) if len(sys.argv) > 3 else 0)
