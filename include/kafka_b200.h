@@ -88,6 +88,13 @@ int kafka_gather_band(const double* obs, const double* inv_var, const uint8_t* o
                       const int32_t* idx, int64_t n_pix, double* y, double* w, uint8_t* m_out,
                       void* stream);
 
+/* The same gather for all bands of one date in one launch: band b's rasters start
+ * at obs + b*raster_stride (likewise inv_var, obs_mask), its compacted rows at
+ * y + b*ld (likewise w, m_out).  Same values as n_bands calls of kafka_gather_band. */
+int kafka_gather_bands(const double* obs, const double* inv_var, const uint8_t* obs_mask,
+                       int64_t raster_stride, int n_bands, const int32_t* idx, int64_t n_pix,
+                       int64_t ld, double* y, double* w, uint8_t* m_out, void* stream);
+
 /* Observation ingest fused with the gather, replacing the arithmetic of
  * Sentinel2Observations.get_band_data
  * (kafka/input_output/Sentinel2_Observations.py:166-179): from the RAW surface

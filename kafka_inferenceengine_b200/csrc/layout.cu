@@ -124,6 +124,21 @@ __global__ void gather_band_kernel(const double* __restrict__ obs, const double*
     if (m_out) m_out[i] = m ? 1 : 0;
 }
 
+// all bands of one date in one launch (blockIdx.y = band): for small images the launch is the cost
+__global__ void gather_bands_kernel(const double* __restrict__ obs, const double* __restrict__ inv_var,
+                                    const uint8_t* __restrict__ obs_mask, int64_t raster_stride,
+                                    const int32_t* __restrict__ idx, int64_t n_pix, int64_t ld,
+                                    double* __restrict__ y, double* __restrict__ w, uint8_t* __restrict__ m_out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pix) return;
+    const int64_t src = (int64_t)blockIdx.y * raster_stride + idx[i];
+    const int64_t dst = (int64_t)blockIdx.y * ld + i;
+    const bool m = obs_mask[src] != 0;
+    y[dst] = m ? obs[src] : 0.0;
+    w[dst] = m ? inv_var[src] : 0.0;
+    if (m_out) m_out[dst] = m ? 1 : 0;
+}
+
 template <typename RawT>
 __global__ void gather_scaled_band_kernel(const RawT* __restrict__ raw, const uint8_t* __restrict__ ext_mask,
                                           const int32_t* __restrict__ idx, int64_t n_pix, double divisor,
@@ -282,6 +297,21 @@ int kafka_gather_band(const double* obs, const double* inv_var, const uint8_t* o
     gather_band_kernel<<<(unsigned)((n_pix + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
         obs, inv_var, obs_mask, idx, n_pix, y, w, m_out);
     return launch_status("gather_band");
+}
+
+int kafka_gather_bands(const double* obs, const double* inv_var, const uint8_t* obs_mask, int64_t raster_stride,
+                       int n_bands, const int32_t* idx, int64_t n_pix, int64_t ld, double* y, double* w,
+                       uint8_t* m_out, void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "kafka_gather_bands: need 0 <= n_pix <= ld");
+    KAFKA_CHECK_ARG(n_bands >= 0 && n_bands <= KAFKA_MAX_BANDS, "kafka_gather_bands: n_bands=%d outside 0..%d", n_bands,
+                    KAFKA_MAX_BANDS);
+    if (n_pix == 0 || n_bands == 0) return 0;
+    KAFKA_CHECK_ARG(obs && inv_var && obs_mask && idx && y && w, "kafka_gather_bands: null pointer");
+    const int threads = 256;
+    dim3 grid((unsigned)((n_pix + threads - 1) / threads), (unsigned)n_bands);
+    gather_bands_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(obs, inv_var, obs_mask, raster_stride, idx, n_pix, ld,
+                                                                    y, w, m_out);
+    return launch_status("gather_bands");
 }
 
 int kafka_gather_scaled_band(const void* raw, int raw_type, const uint8_t* ext_mask, const int32_t* idx,

@@ -73,6 +73,15 @@ class PixelIndex(object):
                                              _lib.ptr(self.idx), self.n_pix, _lib.ptr(y), _lib.ptr(w),
                                              _lib.ptr(m), _lib.stream_ptr()), "kafka_gather_band")
 
+    def gather_bands(self, obs, inv_var, obs_mask, n_bands, y, w, m):
+        """All bands of one date in one launch: (n_bands, n_raster) device rasters ->
+        (n_bands, ld) compacted rows."""
+        lib = _lib.get_lib()
+        with torch.cuda.device(self.device):
+            _lib.check(lib.kafka_gather_bands(_lib.ptr(obs), _lib.ptr(inv_var), _lib.ptr(obs_mask), obs.stride(0),
+                                              n_bands, _lib.ptr(self.idx), self.n_pix, y.stride(0), _lib.ptr(y),
+                                              _lib.ptr(w), _lib.ptr(m), _lib.stream_ptr()), "kafka_gather_bands")
+
     def scatter_output(self, x, a_packed, n_params, want_unc=True):
         """(n_params, ny, nx) float32 rasters of the mean and 1/sqrt(diag(P^-1))
         (input_output/observations.py:374-375,392-393)."""

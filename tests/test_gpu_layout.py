@@ -88,6 +88,29 @@ def test_gather_band_matches_oracle_and_gates_inf():
     assert np.isfinite(w[:n].cpu().numpy()).all()
 
 
+def test_gather_bands_one_launch_equals_per_band_gathers():
+    rng = np.random.default_rng(15)
+    mask = gio.barrax_mask()
+    pix = PixelIndex(mask, gu.DEV)
+    nb, n_r, n = 4, mask.size, pix.n_pix
+    obs = rng.random((nb, n_r))
+    omask = rng.random((nb, n_r)) < 0.7
+    with np.errstate(divide="ignore"):
+        inv = np.where(omask, 1.0 / (0.05 * obs) ** 2, np.inf)
+    d_obs, d_inv = torch.from_numpy(obs).to(gu.DEV), torch.from_numpy(inv).to(gu.DEV)
+    d_msk = torch.from_numpy(omask.astype(np.uint8)).to(gu.DEV)
+    y = torch.full((nb, pix.ld), -1.0, dtype=torch.float64, device=gu.DEV)
+    w = torch.full_like(y, -1.0)
+    m = torch.full((nb, pix.ld), 9, dtype=torch.uint8, device=gu.DEV)
+    pix.gather_bands(d_obs, d_inv, d_msk, nb, y, w, m)
+    for b in range(nb):
+        yo, ro, mo = kc.gather_band(obs[b].reshape(mask.shape), inv[b], omask[b].reshape(mask.shape), mask)
+        assert np.array_equal(y[b, :n].cpu().numpy(), yo)
+        assert np.array_equal(w[b, :n].cpu().numpy(), kc.gate_inverse_variance(ro, mo))
+        assert np.array_equal(m[b, :n].cpu().numpy().astype(bool), mo)
+    assert (y[:, n:] == -1.0).all() and (m[:, n:] == 9).all()          # padding columns untouched
+
+
 def test_scatter_output_matches_oracle():
     rng = np.random.default_rng(6)
     mask = gio.barrax_mask()
