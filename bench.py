@@ -519,6 +519,8 @@ def main():
     device = torch.device("cuda", local)
     comm = None
     if world > 1:
+        # stdout carries exactly one JSON line: NCCL's own banner / debug lines go to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=device)
         comm = dist.group.WORLD
 
