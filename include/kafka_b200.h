@@ -65,6 +65,8 @@ extern "C" {
 #define KAFKA_ROUND_F32 1u      /* round H0/J to float32 as the reference stores them \
                                    (kafka/inference/utils.py:193-195)                  */
 #define KAFKA_PRIOR_BROADCAST 2u /* pinv_f is ONE packed block shared by all pixels    */
+#define KAFKA_SOLVE_PAIR 4u       /* kafka_solve_bands: use the two-lanes-per-pixel kernel at any size
+                                    (it is the default at 16 parameters; for tests) */
 
 const char* kafka_last_error(void);
 int kafka_version(void);

@@ -21,6 +21,7 @@ BAND_WCM = 3
 RAW_I16, RAW_U16, RAW_F32 = 0, 1, 2
 ROUND_F32 = 1
 PRIOR_BROADCAST = 2
+SOLVE_PAIR = 4
 STATIC_SCRATCH_DOUBLES = 262144
 STATIC_MAX_PIXELS = 16777088
 

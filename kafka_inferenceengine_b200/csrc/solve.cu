@@ -163,8 +163,8 @@ constexpr int kAsyncStages = KAFKA_ASYNC_STAGES;
 // Packed entries kept in registers: all of them up to n_params 12 (78 entries).  For 13..15
 // the first 124 - 4 n_params stay in registers and the remaining rows live in the thread's
 // own shared-memory column (measured: 13 -> 74 %, 14 -> 61 %, 15 -> 46 % of the HBM peak,
-// against 70 / 55 / 37 % with everything in registers and spilling).  At 16 the column would
-// leave one 4-warp CTA per SM, which is slower than spilling; it stays in registers.
+// against 70 / 55 / 37 % with everything in registers and spilling).  16 is dispatched to the
+// two-lanes-per-pixel kernel of solve_pair.cuh instead.
 template <int P>
 struct SolveBlock {
     static constexpr int L = tri_count(P);
@@ -312,6 +312,10 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
         prm.partials[gridDim.x + blockIdx.x] = s1;
     }
 }
+
+}  // namespace kafka
+#include "solve_pair.cuh"
+namespace kafka {
 
 // Fixed-order second stage: same bits every run, whatever the launch order.
 __global__ void __launch_bounds__(256)
@@ -469,6 +473,22 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         if (prm.bands[b].kind == KAFKA_BAND_ARRAYS && prm.bands[b].n_planes > n_dim_max) n_dim_max = prm.bands[b].n_planes;
     const size_t ring = (size_t)kAsyncStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
     int rc = KAFKA_E_UNSUPPORTED;
+    if (n_params >= kPairFromParams || (flags & KAFKA_SOLVE_PAIR)) {
+        KAFKA_DISPATCH_P(n_params, {
+            auto kern = solve_bands_pair_kernel<kP>;
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring);
+            if (e != cudaSuccess) {
+                set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+                rc = (int)e;
+            } else {
+                kern<<<grid, kPairThreads, ring, s>>>(prm, n_dim_max);
+                rc = launch_status("solve_bands_pair_kernel");
+            }
+        });
+        if (rc != 0) return rc;
+        reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
+        return launch_status("reduce_partials_kernel");
+    }
     KAFKA_DISPATCH_P(n_params, {
         auto kern = solve_bands_kernel<kP>;
         const size_t smem = ring + (size_t)(SolveBlock<kP>::L - SolveBlock<kP>::R) * kSolveThreads * sizeof(double);

@@ -45,7 +45,21 @@ def _call(n, P, bands, x_prev, x_f, pinv_t, flags=0, want_fwd=True):
         w = gu.planar(bd["w"], ld)
         keep += [y, w]
         arr[b].y, arr[b].w = y.data_ptr(), w.data_ptr()
-        if "row" in bd:
+        if "wcm" in bd:
+            arr[b].kind = _lib.BAND_WCM
+            for k in range(6):
+                arr[b].row[k] = bd["wcm"][k]
+            arr[b].mapper[0], arr[b].mapper[1] = bd["mapper"]
+        elif "uni_J" in bd:
+            arr[b].kind = _lib.BAND_UNIFORM
+            J = torch.from_numpy(np.ascontiguousarray(bd["uni_J"], dtype=np.float64)).to(gu.DEV)
+            h0 = torch.tensor([bd["uni_H0"]], dtype=torch.float64, device=gu.DEV)
+            keep += [J, h0]
+            arr[b].jac, arr[b].h0 = J.data_ptr(), h0.data_ptr()
+            arr[b].n_dim = len(bd["mapper"])
+            for k, sl in enumerate(bd["mapper"]):
+                arr[b].mapper[k] = int(sl)
+        elif "row" in bd:
             arr[b].kind = _lib.BAND_LINEAR
             for p in range(P):
                 arr[b].row[p] = bd["row"][p]
@@ -78,15 +92,18 @@ def _call(n, P, bands, x_prev, x_f, pinv_t, flags=0, want_fwd=True):
             fwd[:B, :n].cpu().numpy().ravel(), float(norm2.item()), int(n_bad.item()))
 
 
+@pytest.mark.parametrize("pair", [False, True])
 @pytest.mark.parametrize("P", list(range(1, 17)))
-def test_supplied_jacobian_all_state_sizes(P):
-    """Config 5 sweep axis n_params 1..16 (x bands 1..13)."""
+def test_supplied_jacobian_all_state_sizes(P, pair):
+    """Config 5 sweep axis n_params 1..16 (x bands 1..13); ``pair`` forces the
+    two-lanes-per-pixel kernel (the default at 16 parameters) at every size."""
     rng = np.random.default_rng(P)
     B = 1 + (5 * P) % 13
     n = 1500 + 37 * P
     Js, H0s, ws, ys, Pinv, x_f, x_prev = _problem(rng, n, P, B)
     bands = [dict(J=Js[b], H0=H0s[b], y=ys[b], w=ws[b]) for b in range(B)]
-    x, A, innov, fwd, norm2, n_bad = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv))
+    x, A, innov, fwd, norm2, n_bad = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv),
+                                           flags=_lib.SOLVE_PAIR if pair else 0)
     xo, Ao, innov_o, fwd_o = kc.solve_dense64(ys, ws, H0s, Js, x_prev, x_f, Pinv)
     assert n_bad == 0
     assert np.max(gu.rel(A, Ao, floor=1e-6)) < RTOL
@@ -96,17 +113,59 @@ def test_supplied_jacobian_all_state_sizes(P):
     assert norm2 == pytest.approx(float(((xo - x_prev) ** 2).sum()), rel=1e-9)
 
 
-def test_norm_is_deterministic_and_edge_sizes():
+@pytest.mark.parametrize("P,flags", [(7, 0), (7, _lib.SOLVE_PAIR), (15, 0)])
+def test_norm_is_deterministic_and_edge_sizes(P, flags):
     rng = np.random.default_rng(99)
     for n in (1, 31, 128, 129, 5000):
-        P, B = 7, 2
+        B = 2
         Js, H0s, ws, ys, Pinv, x_f, x_prev = _problem(rng, n, P, B)
         bands = [dict(J=Js[b], H0=H0s[b], y=ys[b], w=ws[b]) for b in range(B)]
-        r1 = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv))
-        r2 = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv))
+        r1 = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv), flags=flags)
+        r2 = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv), flags=flags)
         assert r1[4] == r2[4] and np.array_equal(r1[0], r2[0]) and np.array_equal(r1[1], r2[1])
         xo, Ao, _, _ = kc.solve_dense64(ys, ws, H0s, Js, x_prev, x_f, Pinv)
         assert np.max(np.abs(r1[0] - xo) / np.maximum(np.abs(xo), 1e-3)) < RTOL
+
+
+@pytest.mark.parametrize("P", [2, 7, 14])
+def test_pair_kernel_on_uniform_linear_and_wcm_bands(P):
+    """Every band kind through both kernels: a shared linearisation (KAFKA_BAND_UNIFORM), a constant
+    row and (P=2) the Water-Cloud model; the two kernels agree to rounding and with the oracle."""
+    rng = np.random.default_rng(40 + P)
+    n = 1111
+    m = [rng.random(n) < 0.8 for _ in range(3)]
+    ws = [np.where(mm, 200.0, 0.0) for mm in m]
+    ys = [np.where(mm, rng.standard_normal(n), 0.0) for mm in m]
+    D = min(P, 4)
+    mapper = rng.permutation(P)[:D]
+    uJ, uH0 = rng.standard_normal(D), 0.37
+    row, off = rng.standard_normal(P), -0.2
+    Pinv = gu.random_spd(rng, n, P)
+    x_f = 1.0 + 0.1 * rng.standard_normal(n * P)
+    x_prev = x_f + 0.02 * rng.standard_normal(n * P)
+    bands = [dict(uni_J=uJ, uni_H0=uH0, mapper=mapper, y=ys[0], w=ws[0]), dict(row=row, offset=off, y=ys[1], w=ws[1])]
+    Jf = [np.zeros((n, P)), np.where(m[1][:, None], row[None, :], 0.0)]
+    Jf[0][:, mapper] = uJ
+    Jf[0][~m[0]] = 0.0
+    H0f = [np.where(m[0], uH0, 0.0), np.where(m[1], x_prev.reshape(n, P) @ row + off, 0.0)]
+    if P == 2:
+        prm = list(kc.WCM_PARAMETERS["VV"]) + [np.cos(np.deg2rad(23.0))]
+        bands.append(dict(wcm=prm, mapper=(0, 1), y=ys[2], w=ws[2]))
+        H0w, Jw = kc.sar_operator(x_prev, 2, m[2], 0, round_f32=False)
+        # sar_operator uses the VV constants of sar_forward_model.py:60; same numbers as prm
+        Jf.append(Jw)
+        H0f.append(H0w)
+    nb = len(bands)
+    res = [_call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv), flags=f) for f in (0, _lib.SOLVE_PAIR)]
+    assert np.allclose(res[0][0], res[1][0], rtol=1e-11, atol=1e-13)
+    assert np.array_equal(res[0][1], res[1][1]) and np.array_equal(res[0][2], res[1][2])
+    assert np.allclose(res[0][3], res[1][3], rtol=1e-11, atol=1e-12)
+    xo, Ao, innov_o, fwd_o = kc.solve_dense64(ys[:nb], ws[:nb], H0f, Jf, x_prev, x_f, Pinv)
+    for x, A, innov, fwd, norm2, n_bad in res:
+        assert n_bad == 0
+        assert np.max(gu.rel(A, Ao, floor=1e-6)) < 1e-8
+        assert np.max(np.abs(x - xo) / np.maximum(np.abs(xo), 1e-3)) < 1e-8
+        assert np.allclose(innov, innov_o, rtol=1e-9, atol=1e-10)
 
 
 def test_no_bands_and_empty_image():
@@ -123,7 +182,8 @@ def test_no_bands_and_empty_image():
     assert st == 0 and norm2.item() == 0.0 and nb.item() == 0
 
 
-def test_mapper_linear_and_broadcast_prior():
+@pytest.mark.parametrize("pair", [0, _lib.SOLVE_PAIR])
+def test_mapper_linear_and_broadcast_prior(pair):
     """TIP layout: band Jacobians live on 4 of 7 slots (utils.py:148-153); a linear
     band in tuple form; one prior block shared by all pixels (kafka_test_S2.py:106-118)."""
     rng = np.random.default_rng(5)
@@ -143,7 +203,7 @@ def test_mapper_linear_and_broadcast_prior():
     bands.append(dict(row=row, offset=off, y=ys[2], w=ws[2]))
     r, c = np.tril_indices(P)
     pinv_b = torch.from_numpy(np.ascontiguousarray(inv.astype(np.float64)[r, c])).to(gu.DEV)
-    x, A, innov, fwd, norm2, n_bad = _call(n, P, bands, x_prev, x_f, pinv_b, flags=_lib.PRIOR_BROADCAST)
+    x, A, innov, fwd, norm2, n_bad = _call(n, P, bands, x_prev, x_f, pinv_b, flags=_lib.PRIOR_BROADCAST | pair)
     Jf = []
     for b in range(2):
         J = np.zeros((n, P))
@@ -160,15 +220,16 @@ def test_mapper_linear_and_broadcast_prior():
     assert np.allclose(fwd, fwd_o, rtol=1e-9, atol=1e-10)
 
 
-def test_non_positive_definite_blocks_are_flagged():
+@pytest.mark.parametrize("P,flags", [(4, 0), (4, _lib.SOLVE_PAIR), (13, 0)])
+def test_non_positive_definite_blocks_are_flagged(P, flags):
     rng = np.random.default_rng(8)
-    n, P = 500, 4
+    n = 500
     Js, H0s, ws, ys, Pinv, x_f, x_prev = _problem(rng, n, P, 1)
     Pinv[7] = -Pinv[7]
     Pinv[300] = 0.0
     ws[0][300] = 0.0
     bands = [dict(J=Js[0], H0=H0s[0], y=ys[0], w=ws[0])]
-    x, A, _, _, norm2, n_bad = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv))
+    x, A, _, _, norm2, n_bad = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv), flags=flags)
     assert n_bad == 2
     xr = x.reshape(n, P)
     assert np.array_equal(xr[7], x_f.reshape(n, P)[7]) and np.array_equal(xr[300], x_f.reshape(n, P)[300])
