@@ -86,7 +86,9 @@ class ObservationStager(object):
     iteration loop).  Buffers are allocated once and reused across dates."""
 
     # staging threads: up to 8, but never more than this rank's share of the host cores
-    N_THREADS = max(2, min(8, (os.cpu_count() or 8) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))))
+    # (KAFKA_STAGE_THREADS overrides)
+    N_THREADS = int(os.environ.get("KAFKA_STAGE_THREADS", 0)) or \
+        max(2, min(8, (os.cpu_count() or 8) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))))
     N_SLOTS = 2
 
     def __init__(self, pix):
