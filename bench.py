@@ -611,7 +611,16 @@ def main():
         n_warm = max(2, args.warmup)
         all_dates = [base + dt.timedelta(days=d, hours=12) for d in range(n_warm + args.steps)]
         obs_host = HostObservations(all_dates, gps, rho, inv, mask, shape)
-        out = RasterOutput(syn.S2_PARAMETERS)          # float32 mean + 1/sqrt(diag) rasters, read back to the host
+        class TimedRasterOutput(RasterOutput):
+            """RasterOutput that notes when each date is handed over (host clock)."""
+            stamps = None
+
+            def dump_data(self, *a, **k):
+                if self.stamps is not None:
+                    self.stamps.append(time.perf_counter())
+                return RasterOutput.dump_data(self, *a, **k)
+
+        out = TimedRasterOutput(syn.S2_PARAMETERS)     # float32 mean + 1/sqrt(diag) rasters, read back to the host
         kf2, prior2 = make_filter(obs_host, out)
         out.pixels = kf2.pixels
         kf2.set_trajectory_uncertainty(0.0)
@@ -623,14 +632,22 @@ def main():
         kf2.run(grid_warm, x0h, None, Pinv0h, iter_obs_op=True)
         barrier()
         h2d0, d2h0 = kf2._stager.h2d_bytes, out.d2h_bytes
+        out.stamps = []
         t0 = time.perf_counter()
         kf2.run(grid_timed, x0h, None, Pinv0h, iter_obs_op=True)
         torch.cuda.synchronize()
         ms_e2e = max_over_ranks(1e3 * (time.perf_counter() - t0)) / args.steps
+        gaps = np.diff(out.stamps)
+        ms_steady = max_over_ranks(1e3 * float(np.median(gaps))) if len(gaps) else None
+        out.stamps = None
         barrier()
         e2e = {"value": world * n_pix / (ms_e2e * 1e-3), "unit": "pixel-dates/s", "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": (kf2._stager.h2d_bytes - h2d0) // args.steps,
                "d2h_bytes_per_step": (out.d2h_bytes - d2h0) // args.steps,
+               "steady_state_ms_per_step": ms_steady,
+               "steady_state_note": "median interval between successive dates inside the same run(); value/ms_per_step "
+                                    "are the WHOLE call / K and also carry the first date's staging, which nothing can "
+                                    "hide behind, and the last date's read-back",
                "api": "one LinearKalman.run(time_grid, x_forecast, None, P_forecast_inverse) over %d dates: host numpy "
                       "rasters from observations.get_band_data (pageable, float64 obs + inverse variance + bool mask) "
                       "copied host->device every date, prior-only advance, output.dump_data = RasterOutput "

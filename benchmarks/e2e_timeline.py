@@ -26,6 +26,9 @@ from kafka_inferenceengine_b200.output import RasterOutput  # noqa: E402
 ACC = collections.defaultdict(float)
 
 
+LOG = []            # (tag, start, end) of every timed call, seconds
+
+
 def timed(cls, name, tag):
     fn = getattr(cls, name)
 
@@ -34,7 +37,9 @@ def timed(cls, name, tag):
         try:
             return fn(*a, **k)
         finally:
-            ACC[tag] += time.perf_counter() - t0
+            t1 = time.perf_counter()
+            ACC[tag] += t1 - t0
+            LOG.append((tag, t0, t1))
     setattr(cls, name, wrap)
 
 
@@ -64,6 +69,21 @@ def main():
     kf.run([base + dt.timedelta(days=d) for d in range(n_warm + 1)], x0, None, Pinv0, iter_obs_op=True)
     torch.cuda.synchronize()
 
+    # device-side timeline: when do the H2D copies of the NEXT date start/end relative to the
+    # start of the emulator pass they are meant to hide behind?
+    marks = []
+    orig_stage = engine.ObservationStager.stage
+
+    def stage_marked(self, data):
+        e_gp = torch.cuda.Event(enable_timing=True)
+        e_gp.record(torch.cuda.current_stream())          # main stream: emulator + solve of iteration 2 are queued
+        tok = orig_stage(self, data)
+        e_end = torch.cuda.Event(enable_timing=True)
+        if self._copy_stream is not None:
+            e_end.record(self._copy_stream)
+        marks.append((e_gp, e_end))
+        return tok
+    engine.ObservationStager.stage = stage_marked
     timed(kb.LinearKalman, "_read_bands", "read_bands")
     timed(engine.ObservationStager, "stage", "stage (host copies + queue H2D)")
     timed(engine.ObservationStager, "finish", "finish (queue gathers)")
@@ -90,6 +110,16 @@ def main():
     for k, v in ACC.items():
         print("  %-44s %8.2f ms/date" % (k, 1e3 * v / steps))
     print("  iterations", kf.last_iterations[-steps:])
+    if os.environ.get("KAFKA_TIMELINE_LOG"):
+        z = LOG[0][1]
+        for tag, a, b in LOG:
+            print("    %8.2f -> %8.2f ms  %s" % (1e3 * (a - z), 1e3 * (b - z), tag))
+    for e_gp, e_end in marks:
+        try:
+            print("  H2D of the next date done %.1f ms after the main stream finished the current date's kernels"
+                  % e_gp.elapsed_time(e_end))
+        except Exception as exc:
+            print("  (no mark: %s)" % exc)
     for k, v in kf.profile.items():
         print("  GPU %-40s %8.2f ms/date (CUDA events)" % (k, sum(a.elapsed_time(b) for a, b in v) / steps))
 
