@@ -27,6 +27,11 @@ VARIANTS = {
     "tab256_checked": ["-DKAFKA_EXP_CLAMP=0", "-DKAFKA_EXP_LOG2N=8"],
     "tab256": ["-DKAFKA_EXP_LOG2N=8"],
     "checked": ["-DKAFKA_EXP_CLAMP=0"],
+    "u1_mb4": ["-DKAFKA_GP_UNROLL=1", "-DKAFKA_GP_MINBLOCKS=4"],
+    "u2_mb4": ["-DKAFKA_GP_UNROLL=2", "-DKAFKA_GP_MINBLOCKS=4"],
+    "u4_mb4": ["-DKAFKA_GP_UNROLL=4", "-DKAFKA_GP_MINBLOCKS=4"],
+    "u8": ["-DKAFKA_GP_UNROLL=8"],
+    "u5": ["-DKAFKA_GP_UNROLL=5"],
 }
 if os.environ.get("KAFKA_GP_VARIANTS"):
     VARIANTS = {k: v for k, v in VARIANTS.items() if k in os.environ["KAFKA_GP_VARIANTS"].split(",")}
