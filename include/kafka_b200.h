@@ -230,7 +230,8 @@ int64_t kafka_solve_scratch_doubles(int64_t n_pix);
  *     rhs  = sum_b w_b y'_b J_b + Pinv_f x_f
  *     x    = A^-1 rhs   (fp64 Cholesky per pixel)   (written to x_out)
  *     *norm2 = sum_i sum_p (x - x_prev)^2           (deterministic two-stage sum)
- * Optional outputs (may be NULL): innovations[b*ld+i] = y_b - H0_b
+ * Optional outputs (may be NULL): a_out (an iteration that cannot be the last
+ * one needs no A), innovations[b*ld+i] = y_b - H0_b
  * (solvers.py:142), fwd[b*ld+i] = J_b.(x - x_f) + H0_b (solvers.py:137),
  * n_bad = number of pixels whose block was not positive definite (their x is
  * left at x_f).  `scratch` holds kafka_solve_scratch_doubles(n_pix) doubles.

@@ -266,8 +266,10 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     cp_async_wait<0>();
 
     if (live) {
+        if (prm.a_out) {
 #pragma unroll
-        for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A.get(c));
+            for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A.get(c));
+        }
         double invd[P];
         const bool ok = chol_factor_blk<P>(A, invd) && !domain_bad;
         chol_solve_blk<P>(A, invd, rhs);
@@ -414,7 +416,7 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         if (n_bad) KAFKA_CUDA(cudaMemsetAsync(n_bad, 0, sizeof(int32_t), s));
         return 0;
     }
-    KAFKA_CHECK_ARG(x_prev && x_f && pinv_f && x_out && a_out && scratch, "kafka_solve_bands: null pointer");
+    KAFKA_CHECK_ARG(x_prev && x_f && pinv_f && x_out && scratch, "kafka_solve_bands: null pointer");
     SolveParams prm;
     memset(&prm, 0, sizeof(prm));
     for (int b = 0; b < n_bands; ++b) {

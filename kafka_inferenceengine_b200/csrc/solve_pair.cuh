@@ -175,7 +175,7 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
     }
     cp_async_wait<0>();
 
-    if (live) {
+    if (live && prm.a_out) {
 #pragma unroll
         for (int k = 0; k < K; ++k)
 #pragma unroll

@@ -335,7 +335,7 @@ def solve_bands(ws, descs, bufs, x_prev, x_f, pinv_f, x_out, a_out, want_fwd=Fal
     with torch.cuda.device(ws.device):
         _lib.check(lib.kafka_solve_bands(ws.n_pix, ws.ld, ws.n_params, arr, len(descs), _lib.ptr(x_prev.data),
                                          _lib.ptr(x_f.data), _lib.ptr(pinv_f.data), _lib.ptr(x_out.data),
-                                         _lib.ptr(a_out.data), _lib.ptr(ws.innov),
+                                         _lib.ptr(a_out.data) if a_out is not None else None, _lib.ptr(ws.innov),
                                          _lib.ptr(ws.fwd) if want_fwd else None, _lib.ptr(ws.norm2),
                                          _lib.ptr(ws.n_bad), _lib.ptr(ws.scratch), flags, _lib.stream_ptr()),
                    "kafka_solve_bands")

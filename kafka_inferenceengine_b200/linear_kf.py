@@ -337,7 +337,10 @@ class LinearKalman(object):
                         descs[g[0]] = ("arrays", hsub[k], jsub[k], g[2])
                 x_new = bufsx[(n_iter - 1) % 2]
                 ev = self._tick("solve_bands" if shared is None else "solve_bands_shared_linearisation")
-                engine.solve_bands(ws, descs, bufs, x_prev, x_forecast, P_forecast_inverse, x_new, a_out,
+                # an iteration below min_iterations cannot be the last one (linear_kf.py:296): its A
+                # would be overwritten unread, so it is not stored
+                engine.solve_bands(ws, descs, bufs, x_prev, x_forecast, P_forecast_inverse, x_new,
+                                   a_out if (n_iter >= min_iterations or n_iter > 25 or all_linear) else None,
                                    want_fwd=self.want_forward_modelled, round_f32=self.round_operator_f32)
                 self._tock(ev)
                 if shared is None or n_iter >= 2:
