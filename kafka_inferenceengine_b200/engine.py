@@ -328,14 +328,16 @@ def make_solve_bands(descs, bufs):
 def solve_bands(ws, descs, bufs, x_prev, x_f, pinv_f, x_out, a_out, want_fwd=False, round_f32=False):
     """One linearised update (kafka_solve_bands).  Results land in ``x_out``,
     ``a_out``, ``ws.innov``, ``ws.fwd``; ``ws.norm2`` / ``ws.n_bad`` stay on the
-    device until the caller reads them."""
+    device until the caller reads them.  ``a_out=None`` marks an iteration whose
+    A, innovations and forward-modelled values nobody will read: none is stored."""
     lib = _lib.get_lib()
     arr = make_solve_bands(descs, bufs)
     flags = (_lib.PRIOR_BROADCAST if pinv_f.is_broadcast else 0) | (_lib.ROUND_F32 if round_f32 else 0)
     with torch.cuda.device(ws.device):
         _lib.check(lib.kafka_solve_bands(ws.n_pix, ws.ld, ws.n_params, arr, len(descs), _lib.ptr(x_prev.data),
                                          _lib.ptr(x_f.data), _lib.ptr(pinv_f.data), _lib.ptr(x_out.data),
-                                         _lib.ptr(a_out.data) if a_out is not None else None, _lib.ptr(ws.innov),
-                                         _lib.ptr(ws.fwd) if want_fwd else None, _lib.ptr(ws.norm2),
+                                         _lib.ptr(a_out.data) if a_out is not None else None,
+                                         _lib.ptr(ws.innov) if a_out is not None else None,
+                                         _lib.ptr(ws.fwd) if (want_fwd and a_out is not None) else None, _lib.ptr(ws.norm2),
                                          _lib.ptr(ws.n_bad), _lib.ptr(ws.scratch), flags, _lib.stream_ptr()),
                    "kafka_solve_bands")

@@ -291,6 +291,11 @@ class LinearKalman(object):
         P_forecast_inverse = self._precision(P_forecast_inverse)
         n_bands = len(current_data)
         ws = self._workspace(n_bands)
+        # the per-band outputs are handed to the caller at the end: fresh buffers per call
+        # instead of a copy out of the workspace
+        ws.innov = torch.zeros_like(ws.innov)
+        if ws.fwd is not None:
+            ws.fwd = torch.zeros_like(ws.fwd)
         token = getattr(self, "_token", None)
         self._token = None
         bufs = self._stager.finish(token if token is not None else self._stager.stage(current_data))
@@ -384,8 +389,8 @@ class LinearKalman(object):
                     P, [g[2] for g in group], self.device, a_inout=a_out, want_corr=False)
         self.last_iterations.append(n_iter - 1)
         self.last_norms.append(norms)
-        innovations = DeviceBands(ws.innov.clone(), n)
-        self.fwd_modelled = DeviceBands(ws.fwd.clone(), n) if self.want_forward_modelled else None
+        innovations = DeviceBands(ws.innov, n)
+        self.fwd_modelled = DeviceBands(ws.fwd, n) if self.want_forward_modelled else None
         return x_analysis, None, a_out, innovations
 
     # ------------------------------------------------------------------
