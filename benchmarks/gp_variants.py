@@ -32,6 +32,10 @@ VARIANTS = {
     "u4_mb4": ["-DKAFKA_GP_UNROLL=4", "-DKAFKA_GP_MINBLOCKS=4"],
     "u8": ["-DKAFKA_GP_UNROLL=8"],
     "u5": ["-DKAFKA_GP_UNROLL=5"],
+    "ppt3": ["-DKAFKA_GP_PPT_BIG=3"],
+    "ppt3_t96": ["-DKAFKA_GP_PPT_BIG=3", "-DKAFKA_GP_THREADS=96"],
+    "ppt4": ["-DKAFKA_GP_PPT_BIG=4"],
+    "ppt4_t64": ["-DKAFKA_GP_PPT_BIG=4", "-DKAFKA_GP_THREADS=64"],
 }
 if os.environ.get("KAFKA_GP_VARIANTS"):
     VARIANTS = {k: v for k, v in VARIANTS.items() if k in os.environ["KAFKA_GP_VARIANTS"].split(",")}

@@ -164,6 +164,10 @@ struct GpLinParams {
 #ifndef KAFKA_GP_FORCE_PPT
 #define KAFKA_GP_FORCE_PPT 0
 #endif
+#ifndef KAFKA_GP_PPT_BIG
+#define KAFKA_GP_PPT_BIG 2    // pixels per thread on large images
+#endif
+constexpr int kGpPptBig = KAFKA_GP_PPT_BIG;
 constexpr int kGpThreads = KAFKA_GP_THREADS;
 constexpr int kGpUnroll = KAFKA_GP_UNROLL;
 
@@ -512,11 +516,11 @@ template <int D>
 static int dispatch_ppt(const GpLinParams& prm, int n_bands, int max_T, cudaStream_t s) {
     // two pixels per thread halve the shared-memory operand traffic per FMA; only
     // worth it when the grid still fills the machine several times over
-    int64_t ctas2 = (prm.n_pix + 2 * kGpThreads - 1) / (2 * kGpThreads) * n_bands;
+    int64_t ctas2 = (prm.n_pix + kGpPptBig * kGpThreads - 1) / (kGpPptBig * kGpThreads) * n_bands;
     bool two = ctas2 >= 8 * (int64_t)num_sms();
     if (KAFKA_GP_FORCE_PPT == 1) two = false;
     if (KAFKA_GP_FORCE_PPT == 2) two = true;
-    if (two) return launch_linearize<D, 2>(prm, n_bands, max_T, s);
+    if (two) return launch_linearize<D, kGpPptBig>(prm, n_bands, max_T, s);
     return launch_linearize<D, 1>(prm, n_bands, max_T, s);
 }
 
