@@ -301,7 +301,7 @@ def run_reference(args):
                              "sample": "%d px per step, all bands, iterated to convergence (%s solves)"
                                        % (n_sample, sorted(set(iters)))},
             "e2e": {"value": value, "unit": "pixel-dates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(json.dumps(line))
 
 
 def workload_config(args, note=None):
@@ -372,7 +372,7 @@ def run_other_workload(args):
             kf.run(grid, x0, None, P0, iter_obs_op=True)
         torch.cuda.synchronize()
         ms = 1e3 * (time.perf_counter() - t0) / args.steps
-        print(json.dumps({"workload": "c2: Barrax mask 13027 px, P=10, B=10, T=250, 20 dates, LinearKalman.run with host "
+        emit(json.dumps({"workload": "c2: Barrax mask 13027 px, P=10, B=10, T=250, 20 dates, LinearKalman.run with host "
                                       "rasters, end to end", "metric": "pixel-dates/sec",
                           "value": N * n_dates / (ms * 1e-3), "ms_per_run": ms, "ms_per_date": ms / n_dates,
                           "iterations": kf.last_iterations[-n_dates:], "n_gpus": 1}))
@@ -425,7 +425,7 @@ def run_other_workload(args):
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
             os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm = float(peaks.get("hbm_gbs", 6650.0))
-        print(json.dumps({"workload": "c3: MODIS tile 2400x2400 (5.76 M px), TIP P=7, B=2 (D=4, T=500), %d daily steps, "
+        emit(json.dumps({"workload": "c3: MODIS tile 2400x2400 (5.76 M px), TIP P=7, B=2 (D=4, T=500), %d daily steps, "
                                       "observations every 8th day, LAI propagator; device-resident rasters" % n_steps,
                           "metric": "pixel-steps/sec", "value": N * n_steps / (ms * 1e-3), "ms_per_step": ms / n_steps,
                           "pixel_dates_per_s": N * len(dates) / (ms * 1e-3), "iterations": kf.last_iterations,
@@ -478,7 +478,7 @@ def run_other_workload(args):
                 rows.append({"n_params": Pn, "n_bands": Bn, "ms": ms, "Mpx_per_s": n / ms / 1e3,
                              "GBs": n * bytes_pp / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": n * bytes_pp / (ms * 1e-3) / 1e9 / hbm})
                 del J, h0, y, w, xp, xf, pinv, xo, ao
-        print(json.dumps({"workload": "c5: batched update with supplied Jacobians, 4 M px, per-pixel prior blocks",
+        emit(json.dumps({"workload": "c5: batched update with supplied Jacobians, 4 M px, per-pixel prior blocks",
                           "metric": "pixels/sec", "rows": rows, "n_gpus": 1}))
 
 
@@ -765,10 +765,45 @@ def main():
                                "later iterations evaluate every pixel",
             "value_without_shared_first_linearisation": world * n_pix / (ms_nodedup * 1e-3),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
-    print(json.dumps(line))
+    emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
+class _QuietStdout(object):
+    """Everything written to file descriptor 1 while the bench runs -- by Python or by a C
+    library such as NCCL's version banner -- goes to stderr; the JSON line is written to the
+    real stdout at the end, so stdout carries exactly one line."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.real = os.dup(1)
+        os.dup2(2, 1)
+        self.lines = []
+        return self
+
+    def emit(self, text):
+        self.lines.append(text)
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.real, 1)
+        os.close(self.real)
+        for text in self.lines:
+            print(text, flush=True)
+        return False
+
+
+_OUT = None
+
+
+def emit(text):
+    if _OUT is None:
+        print(text, flush=True)
+    else:
+        _OUT.emit(text)
+
+
 if __name__ == "__main__":
-    main()
+    with _QuietStdout() as _OUT:
+        main()
