@@ -60,6 +60,7 @@ extern "C" {
 #define KAFKA_RAW_I16 0
 #define KAFKA_RAW_U16 1
 #define KAFKA_RAW_F32 2
+#define KAFKA_RAW_F64 3 /* kafka_gather_bhr_band only */
 
 /* flags */
 #define KAFKA_ROUND_F32 1u      /* round H0/J to float32 as the reference stores them \
@@ -118,6 +119,21 @@ int kafka_gather_scaled_band(const void* raw, int raw_type, const uint8_t* ext_m
 int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, int64_t n_pix,
                          int n_params, const int32_t* idx, int64_t n_raster, float* mean_raster,
                          float* unc_raster, void* stream);
+
+/* Observation ingest of the MODIS broadband-albedo reader fused with the gather,
+ * replacing the arithmetic of BHRObservations.get_band_data
+ * (kafka/input_output/observations.py:288-310).  kernels: the band's three BRDF
+ * kernel weights (isotropic, volumetric, geometric), plane k at
+ * kernels + k*plane_stride elements, KAFKA_RAW_F32 or KAFKA_RAW_F64; mask, qa:
+ * uint8 rasters (qa = MCD43A2 quality level).
+ *   bhr   = (k0*1.0 + k1*0.189184) + k2*(-1.377622)    (rounded step by step, as numpy)
+ *   sigma = max(2.5e-3, 0.05 bhr) if qa == 0, max(2.5e-3, 0.07 bhr) if qa == 1, else 0
+ *   m = mask[idx];  y = m ? bhr : 0;  w = m ? 1/sigma^2 : 0
+ * A pixel with its mask set and qa outside {0,1} gets w = inf, exactly as the
+ * reader's 1/R^2 does. */
+int kafka_gather_bhr_band(const void* kernels, int kernel_type, int64_t plane_stride,
+                          const uint8_t* mask, const uint8_t* qa, const int32_t* idx,
+                          int64_t n_pix, double* y, double* w, uint8_t* m_out, void* stream);
 
 /* Number of pixels whose state differs (bitwise) from pixel 0's: 0 means every
  * pixel holds the same vector, which is what run_emulator's de-duplication

@@ -12,6 +12,6 @@ from .device import BlockDiag, DeviceVector, PixelIndex    # noqa: F401
 from .inference import *                                   # noqa: F401,F403
 from .linear_kf import LinearKalman                        # noqa: F401
 from .observation_operators import *                       # noqa: F401,F403
-from .engine import ScaledReflectance                      # noqa: F401
+from .engine import BHRKernelWeights, ScaledReflectance    # noqa: F401
 
 __version__ = "0.1.0"

@@ -18,7 +18,7 @@ BAND_ARRAYS = 0
 BAND_LINEAR = 1
 BAND_UNIFORM = 2
 BAND_WCM = 3
-RAW_I16, RAW_U16, RAW_F32 = 0, 1, 2
+RAW_I16, RAW_U16, RAW_F32, RAW_F64 = 0, 1, 2, 3
 ROUND_F32 = 1
 PRIOR_BROADCAST = 2
 SOLVE_PAIR = 4
@@ -51,6 +51,7 @@ SIGNATURES = {
     "kafka_compact_mask": (C.c_int, [_p, _i64, _p, _i64, _p, C.POINTER(C.c_int64), _p]),
     "kafka_gather_band": (C.c_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p]),
     "kafka_gather_bands": (C.c_int, [_p, _p, _p, _i64, _i32, _p, _i64, _i64, _p, _p, _p, _p]),
+    "kafka_gather_bhr_band": (C.c_int, [_p, _i32, _i64, _p, _p, _p, _i64, _p, _p, _p, _p]),
     "kafka_gather_scaled_band": (C.c_int, [_p, _i32, _p, _p, _i64, C.c_double, C.c_double, _p, _p, _p, _p]),
     "kafka_scatter_output": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p, _p, _p]),
     "kafka_state_uniform": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),

@@ -139,6 +139,31 @@ __global__ void gather_bands_kernel(const double* __restrict__ obs, const double
     if (m_out) m_out[dst] = m ? 1 : 0;
 }
 
+// MODIS broadband-albedo ingest (observations.py:288-310).  Products and sums are rounded one by
+// one (__dmul_rn / __dadd_rn: no FMA contraction), in numpy's order, so the result is bit-identical
+// to the reader's.
+template <typename KT>
+__global__ void gather_bhr_band_kernel(const KT* __restrict__ kernels, int64_t plane_stride,
+                                       const uint8_t* __restrict__ mask, const uint8_t* __restrict__ qa,
+                                       const int32_t* __restrict__ idx, int64_t n_pix, double* __restrict__ y,
+                                       double* __restrict__ w, uint8_t* __restrict__ m_out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pix) return;
+    const int32_t j = idx[i];
+    const bool m = mask[j] != 0;
+    const double k0 = (double)kernels[j], k1 = (double)kernels[plane_stride + j], k2 = (double)kernels[2 * plane_stride + j];
+    const double bhr = __dadd_rn(__dadd_rn(__dmul_rn(k0, 1.0), __dmul_rn(k1, 0.189184)), __dmul_rn(k2, -1.377622));
+    const uint8_t q = qa[j];
+    double sigma = 0.0;                                            // R_mat = zeros_like(bhr)        (:299)
+    // np.maximum(2.5e-3, v): unlike fmax it hands a NaN through
+    auto np_maximum = [](double v) { return (v > 2.5e-3 || v != v) ? v : 2.5e-3; };
+    if (q == 0) sigma = np_maximum(__dmul_rn(bhr, 0.05));          // (:301)
+    if (q == 1) sigma = np_maximum(__dmul_rn(bhr, 0.07));          // (:302)
+    y[i] = m ? bhr : 0.0;
+    w[i] = m ? 1.0 / __dmul_rn(sigma, sigma) : 0.0;                // 1/R^2 (:306); mask set but qa > 1 -> inf, as the reader
+    if (m_out) m_out[i] = m ? 1 : 0;
+}
+
 template <typename RawT>
 __global__ void gather_scaled_band_kernel(const RawT* __restrict__ raw, const uint8_t* __restrict__ ext_mask,
                                           const int32_t* __restrict__ idx, int64_t n_pix, double divisor,
@@ -312,6 +337,27 @@ int kafka_gather_bands(const double* obs, const double* inv_var, const uint8_t* 
     gather_bands_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(obs, inv_var, obs_mask, raster_stride, idx, n_pix, ld,
                                                                     y, w, m_out);
     return launch_status("gather_bands");
+}
+
+int kafka_gather_bhr_band(const void* kernels, int kernel_type, int64_t plane_stride, const uint8_t* mask,
+                          const uint8_t* qa, const int32_t* idx, int64_t n_pix, double* y, double* w, uint8_t* m_out,
+                          void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0, "kafka_gather_bhr_band: n_pix < 0");
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(kernels && mask && qa && idx && y && w, "kafka_gather_bhr_band: null pointer");
+    KAFKA_CHECK_ARG(plane_stride > 0, "kafka_gather_bhr_band: plane_stride must be positive");
+    const int threads = 256;
+    const unsigned grid = (unsigned)((n_pix + threads - 1) / threads);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (kernel_type == KAFKA_RAW_F32)
+        gather_bhr_band_kernel<float><<<grid, threads, 0, s>>>((const float*)kernels, plane_stride, mask, qa, idx, n_pix, y, w, m_out);
+    else if (kernel_type == KAFKA_RAW_F64)
+        gather_bhr_band_kernel<double><<<grid, threads, 0, s>>>((const double*)kernels, plane_stride, mask, qa, idx, n_pix, y, w, m_out);
+    else {
+        set_error("kafka_gather_bhr_band: kernel_type %d is neither KAFKA_RAW_F32 nor KAFKA_RAW_F64", kernel_type);
+        return KAFKA_E_BADARG;
+    }
+    return launch_status("gather_bhr_band");
 }
 
 int kafka_gather_scaled_band(const void* raw, int raw_type, const uint8_t* ext_mask, const int32_t* idx,

@@ -41,6 +41,21 @@ class ScaledReflectance(object):
         self.rel_sigma = float(rel_sigma)
 
 
+class BHRKernelWeights(object):
+    """Marker passed in the ``uncertainty`` field of a band whose ``observations``
+    are the three BRDF kernel weights ``(3, ny, nx)`` (float32 or float64) of a
+    MODIS broadband: the arithmetic of ``BHRObservations.get_band_data``
+    (input_output/observations.py:288-310: bi-hemispherical reflectance, sigma =
+    max(2.5e-3, 5 % or 7 % of it by quality level, 1/sigma^2) then runs on the
+    device fused with the compaction gather.  ``qa_level`` is the MCD43A2 quality
+    raster (integers); the band's ``mask`` is the reader's boolean mask."""
+
+    KERNEL_TYPES = {np.dtype(np.float32): _lib.RAW_F32, np.dtype(np.float64): _lib.RAW_F64}
+
+    def __init__(self, qa_level):
+        self.qa_level = np.asarray(qa_level)
+
+
 class _Slot(object):
     """One set of pinned staging buffers + device rasters."""
 
@@ -64,11 +79,12 @@ class _Slot(object):
 
 class StagedDate(object):
     """Hand-over between ``stage`` and ``finish``."""
-    __slots__ = ("slot", "n_bands", "device_data", "raw", "one_event")
+    __slots__ = ("slot", "n_bands", "device_data", "raw", "one_event", "bhr")
 
-    def __init__(self, slot, n_bands, device_data=None, raw=None, one_event=False):
+    def __init__(self, slot, n_bands, device_data=None, raw=None, one_event=False, bhr=None):
         self.slot, self.n_bands, self.device_data = slot, n_bands, device_data
         self.raw = raw or {}                 # band -> (raw_type, ScaledReflectance, has_mask)
+        self.bhr = bhr or {}                 # band -> (kernel_type, kernels, mask, qa) device tensors
         self.one_event = one_event           # all bands went up in one copy: only copied[n_bands-1] was recorded
 
 
@@ -156,7 +172,11 @@ class ObservationStager(object):
             self._copy_stream.wait_event(slot.gathered)           # device rasters no longer being gathered
         parts = max(1, min(self.N_THREADS, n // (1 << 20)))       # split big rasters across the pool
         raw = {}
+        bhr = {}
         for b, d in enumerate(current_data):
+            if isinstance(d.uncertainty, BHRKernelWeights):
+                bhr[b] = self._upload_bhr(d, n)
+                continue
             if isinstance(d.uncertainty, ScaledReflectance):
                 dt_ = np.asarray(d.observations).dtype
                 if dt_ not in ScaledReflectance.RAW_TYPES:
@@ -166,12 +186,12 @@ class ObservationStager(object):
             slot.h_raw = torch.empty((slot.cap, n), dtype=torch.int32).pin_memory()
             slot.d_raw = torch.empty((slot.cap, n), dtype=torch.int32, device=self.device)
             slot.np_raw = slot.h_raw.numpy()
-        holders = [None if b in raw else _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
+        holders = [None if (b in raw or b in bhr) else _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
                    for b, d in enumerate(current_data)]
         futures = []
         small = n < (1 << 18)                          # tiny rasters: the pool's hand-over costs more than the copy
         for b, d in enumerate(current_data):
-            if small:
+            if small or b in bhr:
                 futures.append([])
             elif b in raw:
                 futures.append([self._pool.submit(self._stage_raw, slot, b, d, raw[b], n * k // parts,
@@ -179,7 +199,7 @@ class ObservationStager(object):
             else:
                 futures.append([self._pool.submit(self._stage_part, slot, b, holders[b], n * k // parts,
                                                   n * (k + 1) // parts) for k in range(parts)])
-        if small and not raw:
+        if small and not raw and not bhr:
             # tiny rasters, the reference's float rasters: launch overhead is all there is, so
             # stage every band inline and queue ONE copy per array instead of three per band
             for b in range(nb):
@@ -192,6 +212,9 @@ class ObservationStager(object):
             self.h2d_bytes += nb * n * 17
             return StagedDate(slot, nb, raw=raw, one_event=True)
         for b in range(nb):
+            if b in bhr:
+                slot.copied[b].record(self._copy_stream)           # uploaded above, on the copy stream
+                continue
             if small:
                 if b in raw:
                     self._stage_raw(slot, b, current_data[b], raw[b], 0, n)
@@ -215,7 +238,25 @@ class ObservationStager(object):
                     slot.d_msk[b].copy_(slot.h_msk[b], non_blocking=True)
                     self.h2d_bytes += n * 17
                 slot.copied[b].record(self._copy_stream)
-        return StagedDate(slot, nb, raw=raw)
+        return StagedDate(slot, nb, raw=raw, bhr=bhr)
+
+    def _upload_bhr(self, d, n):
+        """Kernel weights (3, ny, nx), quality level and mask of one MODIS band to the device
+        (a 2400 x 2400 tile is 80 MB per band: plain copies on the copy stream)."""
+        k = np.asarray(d.observations)
+        if k.dtype not in BHRKernelWeights.KERNEL_TYPES or k.shape[0] != 3 or k.size != 3 * n:
+            raise TypeError("BRDF kernel weights must be a float32/float64 array of shape (3, ny, nx)")
+        qa = np.asarray(d.uncertainty.qa_level)
+        if qa.size != n or np.asarray(d.mask).size != n:
+            raise ValueError("quality level and mask must have the raster's shape")
+        qa8 = np.where((qa >= 0) & (qa <= 254), qa, 255).astype(np.uint8).reshape(-1)   # only 0 and 1 carry meaning
+        m8 = (np.asarray(d.mask).reshape(-1) != 0).astype(np.uint8)
+        with torch.cuda.stream(self._copy_stream):
+            kt = torch.from_numpy(np.ascontiguousarray(k.reshape(3, n))).to(self.device, non_blocking=True)
+            qt = torch.from_numpy(qa8).to(self.device, non_blocking=True)
+            mt = torch.from_numpy(m8).to(self.device, non_blocking=True)
+        self.h2d_bytes += k.nbytes + 2 * n
+        return (BHRKernelWeights.KERNEL_TYPES[k.dtype], kt, mt, qt)
 
     def finish(self, token, out=None):
         """Gather the staged rasters into compacted rows on the compute stream."""
@@ -239,6 +280,16 @@ class ObservationStager(object):
             return out
         for b in range(nb):
             main.wait_event(slot.copied[b])
+            if b in token.bhr:
+                ktype, kt, mt, qt = token.bhr[b]
+                with torch.cuda.device(self.device):
+                    _lib.check(lib.kafka_gather_bhr_band(_lib.ptr(kt), ktype, kt.stride(0), _lib.ptr(mt), _lib.ptr(qt),
+                                                         _lib.ptr(pix.idx), pix.n_pix, _lib.ptr(out.y[b]),
+                                                         _lib.ptr(out.w[b]), _lib.ptr(out.m[b]), _lib.stream_ptr()),
+                               "kafka_gather_bhr_band")
+                for t in (kt, mt, qt):
+                    t.record_stream(main)        # allocated on the copy stream, read on the main stream
+                continue
             if b in token.raw:
                 raw_type, sr, has_mask, _ = token.raw[b]
                 with torch.cuda.device(self.device):

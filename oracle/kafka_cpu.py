@@ -214,6 +214,24 @@ def s2_ingest(raw, ext_mask=None, divisor=10000.0, rel_sigma=0.05):
     return rho, inv_var, mask
 
 
+def bhr_ingest(kernels, mask, qa_level):
+    """kafka/input_output/observations.py:288-310 (BHRObservations.get_band_data):
+    bi-hemispherical reflectance from the three BRDF kernel weights, its
+    standard deviation from the quality level and the inverse variance (inf where
+    the standard deviation is 0: masked pixels and quality levels above 1)."""
+    to_BHR = np.array([1.0, 0.189184, -1.377622])
+    mask = np.asarray(mask, dtype=bool)
+    with np.errstate(invalid="ignore"):
+        bhr = np.where(mask, kernels * to_BHR[:, None, None], np.nan).sum(axis=0)
+        R_mat = np.zeros_like(bhr)
+        R_mat[qa_level == 0] = np.maximum(2.5e-3, bhr[qa_level == 0] * 0.05)
+        R_mat[qa_level == 1] = np.maximum(2.5e-3, bhr[qa_level == 1] * 0.07)
+    R_mat[np.logical_not(mask)] = 0.
+    with np.errstate(divide="ignore"):
+        inv_var = 1. / (R_mat.ravel()) ** 2
+    return bhr, inv_var.reshape(bhr.shape), mask
+
+
 # --------------------------------------------------------------------------
 # a8/a9  one linearised solve
 # --------------------------------------------------------------------------

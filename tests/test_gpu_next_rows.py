@@ -205,3 +205,52 @@ def test_scaled_reflectance_ingest_matches_reader_arithmetic(dtype):
     assert np.array_equal(bufs.y[0, :N].cpu().numpy(), y)
     assert np.array_equal(bufs.w[0, :N].cpu().numpy(), kc.gate_inverse_variance(r, mm))
     assert np.array_equal(bufs.m[0, :N].cpu().numpy().astype(bool), mm)
+
+
+# ---------------------------------------------------------------- MODIS BHR ingest
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_bhr_kernel_weights_ingest_matches_reader_arithmetic(dtype):
+    """BHRObservations.get_band_data (observations.py:288-310) on the device: two
+    broadbands (TIP layout), fed once as kernel weights + quality level and once as
+    the float rasters the reader would have produced: bit-identical posterior."""
+    rng = np.random.default_rng(14)
+    mask = gio.barrax_mask()
+    P, B = 7, 2
+    N = int(mask.sum())
+    mappers = [np.array([0, 1, 6, 2]), np.array([3, 4, 6, 5])]
+    gps = [syn.make_emulator(rng, syn.TIP_MEAN[m], syn.TIP_SIGMA[m], n_train=60, w_scale=0.1) for m in mappers]
+    kernel_bands, float_bands = [], []
+    for b in range(B):
+        k = np.stack([rng.uniform(0.05, 0.6, mask.shape), rng.uniform(0.0, 0.3, mask.shape),
+                      rng.uniform(0.0, 0.08, mask.shape)]).astype(dtype)
+        k[:, 3, 5] = 1e-4                                           # sigma floor 2.5e-3 active
+        qa = rng.integers(0, 2, size=mask.shape)
+        obs_mask = rng.random(mask.shape) < 0.85
+        bhr, inv, m = kc.bhr_ingest(k, obs_mask, qa)
+        kernel_bands.append(syn.BandData(k, kb.BHRKernelWeights(qa), obs_mask, {"band": b}, gps[b]))
+        float_bands.append(syn.BandData(np.where(m, bhr, 0.0), inv, m, {"band": b}, gps[b]))
+    date = dt.datetime(2017, 7, 3)
+    _, _, inv_block = kc.tip_prior()
+    out = []
+    for data in (kernel_bands, float_bands):
+        kf = kb.LinearKalman(None, None, mask, kb.create_nonlinear_observation_operator, syn.TIP_PARAMETERS, prior=None)
+        x, _, A, innov = kf.do_all_bands(date, data, DeviceVector.broadcast(syn.TIP_MEAN, N, gu.DEV), None,
+                                         BlockDiag.from_block(inv_block.astype(np.float64), N, gu.DEV))
+        out.append((np.asarray(x), A.blocks(), np.asarray(innov)))
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+    assert np.array_equal(out[0][2], out[1][2])
+    # the gathered rows themselves, incl. a pixel whose quality level is outside {0, 1}: w = inf like the reader
+    k, marker, obs_mask = kernel_bands[0].observations, kernel_bands[0].uncertainty, kernel_bands[0].mask.copy()
+    qa = marker.qa_level.copy()
+    r0, c0 = np.argwhere(mask & obs_mask)[0]
+    qa[r0, c0] = 3
+    kf = kb.LinearKalman(None, None, mask, kb.create_nonlinear_observation_operator, syn.TIP_PARAMETERS, prior=None)
+    bufs = kf._stager.upload([kernel_bands[0]._replace(uncertainty=kb.BHRKernelWeights(qa))])
+    bhr, inv, m = kc.bhr_ingest(k, obs_mask, qa)
+    y, r, mm = kc.gather_band(np.where(m, bhr, 0.0), inv.ravel(), m, mask)
+    assert np.array_equal(bufs.y[0, :N].cpu().numpy(), y)
+    assert np.array_equal(bufs.w[0, :N].cpu().numpy(), np.where(mm, r, 0.0))
+    assert np.isinf(bufs.w[0, :N].cpu().numpy()).sum() == 1
+    assert kf._stager.h2d_bytes == k.nbytes + 2 * mask.size
+    with pytest.raises(TypeError):
+        kf._stager.upload([kernel_bands[0]._replace(observations=k[:2])])

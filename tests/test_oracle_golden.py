@@ -282,3 +282,25 @@ def test_s2_ingest_matches_reader_arithmetic():
         want_inv = 1. / R ** 2
     assert np.array_equal(m, mask) and np.array_equal(rho, want) and np.array_equal(inv, want_inv)
     assert np.isinf(inv[~mask]).all()
+
+
+def test_bhr_ingest_restates_the_reader_line_by_line():
+    """oracle bhr_ingest against an independent evaluation of observations.py:288-310
+    (the reader itself needs GDAL and the un-vendored BRDF_descriptors package)."""
+    rng = np.random.default_rng(3)
+    k = rng.uniform(0.0, 0.5, (3, 9, 11))
+    mask = rng.random((9, 11)) < 0.8
+    qa = rng.integers(0, 3, size=(9, 11))
+    bhr, inv, m = kc.bhr_ingest(k, mask, qa)
+    for r in range(9):
+        for c in range(11):
+            if not mask[r, c]:
+                assert np.isnan(bhr[r, c]) and np.isinf(inv[r, c])
+                continue
+            v = (k[0, r, c] * 1.0 + k[1, r, c] * 0.189184) + k[2, r, c] * -1.377622
+            assert bhr[r, c] == v
+            if qa[r, c] > 1:
+                assert np.isinf(inv[r, c])
+            else:
+                sig = max(2.5e-3, v * (0.05 if qa[r, c] == 0 else 0.07))
+                assert inv[r, c] == 1.0 / sig ** 2
