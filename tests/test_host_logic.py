@@ -134,3 +134,25 @@ def test_bench_reference_arm_prints_contract_line():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
                          capture_output=True, text=True, timeout=120, env=dict(os.environ, RANK="1", WORLD_SIZE="2"))
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+def test_get_chunks_matches_reference_tiling():
+    """kafka/input_output/utils.py:12-40: same tuples in the same order as the
+    reference's generator (transcribed expectations for 600 x 500 in 256 blocks,
+    plus the unmodified function itself where /root/reference is present)."""
+    from kafka_inferenceengine_b200.input_output import get_chunks
+    got = list(get_chunks(600, 500, block_size=[256, 256]))
+    assert got == [(0, 0, 256, 256, 1), (0, 256, 256, 244, 2), (256, 0, 256, 256, 3), (256, 256, 256, 244, 4),
+                   (512, 0, 88, 256, 5), (512, 256, 88, 244, 6)]
+    assert list(get_chunks(128, 128, block_size=[128, 128])) == [(0, 0, 128, 128, 1)]
+    assert list(get_chunks(0, 10)) == []
+    covered = np.zeros((500, 600), dtype=int)
+    for x0, y0, w, h, _ in get_chunks(600, 500, block_size=[100, 37]):
+        covered[y0:y0 + h, x0:x0 + w] += 1
+    assert (covered == 1).all()
+    from oracle import ref_shim
+    if ref_shim.available():
+        ref_shim.load()
+        from kafka.input_output.utils import get_chunks as ref_chunks
+        for nx, ny, bs in ((600, 500, [256, 256]), (235, 204, [128, 128]), (10980, 10980, [4096, 1000]), (5, 3, [7, 7])):
+            assert list(get_chunks(nx, ny, bs)) == list(ref_chunks(nx, ny, block_size=bs))
