@@ -10,8 +10,8 @@ without a CUDA device) the compute entry points raise.
 from . import _lib                                         # noqa: F401
 from .device import BlockDiag, DeviceVector, PixelIndex    # noqa: F401
 from .inference import *                                   # noqa: F401,F403
+from .input_output import *                                # noqa: F401,F403
 from .linear_kf import LinearKalman                        # noqa: F401
 from .observation_operators import *                       # noqa: F401,F403
-from .engine import BHRKernelWeights, ScaledReflectance    # noqa: F401
 
 __version__ = "0.1.0"
