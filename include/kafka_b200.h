@@ -60,7 +60,7 @@ extern "C" {
 #define KAFKA_RAW_I16 0
 #define KAFKA_RAW_U16 1
 #define KAFKA_RAW_F32 2
-#define KAFKA_RAW_F64 3 /* kafka_gather_bhr_band only */
+#define KAFKA_RAW_F64 3 /* kafka_gather_bhr_band and kafka_gather_backscatter_band only */
 
 /* flags */
 #define KAFKA_ROUND_F32 1u      /* round H0/J to float32 as the reference stores them \
@@ -134,6 +134,20 @@ int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, in
 int kafka_gather_bhr_band(const void* kernels, int kernel_type, int64_t plane_stride,
                           const uint8_t* mask, const uint8_t* qa, const int32_t* idx,
                           int64_t n_pix, double* y, double* w, uint8_t* m_out, void* stream);
+
+/* Observation ingest of the Sentinel-1 reader fused with the gather, replacing the
+ * arithmetic of S1Observations.get_band_data
+ * (kafka/input_output/Sentinel1_Observations.py:107-130,147-149,176-187).  raw: the
+ * sigma0 raster of one polarisation, KAFKA_RAW_F32 or KAFKA_RAW_F64.
+ *   m = raw[idx] != missing_value                 (missing_value = -999)
+ *   y = m ? raw[idx] : 0
+ *   w = m ? 1 / (rel_sigma * raw[idx])^2 : 0      (rel_sigma = 0.05)
+ * The product, the square and the reciprocal are rounded in the raster's own type,
+ * as the reader's numpy expressions are, and then widened: bit-identical to the
+ * reader.  An unmasked zero backscatter gets w = inf, exactly as there. */
+int kafka_gather_backscatter_band(const void* raw, int raw_type, const int32_t* idx, int64_t n_pix,
+                                  double missing_value, double rel_sigma, double* y, double* w,
+                                  uint8_t* m_out, void* stream);
 
 /* Number of pixels whose state differs (bitwise) from pixel 0's: 0 means every
  * pixel holds the same vector, which is what run_emulator's de-duplication

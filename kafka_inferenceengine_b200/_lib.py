@@ -52,6 +52,7 @@ SIGNATURES = {
     "kafka_gather_band": (C.c_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p]),
     "kafka_gather_bands": (C.c_int, [_p, _p, _p, _i64, _i32, _p, _i64, _i64, _p, _p, _p, _p]),
     "kafka_gather_bhr_band": (C.c_int, [_p, _i32, _i64, _p, _p, _p, _i64, _p, _p, _p, _p]),
+    "kafka_gather_backscatter_band": (C.c_int, [_p, _i32, _p, _i64, C.c_double, C.c_double, _p, _p, _p, _p]),
     "kafka_gather_scaled_band": (C.c_int, [_p, _i32, _p, _p, _i64, C.c_double, C.c_double, _p, _p, _p, _p]),
     "kafka_scatter_output": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p, _p, _p]),
     "kafka_state_uniform": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),

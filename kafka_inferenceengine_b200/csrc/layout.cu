@@ -182,6 +182,36 @@ __global__ void gather_scaled_band_kernel(const RawT* __restrict__ raw, const ui
     if (m_out) m_out[i] = m ? 1 : 0;
 }
 
+// Sentinel-1 backscatter ingest (Sentinel1_Observations.py:107-130,147-149,176-187): the reader works
+// in the raster's own type (float32 from the NetCDF, or float64), so the products are rounded in that
+// type, one by one, before the inverse variance is widened to fp64 by setdiag.
+template <typename RawT>
+__device__ __forceinline__ RawT s1_inverse_variance(RawT unc);
+template <>
+__device__ __forceinline__ float s1_inverse_variance<float>(float unc) {
+    return __fdiv_rn(1.0f, __fmul_rn(unc, unc));
+}
+template <>
+__device__ __forceinline__ double s1_inverse_variance<double>(double unc) {
+    return __ddiv_rn(1.0, __dmul_rn(unc, unc));
+}
+__device__ __forceinline__ float s1_scale(float v, float f) { return __fmul_rn(v, f); }
+__device__ __forceinline__ double s1_scale(double v, double f) { return __dmul_rn(v, f); }
+
+template <typename RawT>
+__global__ void gather_backscatter_band_kernel(const RawT* __restrict__ raw, const int32_t* __restrict__ idx,
+                                               int64_t n_pix, RawT missing, RawT rel_sigma, double* __restrict__ y,
+                                               double* __restrict__ w, uint8_t* __restrict__ m_out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pix) return;
+    const RawT r = raw[idx[i]];
+    const bool m = !(r == missing);                               // mask[backscatter == WRONG_VALUE] = False (:148)
+    const RawT unc = s1_scale(r, rel_sigma);                      // unc = backscatter*0.05            (:124)
+    y[i] = m ? (double)r : 0.0;
+    w[i] = m ? (double)s1_inverse_variance<RawT>(unc) : 0.0;     // 1./(R_mat)**2, gated              (:183-187)
+    if (m_out) m_out[i] = m ? 1 : 0;
+}
+
 __global__ void scatter_output_kernel(const double* __restrict__ x, const double* __restrict__ a,
                                       int64_t ld, int64_t n_pix, int n_params,
                                       const int32_t* __restrict__ idx, int64_t n_raster,
@@ -385,6 +415,29 @@ int kafka_gather_scaled_band(const void* raw, int raw_type, const uint8_t* ext_m
             return KAFKA_E_BADARG;
     }
     return launch_status("gather_scaled_band_kernel");
+}
+
+int kafka_gather_backscatter_band(const void* raw, int raw_type, const int32_t* idx, int64_t n_pix,
+                                  double missing_value, double rel_sigma, double* y, double* w, uint8_t* m_out,
+                                  void* stream) {
+    KAFKA_CHECK_ARG(n_pix >= 0, "kafka_gather_backscatter_band: n_pix < 0");
+    KAFKA_CHECK_ARG(rel_sigma > 0.0, "kafka_gather_backscatter_band: rel_sigma must be > 0");
+    if (n_pix == 0) return 0;
+    KAFKA_CHECK_ARG(raw && idx && y && w, "kafka_gather_backscatter_band: null pointer");
+    const int threads = 256;
+    const unsigned grid = (unsigned)((n_pix + threads - 1) / threads);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (raw_type == KAFKA_RAW_F32)
+        gather_backscatter_band_kernel<float><<<grid, threads, 0, s>>>((const float*)raw, idx, n_pix, (float)missing_value,
+                                                                       (float)rel_sigma, y, w, m_out);
+    else if (raw_type == KAFKA_RAW_F64)
+        gather_backscatter_band_kernel<double><<<grid, threads, 0, s>>>((const double*)raw, idx, n_pix, missing_value,
+                                                                        rel_sigma, y, w, m_out);
+    else {
+        set_error("kafka_gather_backscatter_band: raw_type %d is neither KAFKA_RAW_F32 nor KAFKA_RAW_F64", raw_type);
+        return KAFKA_E_BADARG;
+    }
+    return launch_status("gather_backscatter_band");
 }
 
 int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, int64_t n_pix,

@@ -214,6 +214,24 @@ def s2_ingest(raw, ext_mask=None, divisor=10000.0, rel_sigma=0.05):
     return rho, inv_var, mask
 
 
+def s1_ingest(backscatter, missing_value=-999.0, rel_sigma=0.05):
+    """kafka/input_output/Sentinel1_Observations.py:107-130,147-149,176-187
+    (S1Observations.get_band_data): mask, standard deviation and inverse variance of
+    one sigma0 raster.  The arithmetic runs in the raster's own type (float32 as read
+    from the file, or float64) and the inverse variance is widened to float64 when it
+    is stored on the sparse diagonal (:184-186).  inf where masked, and where an
+    unmasked backscatter is zero or its square underflows."""
+    backscatter = np.asarray(backscatter)
+    unc = backscatter * rel_sigma                              # :124
+    mask = np.ones_like(backscatter, dtype=bool)               # :147
+    mask[backscatter == missing_value] = False                 # :148
+    R_mat = unc                                                # :180-181
+    R_mat[np.logical_not(mask)] = 0.                           # :182
+    with np.errstate(divide="ignore", over="ignore"):
+        inv_var = 1. / (R_mat.ravel()) ** 2                    # :186
+    return backscatter, inv_var.astype(np.float64).reshape(backscatter.shape), mask
+
+
 def bhr_ingest(kernels, mask, qa_level):
     """kafka/input_output/observations.py:288-310 (BHRObservations.get_band_data):
     bi-hemispherical reflectance from the three BRDF kernel weights, its

@@ -379,10 +379,62 @@ def kat_hessian(kafka):
     np.savez_compressed(os.path.join(OUT, "kat_hessian.npz"), **res)
 
 
+def kat_s1_ingest(kafka):
+    """S1Observations.get_band_data (input_output/Sentinel1_Observations.py:151-196),
+    unmodified, on synthetic sigma0 rasters: the module's ``reproject_image`` (GDAL) is
+    replaced by a stand-in that hands back the synthetic arrays."""
+    import datetime as dt
+    import kafka.input_output.Sentinel1_Observations as s1
+
+    class _Ptr(object):
+        def __init__(self, a):
+            self.a = a
+
+        def ReadAsArray(self):
+            return self.a.copy()
+
+    rng = np.random.default_rng(21)
+    ny, nx = 37, 41
+    theta = (30.0 + 10.0 * rng.random((ny, nx))).astype(np.float32)
+    res = {"theta": theta, "missing_value": np.float64(s1.WRONG_VALUE)}
+    date = dt.datetime(2017, 5, 4, 6, 2, 11)
+    for name, dtype in (("f32", np.float32), ("f64", np.float64)):
+        rasters = {}
+        for pol in ("VV", "VH"):
+            r = (-26.0 + 22.0 * rng.random((ny, nx))).astype(dtype)
+            r[rng.random((ny, nx)) < 0.15] = s1.WRONG_VALUE
+            r[3, 5] = 0.0                                  # unmasked zero: infinite weight in the reader
+            r[4, 6] = 1e-30 if dtype == np.float32 else 1e-200   # square underflows -> inf as well
+            rasters[pol] = r
+        reader = object.__new__(s1.S1Observations)
+        reader.date_data = {date: "S1A_IW_GRDH_1SDV_x_20170504T060211.nc"}
+        reader.emulators = {"VV": "vv-model", "VH": "vh-model"}
+        reader.state_mask = "state_mask.tif"
+
+        def fake_reproject(fname, target, dstSRSs=None, _r=rasters):
+            for pol in ("VV", "VH"):
+                if fname.endswith("sigma0_" + pol):
+                    return _Ptr(_r[pol])
+            assert fname.endswith(":theta"), fname
+            return _Ptr(theta)
+        s1.reproject_image = fake_reproject
+        for band, pol in enumerate(("VV", "VH")):
+            with np.errstate(divide="ignore", over="ignore"):
+                d = reader.get_band_data(date, band)
+            assert d.emulator == reader.emulators[pol]
+            assert np.array_equal(d.metadata["incidence_angle"], theta)
+            res["%s_%s_raw" % (name, pol)] = rasters[pol]
+            res["%s_%s_obs" % (name, pol)] = d.observations
+            res["%s_%s_inv_var" % (name, pol)] = d.uncertainty.diagonal()
+            res["%s_%s_mask" % (name, pol)] = d.mask
+    np.savez_compressed(os.path.join(OUT, "kat_s1_ingest.npz"), **res)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     kafka = ref_shim.load()
     kat_sar(kafka)
+    kat_s1_ingest(kafka)
     kat_hessian(kafka)
     kat_propagators(kafka)
     kat_time_grid(kafka)

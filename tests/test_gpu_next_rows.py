@@ -254,3 +254,72 @@ def test_bhr_kernel_weights_ingest_matches_reader_arithmetic(dtype):
     assert kf._stager.h2d_bytes == k.nbytes + 2 * mask.size
     with pytest.raises(TypeError):
         kf._stager.upload([kernel_bands[0]._replace(observations=k[:2])])
+
+
+# ---------------------------------------------------------------- Sentinel-1 sigma0 ingest
+@pytest.mark.parametrize("name", ["f32", "f64"])
+def test_backscatter_ingest_matches_the_unmodified_reader(name):
+    """S1Observations.get_band_data (Sentinel1_Observations.py:151-196) on the device:
+    rows gathered from the raw sigma0 raster equal, bit for bit, the rows gathered from
+    the unmodified reader's outputs (fixture kat_s1_ingest) and from the oracle."""
+    g = gio.load("kat_s1_ingest")
+    rng = np.random.default_rng(8)
+    shape = g["theta"].shape
+    mask = rng.random(shape) < 0.7
+    mask[3, 5] = mask[4, 6] = True                       # the two infinite-weight pixels are in the state
+    N = int(mask.sum())
+    kf = kb.LinearKalman(None, None, mask, kb.create_sar_observation_operator, ["lai", "sm"], prior=None)
+    for b, pol in enumerate(("VV", "VH")):
+        raw = g["%s_%s_raw" % (name, pol)]
+        marker = kb.BackscatterSigma0(missing_value=float(g["missing_value"]))
+        before = kf._stager.h2d_bytes
+        bufs = kf._stager.upload([syn.BandData(raw, marker, None, {"band": b}, None)])
+        assert kf._stager.h2d_bytes - before == raw.nbytes               # 4 or 8 B/px instead of 17
+        y, r, mm = kc.gather_band(g["%s_%s_obs" % (name, pol)].astype(np.float64), g["%s_%s_inv_var" % (name, pol)],
+                                  g["%s_%s_mask" % (name, pol)], mask)
+        assert np.array_equal(bufs.y[0, :N].cpu().numpy(), y)
+        assert np.array_equal(bufs.w[0, :N].cpu().numpy(), kc.gate_inverse_variance(r, mm))
+        assert np.array_equal(bufs.m[0, :N].cpu().numpy().astype(bool), mm)
+        assert np.isinf(bufs.w[0, :N].cpu().numpy()).sum() == 2        # unmasked zero and underflowing square, as the reader
+        obs_o, inv_o, m_o = kc.s1_ingest(raw.copy(), missing_value=float(g["missing_value"]))
+        yo, ro, mo = kc.gather_band(obs_o.astype(np.float64), inv_o.ravel(), m_o, mask)
+        assert np.array_equal(y, yo) and np.array_equal(r, ro) and np.array_equal(mm, mo)
+    with pytest.raises(TypeError):
+        kf._stager.upload([syn.BandData(np.zeros(shape, dtype=np.int16), kb.BackscatterSigma0(), None, {}, None)])
+
+
+def test_sar_filter_run_from_raw_sigma0_equals_run_from_reader_outputs():
+    """The Water-Cloud filter run fed with raw sigma0 rasters + BackscatterSigma0 markers
+    gives the same bits as the run fed with what the reader would have produced."""
+    rng = np.random.default_rng(23)
+    mask, N, obs, dates, base = _sar_case(rng)
+    P = 2
+    raw_store, float_store = {}, {}
+    for d in dates:
+        raws, floats = [], []
+        for b in range(2):
+            src = obs.get_band_data(d, b)
+            sigma0 = np.where(src.mask & mask, src.observations, -999.0).astype(np.float32)
+            o, inv, m = kc.s1_ingest(sigma0.copy())
+            raws.append(syn.BandData(sigma0, kb.BackscatterSigma0(), None, {"band": b}, None))
+            floats.append(syn.BandData(o.astype(np.float64), syn.inverse_variance_matrix(inv), m, {"band": b}, None))
+        raw_store[d], float_store[d] = raws, floats
+    mean = np.array([2.5, 0.25])
+    inv = np.diag(1.0 / np.array([0.8, 0.08]) ** 2)
+    outs = []
+    for store in (raw_store, float_store):
+        obs.get_band_data = lambda date, band, s=store: s[date][band]
+        prior = syn.BroadcastPrior(mean, inv, N, lambda blk, n: BlockDiag.from_block(blk, n, gu.DEV))
+        out = syn.MemoryOutput(["lai", "sm"])
+        kf = kb.LinearKalman(obs, out, mask, kb.create_sar_observation_operator, ["lai", "sm"],
+                             state_propagation=None, prior=prior, linear=False)
+        kf.set_trajectory_model()
+        kf.set_trajectory_uncertainty(np.zeros(N * P))
+        x0, Pinv0 = prior.process_prior(None)
+        grid = [base + dt.timedelta(days=3 * d) for d in range(len(dates) + 1)]
+        kf.run(grid, x0, None, Pinv0)
+        outs.append((out, kf.last_iterations))
+    assert outs[0][1] == outs[1][1]
+    for t in outs[0][0].output:
+        assert np.array_equal(outs[0][0].output[t]["x"], outs[1][0].output[t]["x"])
+        assert np.array_equal(outs[0][0].output[t]["diag"], outs[1][0].output[t]["diag"])

@@ -304,3 +304,21 @@ def test_bhr_ingest_restates_the_reader_line_by_line():
             else:
                 sig = max(2.5e-3, v * (0.05 if qa[r, c] == 0 else 0.07))
                 assert inv[r, c] == 1.0 / sig ** 2
+
+
+def test_s1_ingest_matches_the_unmodified_reader():
+    """oracle s1_ingest against outputs of the unmodified S1Observations.get_band_data
+    (fixture made by oracle/make_golden.py:kat_s1_ingest with GDAL's reproject_image
+    replaced by a stand-in): bit-exact for float32 and float64 rasters, including the
+    infinite weights of masked pixels, of an unmasked zero and of an underflowing square."""
+    g = gio.load("kat_s1_ingest")
+    for name in ("f32", "f64"):
+        for pol in ("VV", "VH"):
+            raw = g["%s_%s_raw" % (name, pol)]
+            obs, inv, m = kc.s1_ingest(raw.copy(), missing_value=float(g["missing_value"]))
+            assert obs.dtype == raw.dtype
+            assert np.array_equal(obs, g["%s_%s_obs" % (name, pol)])
+            assert np.array_equal(m, g["%s_%s_mask" % (name, pol)])
+            assert inv.dtype == np.float64
+            assert np.array_equal(inv.ravel(), g["%s_%s_inv_var" % (name, pol)])
+            assert np.isinf(inv[~m]).all() and np.isinf(inv[3, 5]) and np.isinf(inv[4, 6]) and m[3, 5] and m[4, 6]
