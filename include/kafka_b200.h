@@ -105,8 +105,11 @@ int kafka_gather_bands(const double* obs, const double* inv_var, const uint8_t* 
  *   m = raw[idx] > 0 (and ext_mask[idx] != 0 when ext_mask is given)
  *   y = m ? raw[idx] / divisor      : 0        (divisor = 10000)
  *   w = m ? 1 / (rel_sigma * y)^2   : 0        (rel_sigma = 0.05)
- * Only the raw raster (2 or 4 bytes per pixel) has to cross PCIe instead of the
- * 17 bytes of (float64 reflectance, float64 inverse variance, mask). */
+ * Integer rasters are converted to fp64 first, as numpy does; a KAFKA_RAW_F32 raster
+ * stays float32 through the reader's expressions, so there every step is rounded in
+ * float32 and the results widened at the end (bit-identical to the reader in both
+ * cases).  Only the raw raster (2 or 4 bytes per pixel) has to cross PCIe instead of
+ * the 17 bytes of (float64 reflectance, float64 inverse variance, mask). */
 int kafka_gather_scaled_band(const void* raw, int raw_type, const uint8_t* ext_mask, const int32_t* idx,
                              int64_t n_pix, double divisor, double rel_sigma, double* y, double* w,
                              uint8_t* m_out, void* stream);

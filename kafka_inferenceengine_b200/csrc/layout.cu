@@ -175,10 +175,19 @@ __global__ void gather_scaled_band_kernel(const RawT* __restrict__ raw, const ui
     const RawT r = raw[j];
     bool m = r > (RawT)0;                                        // mask = rho_surface > 0   (:168)
     if (ext_mask) m = m && ext_mask[j] != 0;
-    const double rho = m ? (double)r / divisor : 0.0;            // rho_surface / 10000.     (:169)
-    const double sig = rho * rel_sigma;                          // R_mat = rho_surface*0.05 (:174)
-    y[i] = rho;
-    w[i] = m ? 1.0 / (sig * sig) : 0.0;                          // 1./(R_mat)**2, gated     (:175-178)
+    if constexpr (sizeof(RawT) == 4) {
+        // a float32 raster stays float32 through the reader's numpy expressions (scalars do not
+        // widen an array): every step is rounded in float32, the result widened at the end
+        const float rho = m ? __fdiv_rn((float)r, (float)divisor) : 0.0f;
+        const float sig = __fmul_rn(rho, (float)rel_sigma);
+        y[i] = (double)rho;
+        w[i] = m ? (double)__fdiv_rn(1.0f, __fmul_rn(sig, sig)) : 0.0;
+    } else {
+        const double rho = m ? __ddiv_rn((double)r, divisor) : 0.0;  // rho_surface / 10000.     (:169)
+        const double sig = __dmul_rn(rho, rel_sigma);                // R_mat = rho_surface*0.05 (:174)
+        y[i] = rho;
+        w[i] = m ? __ddiv_rn(1.0, __dmul_rn(sig, sig)) : 0.0;        // 1./(R_mat)**2, gated     (:175-178)
+    }
     if (m_out) m_out[i] = m ? 1 : 0;
 }
 

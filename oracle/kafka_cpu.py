@@ -202,7 +202,9 @@ def hessian_correction(gp, x0, inv_var, innovation, obs_mask, n_params, mapper):
 
 def s2_ingest(raw, ext_mask=None, divisor=10000.0, rel_sigma=0.05):
     """Sentinel2_Observations.py:166-179: mask, reflectance and inverse variance
-    (inf where masked) from the raw scaled-integer raster."""
+    (inf where masked) from the raw raster.  Scaled integers become float64 at the
+    division; a float32 raster stays float32 through every expression and only the
+    inverse variance is widened when it is stored on the sparse diagonal (:177-178)."""
     mask = raw > 0
     if ext_mask is not None:
         mask = mask & (np.asarray(ext_mask) != 0)
@@ -211,7 +213,7 @@ def s2_ingest(raw, ext_mask=None, divisor=10000.0, rel_sigma=0.05):
     R[np.logical_not(mask)] = 0.
     with np.errstate(divide="ignore"):
         inv_var = 1. / (R) ** 2
-    return rho, inv_var, mask
+    return rho, inv_var.astype(np.float64), mask
 
 
 def s1_ingest(backscatter, missing_value=-999.0, rel_sigma=0.05):

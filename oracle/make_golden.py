@@ -430,11 +430,77 @@ def kat_s1_ingest(kafka):
     np.savez_compressed(os.path.join(OUT, "kat_s1_ingest.npz"), **res)
 
 
+def kat_reader_ingest(kafka):
+    """Sentinel2Observations.get_band_data (input_output/Sentinel2_Observations.py:148-185)
+    and BHRObservations.get_band_data (input_output/observations.py:288-310), unmodified,
+    on synthetic rasters.  Stand-ins replace what needs GDAL or un-vendored packages:
+    ``reproject_image`` / ``parse_xml`` / ``_find_emulator`` (S2, plus an emulator pickle
+    written to a temporary file) and ``get_brdf_descriptors`` (MODIS)."""
+    import datetime as dt
+    import pickle
+    import tempfile
+    import kafka.input_output.Sentinel2_Observations as s2
+    import kafka.input_output.observations as mod
+
+    class _Ptr(object):
+        def __init__(self, a):
+            self.a = a
+
+        def ReadAsArray(self):
+            return self.a.copy()
+
+    rng = np.random.default_rng(33)
+    ny, nx = 29, 31
+    res = {}
+    date = dt.datetime(2017, 7, 3)
+    band_names = [b"S2A_MSI_%02d" % k for k in (2, 3, 4, 5, 6, 7, 8, 9, 12, 13)]
+    with tempfile.TemporaryDirectory() as tmp:
+        emu_file = os.path.join(tmp, "emulators.pkl")
+        with open(emu_file, "wb") as f:
+            pickle.dump({k: "emulator-%s" % k.decode() for k in band_names}, f)
+        for name, dtype in (("i16", np.int16), ("u16", np.uint16), ("f32", np.float32)):
+            raw = rng.integers(0 if dtype == np.uint16 else -40, 7000, size=(ny, nx)).astype(dtype)
+            raw[rng.random((ny, nx)) < 0.12] = 0
+            reader = object.__new__(s2.Sentinel2Observations)
+            reader.date_data = {date: os.path.join(tmp, "granule")}
+            reader.band_map = ['02', '03', '04', '05', '06', '07', '08', '8A', '09', '12']
+            reader.state_mask = "state_mask.tif"
+            reader._find_emulator = lambda sza, saa, vza, vaa: emu_file
+            s2.parse_xml = lambda fname: (30.0, 150.0, 5.0, 100.0)
+            s2.reproject_image = lambda fname, target, dstSRSs=None, _r=raw: _Ptr(_r)
+            with np.errstate(divide="ignore"):
+                d = reader.get_band_data(date, 3)
+            assert d.emulator == "emulator-S2A_MSI_05"
+            res["s2_%s_raw" % name] = raw
+            res["s2_%s_obs" % name] = d.observations
+            res["s2_%s_inv_var" % name] = d.uncertainty.diagonal()
+            res["s2_%s_mask" % name] = d.mask
+    for name, dtype in (("f32", np.float32), ("f64", np.float64)):
+        kernels = rng.uniform(0.0, 0.5, (3, ny, nx)).astype(dtype)
+        kernels[:, 2, 3] = 0.0                               # bhr = 0 -> sigma clamps at 2.5e-3
+        mask = rng.random((ny, nx)) < 0.8
+        qa = rng.integers(0, 4, size=(ny, nx))
+        reader = object.__new__(mod.BHRObservations)
+        reader.emulator = "tip-emulator"
+        reader.get_brdf_descriptors = lambda band_no, the_date, _r=(kernels, mask, qa): _r
+        with np.errstate(divide="ignore", invalid="ignore"):
+            d = reader.get_band_data(date, 0)
+        assert d.emulator == "tip-emulator" and d.metadata is None
+        res["bhr_%s_kernels" % name] = kernels
+        res["bhr_%s_mask_in" % name] = mask
+        res["bhr_%s_qa" % name] = qa
+        res["bhr_%s_obs" % name] = d.observations
+        res["bhr_%s_inv_var" % name] = d.uncertainty.diagonal()
+        res["bhr_%s_mask" % name] = d.mask
+    np.savez_compressed(os.path.join(OUT, "kat_reader_ingest.npz"), **res)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     kafka = ref_shim.load()
     kat_sar(kafka)
     kat_s1_ingest(kafka)
+    kat_reader_ingest(kafka)
     kat_hessian(kafka)
     kat_propagators(kafka)
     kat_time_grid(kafka)

@@ -181,9 +181,9 @@ def test_scaled_reflectance_ingest_matches_reader_arithmetic(dtype):
         lo = 0 if dtype == np.uint16 else -30
         raw = rng.integers(lo, 6000, size=mask.shape).astype(dtype)
         raw[rng.random(mask.shape) < 0.1] = 0
-        rho, inv, m = kc.s2_ingest(raw.astype(np.float64) if dtype == np.float32 else raw)
+        rho, inv, m = kc.s2_ingest(raw)
         raws.append(syn.BandData(raw, kb.ScaledReflectance(), None, {"band": b}, gps[b]))
-        floats.append(syn.BandData(rho, inv, m, {"band": b}, gps[b]))
+        floats.append(syn.BandData(rho.astype(np.float64), inv, m, {"band": b}, gps[b]))
     date = dt.datetime(2017, 7, 3)
     inv_block = np.diag(1.0 / syn.SAIL_SIGMA ** 2)
     out = []
@@ -199,9 +199,8 @@ def test_scaled_reflectance_ingest_matches_reader_arithmetic(dtype):
     extra = rng.random(mask.shape) < 0.7
     kf = kb.LinearKalman(None, None, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS, prior=None)
     bufs = kf._stager.upload([raws[0]._replace(mask=extra)])
-    rho, inv, m = kc.s2_ingest(raws[0].observations.astype(np.float64) if dtype == np.float32 else raws[0].observations,
-                               ext_mask=extra)
-    y, r, mm = kc.gather_band(rho, inv.ravel(), m, mask)
+    rho, inv, m = kc.s2_ingest(raws[0].observations, ext_mask=extra)
+    y, r, mm = kc.gather_band(rho.astype(np.float64), inv.ravel(), m, mask)
     assert np.array_equal(bufs.y[0, :N].cpu().numpy(), y)
     assert np.array_equal(bufs.w[0, :N].cpu().numpy(), kc.gate_inverse_variance(r, mm))
     assert np.array_equal(bufs.m[0, :N].cpu().numpy().astype(bool), mm)
@@ -323,3 +322,26 @@ def test_sar_filter_run_from_raw_sigma0_equals_run_from_reader_outputs():
     for t in outs[0][0].output:
         assert np.array_equal(outs[0][0].output[t]["x"], outs[1][0].output[t]["x"])
         assert np.array_equal(outs[0][0].output[t]["diag"], outs[1][0].output[t]["diag"])
+
+
+def test_s2_and_bhr_ingest_match_the_unmodified_readers():
+    """Device ingest of raw Sentinel-2 reflectance (int16 / uint16 / float32) and of MODIS
+    kernel weights against rows gathered from the outputs of the unmodified readers
+    (fixture kat_reader_ingest): bit-exact."""
+    g = gio.load("kat_reader_ingest")
+    rng = np.random.default_rng(12)
+    shape = g["s2_i16_raw"].shape
+    mask = rng.random(shape) < 0.75
+    mask[2, 3] = True
+    N = int(mask.sum())
+    kf = kb.LinearKalman(None, None, mask, kb.create_prosail_observation_operator, syn.S2_PARAMETERS, prior=None)
+    cases = [(g["s2_%s_raw" % n], kb.ScaledReflectance(), None, "s2_" + n) for n in ("i16", "u16", "f32")]
+    cases += [(g["bhr_%s_kernels" % n], kb.BHRKernelWeights(g["bhr_%s_qa" % n]), g["bhr_%s_mask_in" % n], "bhr_" + n)
+              for n in ("f32", "f64")]
+    for obs, marker, in_mask, key in cases:
+        bufs = kf._stager.upload([syn.BandData(obs, marker, in_mask, {}, None)])
+        want_obs = np.nan_to_num(g[key + "_obs"].astype(np.float64), nan=0.0)
+        y, r, mm = kc.gather_band(want_obs, g[key + "_inv_var"], g[key + "_mask"], mask)
+        assert np.array_equal(bufs.y[0, :N].cpu().numpy(), y), key
+        assert np.array_equal(bufs.w[0, :N].cpu().numpy(), kc.gate_inverse_variance(r, mm)), key
+        assert np.array_equal(bufs.m[0, :N].cpu().numpy().astype(bool), mm), key

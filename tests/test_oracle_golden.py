@@ -322,3 +322,22 @@ def test_s1_ingest_matches_the_unmodified_reader():
             assert inv.dtype == np.float64
             assert np.array_equal(inv.ravel(), g["%s_%s_inv_var" % (name, pol)])
             assert np.isinf(inv[~m]).all() and np.isinf(inv[3, 5]) and np.isinf(inv[4, 6]) and m[3, 5] and m[4, 6]
+
+
+def test_s2_and_bhr_ingest_match_the_unmodified_readers():
+    """oracle s2_ingest / bhr_ingest against outputs of the unmodified
+    Sentinel2Observations.get_band_data and BHRObservations.get_band_data (fixture made
+    by oracle/make_golden.py:kat_reader_ingest with stand-ins for GDAL and the
+    un-vendored packages): bit-exact, dtypes included."""
+    g = gio.load("kat_reader_ingest")
+    for name in ("i16", "u16", "f32"):
+        rho, inv, m = kc.s2_ingest(g["s2_%s_raw" % name])
+        want = g["s2_%s_obs" % name]
+        assert rho.dtype == want.dtype and np.array_equal(rho, want)
+        assert inv.dtype == np.float64 and np.array_equal(inv.ravel(), g["s2_%s_inv_var" % name])
+        assert np.array_equal(m, g["s2_%s_mask" % name])
+    for name in ("f32", "f64"):
+        bhr, inv, m = kc.bhr_ingest(g["bhr_%s_kernels" % name], g["bhr_%s_mask_in" % name], g["bhr_%s_qa" % name])
+        assert np.array_equal(bhr, g["bhr_%s_obs" % name], equal_nan=True)
+        assert np.array_equal(inv.ravel(), g["bhr_%s_inv_var" % name])
+        assert np.array_equal(m, g["bhr_%s_mask" % name])
