@@ -495,12 +495,76 @@ def kat_reader_ingest(kafka):
     np.savez_compressed(os.path.join(OUT, "kat_reader_ingest.npz"), **res)
 
 
+def kat_output_stage(kafka):
+    """KafkaOutput.dump_data (input_output/observations.py:354-394), unmodified: the
+    module's ``gdal`` is replaced by a stand-in whose driver keeps the arrays handed to
+    WriteArray instead of writing GeoTIFFs."""
+    import datetime as dt
+    import scipy.sparse as sp
+    import kafka.input_output.observations as mod
+
+    written = {}
+
+    class _Band(object):
+        def __init__(self, name):
+            self.name = name
+
+        def WriteArray(self, a):
+            written[self.name] = np.array(a)
+
+    class _Dataset(object):
+        def __init__(self, name):
+            self.name = name
+
+        def SetProjection(self, p):
+            pass
+
+        def SetGeoTransform(self, g):
+            pass
+
+        def GetRasterBand(self, k):
+            return _Band(self.name)
+
+    class _Driver(object):
+        def Create(self, fname, nx, ny, nb, gdt, opts):
+            return _Dataset(os.path.basename(fname))
+
+    class _Gdal(object):
+        GDT_Float32 = 6
+
+        @staticmethod
+        def GetDriverByName(fmt):
+            return _Driver()
+
+    mod.gdal = _Gdal
+    rng = np.random.default_rng(41)
+    mask = _small_mask(rng, 23, 19)
+    N, P = int(mask.sum()), 3
+    names = ["lai", "cab", "sm"]
+    x = rng.standard_normal(N * P) * np.tile([3.0, 40.0, 0.2], N)
+    blocks = []
+    for _ in range(N):
+        g = rng.standard_normal((P, P))
+        blocks.append(g @ g.T + np.diag(rng.uniform(0.5, 50.0, P)))
+    P_inv = sp.block_diag(blocks).tocsr()
+    date = dt.datetime(2017, 7, 3)
+    out = mod.KafkaOutput(names, [0, 10, 0, 0, 0, -10], "proj", "/nowhere")
+    out.dump_data(date, x, None, P_inv, mask, P)
+    res = {"mask": mask, "x": x, "blocks": np.array(blocks)}
+    for ii, name in enumerate(names):
+        res["mean_%d" % ii] = written["%s_A2017184.tif" % name]
+        res["unc_%d" % ii] = written["%s_A2017184_unc.tif" % name]
+        assert res["mean_%d" % ii].dtype == np.float32 and res["unc_%d" % ii].dtype == np.float32
+    np.savez_compressed(os.path.join(OUT, "kat_output_stage.npz"), **res)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     kafka = ref_shim.load()
     kat_sar(kafka)
     kat_s1_ingest(kafka)
     kat_reader_ingest(kafka)
+    kat_output_stage(kafka)
     kat_hessian(kafka)
     kat_propagators(kafka)
     kat_time_grid(kafka)

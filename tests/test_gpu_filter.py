@@ -318,6 +318,24 @@ def test_raster_output_stage_matches_reference_arithmetic():
     assert np.array_equal(sync.last[1], got["mean"]) and np.array_equal(sync.last[2], got["unc"])
 
 
+def test_raster_output_stage_matches_the_unmodified_writer():
+    """RasterOutput against the arrays the unmodified KafkaOutput.dump_data hands to
+    GDAL's WriteArray (fixture kat_output_stage): float32 rasters, bit-exact, from host
+    inputs and from the device objects LinearKalman passes."""
+    from kafka_inferenceengine_b200.output import RasterOutput
+    g = gio.load("kat_output_stage")
+    mask, x, blocks = g["mask"], g["x"], g["blocks"]
+    P = blocks.shape[1]
+    for args in ((x, kc.blocks_to_sparse(blocks)),
+                 (DeviceVector.from_interleaved(x, P, gu.DEV), BlockDiag.from_blocks(blocks, gu.DEV))):
+        out = RasterOutput(["lai", "cab", "sm"], overlap=False)
+        out.dump_data(dt.datetime(2017, 7, 3), args[0], None, args[1], mask, P)
+        for ii in range(P):
+            assert out.last[1][ii].dtype == np.float32
+            assert np.array_equal(out.last[1][ii], g["mean_%d" % ii])
+            assert np.array_equal(out.last[2][ii], g["unc_%d" % ii])
+
+
 def test_run_with_prefetch_and_overlapped_output_matches_plain_run():
     """run() stages the next observation date while the current one is being
     solved and RasterOutput reads results back on a side stream: same rasters as

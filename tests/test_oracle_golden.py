@@ -341,3 +341,14 @@ def test_s2_and_bhr_ingest_match_the_unmodified_readers():
         assert np.array_equal(bhr, g["bhr_%s_obs" % name], equal_nan=True)
         assert np.array_equal(inv.ravel(), g["bhr_%s_inv_var" % name])
         assert np.array_equal(m, g["bhr_%s_mask" % name])
+
+
+def test_output_scatter_matches_the_unmodified_writer():
+    """oracle scatter_param / scatter_unc against the arrays the unmodified
+    KafkaOutput.dump_data hands to GDAL's WriteArray (fixture kat_output_stage)."""
+    g = gio.load("kat_output_stage")
+    P = g["blocks"].shape[1]
+    diag = g["blocks"][:, np.arange(P), np.arange(P)].ravel()
+    for ii in range(P):
+        assert np.array_equal(kc.scatter_param(g["x"], ii, P, g["mask"]), g["mean_%d" % ii])
+        assert np.array_equal(kc.scatter_unc(diag, ii, P, g["mask"]), g["unc_%d" % ii])
