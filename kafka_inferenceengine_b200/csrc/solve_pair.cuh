@@ -69,7 +69,13 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
             cp_async8(st + g * kPairPix, (g ? bd.y : bd.w) + i);
             if (bd.kind == KAFKA_BAND_ARRAYS) {
                 cp_async8(st + (2 + g) * kPairPix, (g ? bd.jac : bd.h0) + i);
-                for (int d = 1 + g; d < bd.n_planes; d += 2) cp_async8(st + (3 + d) * kPairPix, bd.jac + (int64_t)d * ld + i);
+                // running pointers and a predicated, fully unrolled loop: no 64-bit multiply and no branch per copy
+                const double* src = bd.jac + (int64_t)(1 + g) * ld + i;
+                double* dst = st + (4 + g) * kPairPix;
+                const int n_mine = (bd.n_planes - g) / 2;                    // planes 1+g, 3+g, ...
+#pragma unroll
+                for (int t = 0; t < KAFKA_MAX_DIM / 2; ++t, src += 2 * ld, dst += 2 * kPairPix)
+                    if (t < n_mine) cp_async8(dst, src);
             }
         }
         cp_async_commit();
