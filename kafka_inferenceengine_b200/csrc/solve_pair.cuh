@@ -101,17 +101,25 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
     const bool round32 = (prm.flags & KAFKA_ROUND_F32) != 0;
     bool domain_bad = false;
     double a[LA], rown[K], xp[P];
+    {   // packed entry c = r(r+1)/2 + q of row r = 2k + g; row starts are 4k + 2g + 3 planes apart, so the
+        // address is a running pointer (64-bit adds) instead of a 64-bit multiply per entry
+        const int64_t step = bcast ? 1 : ld;
+        const double* rowp = prm.pinv_f + (bcast ? 0 : il) + (int64_t)g * step;      // row g starts at c = g
+        const int64_t g2 = 2 * (int64_t)g * step;
 #pragma unroll
-    for (int k = 0; k < K; ++k)
+        for (int k = 0; k < K; ++k) {
+            const double* ep = rowp;
 #pragma unroll
-        for (int q = 0; q < 2 * k + 2; ++q) {
-            const int r = 2 * k + g;
-            const bool valid = q <= r && r < P;
-            const int c = r * (r + 1) / 2 + q;
-            double v = (q == r) ? 1.0 : 0.0;                        // padding row: decoupled unit block
-            if (valid) v = bcast ? prm.pinv_f[c] : ldg_stream(prm.pinv_f + (int64_t)c * ld + il);
-            a[k * (k + 1) + q] = v;
+            for (int q = 0; q < 2 * k + 2; ++q, ep += step) {
+                const int r = 2 * k + g;
+                const bool valid = q <= r && r < P;
+                double v = (q == r) ? 1.0 : 0.0;                    // padding row: decoupled unit block
+                if (valid) v = bcast ? *ep : ldg_stream(ep);
+                a[k * (k + 1) + q] = v;
+            }
+            rowp += (4 * k + 3) * step + g2;
         }
+    }
 #pragma unroll
     for (int p = 0; p < P; ++p) xp[p] = ldg_stream(prm.x_prev + (int64_t)p * ld + il);
     {   // rhs = P_f^-1 x_f: every lane spreads its own entries over a full-length vector, the pair adds up
@@ -184,13 +192,18 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
     cp_async_wait<0>();
 
     if (live && prm.a_out) {
+        double* rowp = prm.a_out + i + (int64_t)g * ld;                              // same walk as the prior load
+        const int64_t g2 = 2 * (int64_t)g * ld;
 #pragma unroll
-        for (int k = 0; k < K; ++k)
+        for (int k = 0; k < K; ++k) {
+            double* ep = rowp;
 #pragma unroll
-            for (int q = 0; q < 2 * k + 2; ++q) {
+            for (int q = 0; q < 2 * k + 2; ++q, ep += ld) {
                 const int r = 2 * k + g;
-                if (q <= r && r < P) stg_stream(prm.a_out + (int64_t)(r * (r + 1) / 2 + q) * ld + i, a[k * (k + 1) + q]);
+                if (q <= r && r < P) stg_stream(ep, a[k * (k + 1) + q]);
             }
+            rowp += (4 * k + 3) * ld + g2;
+        }
     }
 
     // ---- Cholesky, right-looking; 1/L_jj is left on the diagonal ----
