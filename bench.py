@@ -446,6 +446,7 @@ def run_other_workload(args):
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
             os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm = float(peaks.get("hbm_gbs", 6650.0))
+        c5_flags = _lib.SOLVE_PAIR if os.environ.get("KAFKA_C5_PAIR") else 0     # force the two-lanes-per-pixel kernel
         for Pn in [int(v) for v in os.environ.get("KAFKA_C5_PARAMS", "2,4,7,10,12,16").split(",")]:
             for Bn in (1, 4, 10, 13):
                 Lp = tri_count(Pn)
@@ -472,7 +473,7 @@ def run_other_workload(args):
                 def call():
                     _lib.check(lib.kafka_solve_bands(n, ld, Pn, arr, Bn, _lib.ptr(xp), _lib.ptr(xf), _lib.ptr(pinv),
                                                      _lib.ptr(xo), _lib.ptr(ao), None, None, _lib.ptr(n2), _lib.ptr(nb),
-                                                     _lib.ptr(scratch), 0, _lib.stream_ptr()), "kafka_solve_bands")
+                                                     _lib.ptr(scratch), c5_flags, _lib.stream_ptr()), "kafka_solve_bands")
                 ms = timed(call, 5, 2)
                 bytes_pp = 16 * Pn + 8 * Pn * (Pn + 1) + 8 * Pn + Bn * 8 * (3 + Pn)     # x_f,x_prev,x ; Pinv in + A out ; bands
                 rows.append({"n_params": Pn, "n_bands": Bn, "ms": ms, "Mpx_per_s": n / ms / 1e3,

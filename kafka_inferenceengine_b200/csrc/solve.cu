@@ -162,9 +162,10 @@ constexpr int kAsyncStages = KAFKA_ASYNC_STAGES;
 
 // Packed entries kept in registers: all of them up to n_params 12 (78 entries).  For 13..15
 // the first 124 - 4 n_params stay in registers and the remaining rows live in the thread's
-// own shared-memory column (measured: 13 -> 74 %, 14 -> 61 %, 15 -> 46 % of the HBM peak,
-// against 70 / 55 / 37 % with everything in registers and spilling).  16 is dispatched to the
-// two-lanes-per-pixel kernel of solve_pair.cuh instead.
+// own shared-memory column (measured: 13 -> 71-76 %, 14 -> 55-63 %, 15 -> 44-49 % of the HBM peak,
+// against 70 / 55 / 37 % with everything in registers and spilling).  From 14 the default is the
+// two-lanes-per-pixel kernel of solve_pair.cuh (59-64 %); the split stays for 13 and for callers
+// that pass sizes 14-15 without the pair kernel compiled in (KAFKA_PAIR_FROM_PARAMS).
 template <int P>
 struct SolveBlock {
     static constexpr int L = tri_count(P);

@@ -1,11 +1,13 @@
-// Two lanes per pixel: the update of solve_bands_kernel for the largest blocks (n_params 16:
-// 136 packed entries + the vectors do not fit one thread's registers, and spilling them costs
-// more than sharing the block).  Measured on B200, 4 M px, % of the HBM peak at 1 / 10 bands:
-// this kernel 55 / 40 at n_params 16, against 33 / 29 for solve_bands_kernel with spills; at
-// 13..15 the register + shared-memory split of solve_bands_kernel is faster (13: 72 vs 46 %),
-// so the pair kernel is the default only at 16 and selectable at any size (KAFKA_SOLVE_PAIR,
-// used by the tests).  ncu: 254 registers, 8 warps per SM, stalls on dependent-instruction
-// latency (wait, scoreboards) -- two warps per scheduler cannot hide the factorisation's chain.
+// Two lanes per pixel: the update of solve_bands_kernel for the largest blocks (n_params 14-16:
+// 105-136 packed entries + the vectors do not fit one thread's registers, and spilling them or
+// parking rows in shared memory costs more than sharing the block).  Measured on B200, 4 M px,
+// supplied Jacobians, % of the HBM peak at 1 / 10 bands (bench.py --workload c5):
+//     n_params        13        14        15        16
+//     this kernel   57 / 61   59 / 62   58 / 61   61 / 64
+//     one thread    76 / 71   63 / 55   49 / 44   33 / 29 (spills)
+// so the pair kernel is the default from 14 and selectable at any size (KAFKA_SOLVE_PAIR, used by
+// the tests).  ncu: 254 registers, 8 warps per SM, stalls on dependent-instruction latency (wait,
+// scoreboards) -- two warps per scheduler cannot hide the factorisation's chain.
 //
 // Lane g (0/1) of a pair owns the rows r = 2k + g of the packed lower triangle, k = 0..K-1,
 // K = ceil(P/2); row k of a lane sits at a[k(k+1) .. k(k+1)+2k+1] (lane 0's last slot of every
@@ -25,7 +27,7 @@
 namespace kafka {
 
 #ifndef KAFKA_PAIR_FROM_PARAMS
-#define KAFKA_PAIR_FROM_PARAMS 16
+#define KAFKA_PAIR_FROM_PARAMS 14
 #endif
 constexpr int kPairFromParams = KAFKA_PAIR_FROM_PARAMS;   // state sizes from here on use the pair kernel
 constexpr int kPairThreads = 2 * kSolveThreads;
