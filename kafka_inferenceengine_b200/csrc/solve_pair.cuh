@@ -164,8 +164,13 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
         const double y = in_ld ? st[kPairPix + slot] : 0.0;
         double J[P], h0;
         if (bd.kind == KAFKA_BAND_ARRAYS) {
+            if (bd.identity) {
 #pragma unroll
-            for (int p = 0; p < P; ++p) J[p] = bd.src[p] >= 0 ? st[(3 + bd.src[p]) * kPairPix + slot] : 0.0;
+                for (int p = 0; p < P; ++p) J[p] = st[(3 + p) * kPairPix + slot];
+            } else {
+#pragma unroll
+                for (int p = 0; p < P; ++p) J[p] = bd.src[p] >= 0 ? st[(3 + bd.src[p]) * kPairPix + slot] : 0.0;
+            }
             h0 = st[2 * kPairPix + slot];
         } else if (bd.kind == KAFKA_BAND_UNIFORM) {
             const bool on = w != 0.0;
