@@ -41,6 +41,17 @@ def _empty(rows, ld, device, dtype=torch.float64):
     return torch.empty((rows, ld), dtype=dtype, device=device)
 
 
+def rows_zero_padded(rows, n_pix, device, dtype=torch.float64):
+    """(rows, padded(n_pix)) buffer for kernels that write every pixel < n_pix of every
+    row: only the padding columns are cleared (a full-size fill is 0.16 ms per array at
+    15 M pixels, three to four arrays per date)."""
+    ld = padded(n_pix)
+    t = torch.empty((rows, ld), dtype=dtype, device=device)
+    if ld > n_pix:
+        t[:, n_pix:].zero_()
+    return t
+
+
 class PixelIndex(object):
     """Compaction of a boolean state mask: ``idx[k]`` = row-major raster index of
     the k-th True pixel (bit-exact with ``np.flatnonzero(mask.ravel())``)."""

@@ -8,7 +8,7 @@ import scipy.sparse as sp
 import torch
 
 from . import _lib
-from .device import padded
+from .device import padded, rows_zero_padded
 
 
 class BandBuffers(object):
@@ -17,10 +17,10 @@ class BandBuffers(object):
     def __init__(self, n_bands, pix, device):
         self.n_bands = n_bands
         self.pix = pix
-        ld = pix.ld
-        self.y = torch.zeros((n_bands, ld), dtype=torch.float64, device=device)
-        self.w = torch.zeros((n_bands, ld), dtype=torch.float64, device=device)
-        self.m = torch.zeros((n_bands, ld), dtype=torch.uint8, device=device)
+        # every gather writes all pixels of its band row; only the padding has to start at zero
+        self.y = rows_zero_padded(n_bands, pix.n_pix, device)
+        self.w = rows_zero_padded(n_bands, pix.n_pix, device)
+        self.m = rows_zero_padded(n_bands, pix.n_pix, device, torch.uint8)
 
 
 class ScaledReflectance(object):

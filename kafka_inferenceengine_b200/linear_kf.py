@@ -20,7 +20,7 @@ import torch
 
 from . import _lib
 from . import engine
-from .device import BlockDiag, DeviceBands, DeviceVector, PixelIndex, default_device
+from .device import BlockDiag, DeviceBands, DeviceVector, PixelIndex, default_device, rows_zero_padded
 from .inference import kf_tools
 from .inference.kf_tools import (DiagonalMatrix, IdentityModel, propagate_and_blend_prior,
                                  propagate_information_filter_LAI)
@@ -293,9 +293,13 @@ class LinearKalman(object):
         ws = self._workspace(n_bands)
         # the per-band outputs are handed to the caller at the end: fresh buffers per call
         # instead of a copy out of the workspace
-        ws.innov = torch.zeros_like(ws.innov)
+        # (the last solve of the loop writes every pixel of every band row)
+        if n_bands:
+            ws.innov = rows_zero_padded(n_bands, self.n_state_elems, self.device)
+        else:
+            ws.innov = torch.zeros_like(ws.innov)
         if ws.fwd is not None:
-            ws.fwd = torch.zeros_like(ws.fwd)
+            ws.fwd = rows_zero_padded(n_bands, self.n_state_elems, self.device) if n_bands else torch.zeros_like(ws.fwd)
         token = getattr(self, "_token", None)
         self._token = None
         bufs = self._stager.finish(token if token is not None else self._stager.stage(current_data))
