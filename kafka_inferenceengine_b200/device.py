@@ -157,7 +157,10 @@ class DeviceVector(object):
         if isinstance(x, torch.Tensor):
             t = x.to(device=device, dtype=torch.float64).contiguous().view(-1)
         else:
-            t = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float64).ravel()).to(device)
+            a = np.ascontiguousarray(x, dtype=np.float64).ravel()
+            if not a.flags.writeable:                     # e.g. a slice of an .npz: torch wants a writable source
+                a = a.copy()
+            t = torch.from_numpy(a).to(device)
         if t.numel() % n_params:
             raise ValueError("state vector length %d is not a multiple of n_params=%d" % (t.numel(), n_params))
         n_pix = t.numel() // n_params
