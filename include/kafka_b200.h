@@ -189,11 +189,14 @@ int kafka_packed_diagonal(const double* a_packed, int64_t ld, int64_t n_pix, int
  * Host-side packing of one emulator (fields of gp_emulator.GaussianProcess:
  * inputs[T][D], theta[D+2] = LOG hyper-parameters, invQt[T]) into the table the
  * kernels stream through shared memory.  Table = kafka_gp_table_doubles(T,D)
- * doubles: theta_e[D], centre[D], s_f, nugget, wide, 0, then T rows
- * {L zh[D], L e, alpha} with L = 1024/ln2 (exponents in units of ln2/1024), D
- * padded to even; wide != 0 marks a training set so spread out (a point more
- * than ~1000 length scales from the centre) that the kernels keep their fully
- * range-checked exponential. */
+ * doubles: theta_e[D], centre[D], s_f, nugget, wide, L cbar, then T rows
+ * {L zh[D], L e, alpha, L e2, sign} with L = 1024/ln2 (exponents in units of
+ * ln2/1024), D padded to even; e2 = e + ln|alpha| - cbar with cbar the mean of
+ * ln|alpha| (the linearise kernel forms alpha k in one exponential), sign = 0 or
+ * 0x80000000 as an integer in the slot's low word; wide != 0 marks a training
+ * set so spread out (a point more than ~1000 length scales from the centre, or
+ * weights more than e^100 apart) that the kernels keep their fully range-checked
+ * exponential.  Weights must be finite (KAFKA_E_BADARG otherwise). */
 int64_t kafka_gp_table_doubles(int n_train, int n_dim);
 int kafka_gp_pack_host(const double* inputs_host, const double* theta_host,
                        const double* invqt_host, int n_train, int n_dim, double* table_host);

@@ -15,7 +15,7 @@
 // 5.4e-16).  The per-pixel factor exp(-0.5 sum theta x'^2) is pulled out of the loop and
 // applied once at the end (a warp keeps it inside the exponent when one of its pixels is so
 // far from the centre that the un-shifted exponent could overflow).  Per (pixel, band,
-// training point): 2D FMAs + ~9 fp64 ops, i.e. 29 fp64-pipe instructions at D=10 against
+// training point): 2D FMAs + 8 fp64 ops, i.e. 28 fp64-pipe instructions at D=10 against
 // the 5D+28 = 78 flops of the textbook form.  The training table (T rows of {zh[D], e,
 // alpha}) is staged once per CTA in shared memory by a TMA bulk copy and then read as
 // warp-wide broadcasts.  The kernel is bound by the fp64 pipe, not by HBM.
@@ -55,8 +55,13 @@ __device__ __align__(16) const double g_exp2_tab[kExpN] = {
 
 // ---- table layout -----------------------------------------------------------
 __host__ __device__ constexpr int dpad(int D) { return (D + 1) & ~1; }
-__host__ __device__ constexpr int tab_hdr(int D) { return 2 * dpad(D) + 4; }   // theta_e, centre, s_f, nugget, wide, 0
-__host__ __device__ constexpr int tab_row(int D) { return dpad(D) + 2; }       // zh[DP], e, alpha
+__host__ __device__ constexpr int tab_hdr(int D) { return 2 * dpad(D) + 4; }   // theta_e, centre, s_f, nugget, wide, L*cbar
+// row: zh[DP], e, alpha, then the pair the linearise loop reads instead of {e, alpha}:
+//   e2  = e + L (ln|alpha| - cbar)   -- the weight's magnitude folded into the exponent (cbar = mean ln|alpha|,
+//                                       applied once per pixel after the loop): one DMUL fewer per evaluation
+//   sgn = 0 or 0x80000000 as an integer in the slot's low word -- XOR-ed into the result's high word: the
+//                                       weight's sign (a zero weight gets e2 = -2^29, i.e. an exact or near zero)
+__host__ __device__ constexpr int tab_row(int D) { return dpad(D) + 4; }
 
 // ---- exp in base 2^(1/N): argument already scaled by L = N/ln2 ----------------------
 #if KAFKA_EXP_LOG2N == 6
@@ -92,16 +97,35 @@ constexpr double kFarShift = 600.0 * kL;                 // beyond this the per-
 // the order of 2^-1021 instead of 0 -- three integer instructions fewer per evaluation.
 // |rel err| < 6e-16.  NaN / +inf / overflow are NOT handled here: callers check their inputs
 // once per pixel, outside the hot loop.
-template <bool kChecked = true>
-__device__ __forceinline__ double exp_scaled(double a, const double* __restrict__ tab) {
+// The evaluation comes in two halves so that a caller with several arguments can issue all the
+// table loads before the first polynomial (source order is what the scheduler follows when
+// registers are tight: with the load written after the polynomial it was issued right before its
+// use and every evaluation waited out the shared-memory latency).
+struct ExpPart {
+    double r;       // a - rint(a), exact, |r| <= 1/2
+    double tv;      // 2^((k mod N)/N) from the table
+    int k;          // rint(a)
+};
+
+__device__ __forceinline__ ExpPart exp_lookup(double a, const double* __restrict__ tab) {
+    ExpPart e;
 #if KAFKA_EXP_F2I
-    const int k = __double2int_rn(a);
-    const double r = a - (double)k;                      // exact, |r| <= 1/2
+    e.k = __double2int_rn(a);
+    e.r = a - (double)e.k;
 #else
     const double t = a + c_exp_poly[5];
-    const int k = __double2loint(t);
-    const double r = a - (t - c_exp_poly[5]);            // exact, |r| <= 1/2
+    e.k = __double2loint(t);
+    e.r = a - (t - c_exp_poly[5]);
 #endif
+    e.tv = tab[e.k & (kExpN - 1)];
+    return e;
+}
+
+// sgn (0 or 0x80000000) is XOR-ed into the result's high word: the sign of the result.
+template <bool kChecked>
+__device__ __forceinline__ double exp_finish(const ExpPart& e, double a, int sgn = 0) {
+    const double r = e.r;
+    const int k = e.k;
 #if KAFKA_EXP_LOG2N == 6
     double p = fma(r, c_exp_poly[0], c_exp_poly[1]);
     p = fma(p, r, c_exp_poly[2]);
@@ -114,10 +138,10 @@ __device__ __forceinline__ double exp_scaled(double a, const double* __restrict_
 #endif
     p = fma(p, r, c_exp_poly[4]);
     p = fma(p, r, 1.0);
-    const double v = tab[k & (kExpN - 1)] * p;           // in (0.99, 2.01)
+    const double v = e.tv * p;                           // in (0.99, 2.01)
     if constexpr (!kChecked) {
-        const int e = max(k >> kExpLog2N, -1021);
-        return __hiloint2double(__double2hiint(v) + (e << 20), __double2loint(v));
+        const int ex = max(k >> kExpLog2N, -1021);
+        return __hiloint2double((__double2hiint(v) + (ex << 20)) ^ sgn, __double2loint(v));
     } else {
         const int hi_n = __double2hiint(v) + ((k >> kExpLog2N) << 20);
         const int lo_n = __double2loint(v);
@@ -129,8 +153,13 @@ __device__ __forceinline__ double exp_scaled(double a, const double* __restrict_
             "selp.b32 %1, 0, %5, p;\n\t}"
             : "=r"(hi), "=r"(lo)
             : "r"(__double2hiint(a)), "r"(0x80000000u + kHiUnder), "r"(hi_n), "r"(lo_n));
-        return __hiloint2double(hi, lo);
+        return __hiloint2double(hi ^ sgn, lo);
     }
+}
+
+template <bool kChecked = true>
+__device__ __forceinline__ double exp_scaled(double a, const double* __restrict__ tab) {
+    return exp_finish<kChecked>(exp_lookup(a, tab), a);
 }
 
 // ---- linearise: mean + Jacobian for every (pixel, band) -------------------------
@@ -188,13 +217,21 @@ __device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, i
             zh[d] = v.x;
             zh[d + 1] = v.y;
         }
-        const double2 ea = *reinterpret_cast<const double2*>(row + DP);
+        const double2 ea = *reinterpret_cast<const double2*>(row + DP + 2);       // {e2, sgn}
+        const int sgn = __double2loint(ea.y);                                    // 0 or 0x80000000: the weight's sign
+        double a[PPT];
+        ExpPart ep[PPT];
 #pragma unroll
         for (int pp = 0; pp < PPT; ++pp) {
-            double a = kShiftInside ? ea.x + sh[pp] : ea.x;
+            a[pp] = kShiftInside ? ea.x + sh[pp] : ea.x;
 #pragma unroll
-            for (int d = 0; d < D; ++d) a = fma(zh[d], xr[pp][d], a);
-            const double w = exp_scaled<kShiftInside || !KAFKA_EXP_CLAMP>(a, tab64) * ea.y;
+            for (int d = 0; d < D; ++d) a[pp] = fma(zh[d], xr[pp][d], a[pp]);
+        }
+#pragma unroll
+        for (int pp = 0; pp < PPT; ++pp) ep[pp] = exp_lookup(a[pp], tab64);
+#pragma unroll
+        for (int pp = 0; pp < PPT; ++pp) {
+            const double w = exp_finish<kShiftInside || !KAFKA_EXP_CLAMP>(ep[pp], a[pp], sgn);  // = k_j alpha_j / exp(cbar)
             mu[pp] += w;
 #pragma unroll
             for (int d = 0; d < D; ++d) G[pp][d] = fma(w, zh[d], G[pp][d]);
@@ -276,15 +313,30 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
         // sh inside the exponent so that nothing can overflow
         if (!__any_sync(0xffffffffu, far)) {
             gp_accumulate<D, PPT, false>(rows, T, xr, sh, mu, G, s_exp);
+            // L * mean ln|alpha|, taken out of every row's exponent (read here, not before the loop: more
+            // registers live across it push the polynomial's constants back into the loop)
+            const double lcbar = smem[2 * DP + 3];
 #pragma unroll
             for (int pp = 0; pp < PPT; ++pp) {
-                const double scale = exp_scaled(sh[pp], s_exp);
+                // the pixel's own factor is recomputed (same operations, same bits as sh[pp]) rather than
+                // kept in registers across the loop
+                double s2 = 0.0;
+#pragma unroll
+                for (int d = 0; d < D; ++d) s2 = fma(theta_e[d] * xr[pp][d], xr[pp][d], s2);
+                const double scale = exp_scaled((-0.5 * kL) * s2 + lcbar, s_exp);
                 mu[pp] *= scale;
 #pragma unroll
                 for (int d = 0; d < D; ++d) G[pp][d] *= scale;
             }
         } else {
             gp_accumulate<D, PPT, true>(rows, T, xr, sh, mu, G, s_exp);
+            const double scale = exp_scaled(smem[2 * DP + 3], s_exp);
+#pragma unroll
+            for (int pp = 0; pp < PPT; ++pp) {
+                mu[pp] *= scale;
+#pragma unroll
+                for (int d = 0; d < D; ++d) G[pp][d] *= scale;
+            }
         }
 #pragma unroll
         for (int pp = 0; pp < PPT; ++pp)
@@ -560,6 +612,8 @@ int kafka_gp_pack_host(const double* inputs, const double* theta, const double* 
                        double* table) {
     KAFKA_CHECK_ARG(inputs && theta && invqt && table, "kafka_gp_pack_host: null pointer");
     KAFKA_CHECK_ARG(T >= 1 && D >= 1 && D <= KAFKA_MAX_DIM, "kafka_gp_pack_host: T=%d D=%d unsupported", T, D);
+    for (int j = 0; j < T; ++j)
+        KAFKA_CHECK_ARG(fabs(invqt[j]) <= 1.79769313486231570815e308, "kafka_gp_pack_host: weight %d is not finite", j);
     const int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     for (int k = 0; k < HDR + T * RS; ++k) table[k] = 0.0;
     double* theta_e = table;
@@ -572,22 +626,50 @@ int kafka_gp_pack_host(const double* inputs, const double* theta, const double* 
     }
     table[2 * DP] = exp(theta[D]);
     table[2 * DP + 1] = exp(theta[D + 1]);
+    // cbar = mean ln|alpha| over the non-zero weights: keeps the folded exponents e2 as small as the plain ones
+    long double lsum = 0;
+    int n_nz = 0;
+    for (int j = 0; j < T; ++j)
+        if (invqt[j] != 0.0) {
+            lsum += log(fabs(invqt[j]));
+            ++n_nz;
+        }
+    double cbar = n_nz ? (double)(lsum / n_nz) : 0.0;
+    if (!(fabs(cbar) < 300.0)) cbar = 0.0;
+    table[2 * DP + 3] = kL * cbar;
     double wide = 0.0;
     for (int j = 0; j < T; ++j) {
         double* row = table + HDR + (size_t)j * RS;
         double c = 0.0;
+        long double cl = 0;                           // the same sum in extended precision, for e2
         for (int d = 0; d < D; ++d) {
             double xc = inputs[(size_t)j * D + d] - centre[d];
             double zh = theta_e[d] * xc;
             c = fma(zh, xc, c);
+            cl += (long double)zh * xc;
             row[d] = kL * zh;                         // rows are stored in units of 1/L
         }
         row[DP] = kL * (theta[D] - 0.5 * c);
         row[DP + 1] = invqt[j];
+        const double al = invqt[j];
+        double lshift = 0.0;                          // ln|alpha| - cbar
+        uint64_t sgn = 0;
+        if (al != 0.0) {
+            const long double ll = logl(fabsl((long double)al)) - (long double)cbar;
+            lshift = (double)ll;
+            // one rounding in all: an outlying training point puts |e2| at 1e10 and more, where every
+            // intermediate rounding in double would show in the kernel value
+            row[DP + 2] = (double)((long double)kL * (((long double)theta[D] - 0.5L * cl) + ll));
+            sgn = al < 0.0 ? 0x80000000ull : 0;
+        } else {
+            row[DP + 2] = -536870912.0;               // a zero weight: an exponent far below any underflow
+        }
+        memcpy(row + DP + 3, &sgn, sizeof(sgn));
         // exponent of this row at any pixel the kernel does not treat as far (sum theta x'^2 < 1200):
-        // |a| <= L (|ln s_f| + c/2 + sqrt(1200 c)).  The unchecked exp needs |a| < 2^30.
-        const double bound = kL * (fabs(theta[D]) + 0.5 * c + sqrt(1200.0 * c));
-        if (!(bound < 1073741824.0)) wide = 1.0;
+        // |a| <= L (|ln s_f| + c/2 + |ln|alpha| - cbar| + sqrt(1200 c)).  The unchecked exp needs |a| < 2^30;
+        // 2^29 leaves room for the zero-weight rows' offset of -2^29.
+        const double bound = kL * (fabs(theta[D]) + 0.5 * c + fabs(lshift) + sqrt(1200.0 * c));
+        if (!(bound < 536870912.0) || fabs(lshift) > 100.0) wide = 1.0;
     }
     table[2 * DP + 2] = wide;
     return 0;

@@ -45,8 +45,8 @@ def test_struct_layouts_match_header():
 def test_bad_arguments_are_rejected_without_a_gpu():
     lib = _lib.get_lib()
     assert lib.kafka_gp_table_doubles(250, 17) == -1
-    assert lib.kafka_gp_table_doubles(250, 10) == 2 * 10 + 4 + 250 * 12
-    assert lib.kafka_gp_table_doubles(250, 7) == 2 * 8 + 4 + 250 * 10
+    assert lib.kafka_gp_table_doubles(250, 10) == 2 * 10 + 4 + 250 * 14
+    assert lib.kafka_gp_table_doubles(250, 7) == 2 * 8 + 4 + 250 * 12
     assert lib.kafka_solve_scratch_doubles(-1) == -1
     assert lib.kafka_compact_scratch_elems(4097) == 4
     st = lib.kafka_interleaved_to_planar(None, 10, 0, None, 32, None)
@@ -71,19 +71,26 @@ def test_gp_pack_host_matches_numpy():
         alpha = rng.standard_normal(T)
         tab = _lib.gp_pack(X, theta, alpha)
         DP = (D + 1) & ~1
-        assert tab.size == 2 * DP + 4 + T * (DP + 2)
+        assert tab.size == 2 * DP + 4 + T * (DP + 4)
         e = np.exp(theta)
         c = X.mean(axis=0)
         assert np.allclose(tab[:D], e[:D], rtol=1e-15)
         assert np.allclose(tab[DP:DP + D], c, rtol=1e-14, atol=1e-16)
         assert tab[2 * DP] == pytest.approx(e[D], rel=1e-15)
-        assert tab[2 * DP + 2] == 0.0 and tab[2 * DP + 3] == 0.0     # not a "wide" training set
-        rows = tab[2 * DP + 4:].reshape(T, DP + 2)
-        Xc = X - tab[DP:DP + D]
+        cbar = np.log(np.abs(alpha)).mean()
         L = 1024.0 / np.log(2.0)                     # rows are in units of ln2/1024
+        assert tab[2 * DP + 2] == 0.0                                # not a "wide" training set
+        assert tab[2 * DP + 3] == pytest.approx(L * cbar, rel=1e-14)
+        rows = tab[2 * DP + 4:].reshape(T, DP + 4)
+        Xc = X - tab[DP:DP + D]
         assert np.allclose(rows[:, :D], L * e[:D] * Xc, rtol=4e-16, atol=0)
         assert np.allclose(rows[:, DP], L * (theta[D] - 0.5 * (e[:D] * Xc * Xc).sum(axis=1)), rtol=1e-14)
         assert np.array_equal(rows[:, DP + 1], alpha)
+        # the pair the linearise loop reads: exponent with ln|alpha| - cbar folded in, and the sign bit of
+        # the weight as an integer in the slot's low word (XOR-ed into the result's high word)
+        e_plain = theta[D] - 0.5 * (e[:D] * Xc * Xc).sum(axis=1)
+        assert np.allclose(rows[:, DP + 2], L * (e_plain + np.log(np.abs(alpha)) - cbar), rtol=1e-13, atol=1e-9)
+        assert np.array_equal(rows[:, DP + 3].view(np.uint64), np.where(alpha < 0, 0x80000000, 0).astype(np.uint64))
         if DP != D:
             assert np.all(rows[:, D] == 0.0)
     with pytest.raises(ValueError):
@@ -94,3 +101,9 @@ def test_gp_pack_host_matches_numpy():
     X[0] = 6000.0
     tab = _lib.gp_pack(X, np.zeros(4), np.ones(4))
     assert tab[2 * 2 + 2] == 1.0
+    # a zero weight gets an exponent far below underflow and no sign offset; a non-finite one is refused
+    tab = _lib.gp_pack(np.zeros((3, 2)), np.zeros(4), np.array([0.0, 2.0, -2.0]))
+    rows = tab[2 * 2 + 4:].reshape(3, 2 + 4)
+    assert rows[0, 4] == -2.0 ** 29 and rows[0, 5].view(np.uint64) == 0 and rows[2, 5].view(np.uint64) == 0x80000000
+    with pytest.raises(_lib.KafkaCudaError):
+        _lib.gp_pack(np.zeros((3, 2)), np.zeros(4), np.array([1.0, np.nan, 1.0]))
