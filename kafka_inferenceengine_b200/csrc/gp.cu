@@ -207,9 +207,9 @@ __device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, i
                                               const double (&sh)[PPT], double (&mu)[PPT], double (&G)[PPT][D],
                                               const double* __restrict__ tab64) {
     constexpr int DP = dpad(D), RS = tab_row(D);
+    const double* const rows_end = rows + (size_t)T * RS;       // the row pointer is the loop variable: no separate counter
 #pragma unroll kGpUnroll
-    for (int j = 0; j < T; ++j) {
-        const double* row = rows + j * RS;
+    for (const double* row = rows; row != rows_end; row += RS) {
         double zh[DP];
 #pragma unroll
         for (int d = 0; d < DP; d += 2) {
