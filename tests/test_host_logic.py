@@ -156,3 +156,16 @@ def test_get_chunks_matches_reference_tiling():
         from kafka.input_output.utils import get_chunks as ref_chunks
         for nx, ny, bs in ((600, 500, [256, 256]), (235, 204, [128, 128]), (10980, 10980, [4096, 1000]), (5, 3, [7, 7])):
             assert list(get_chunks(nx, ny, bs)) == list(ref_chunks(nx, ny, block_size=bs))
+
+
+def test_rows_zero_padded_clears_only_the_padding():
+    """Band-row buffers are handed to kernels that write every pixel below n_pix; only
+    the padding columns up to the aligned leading dimension have to start at zero."""
+    import torch
+    from kafka_inferenceengine_b200.device import padded, rows_zero_padded
+    for n in (0, 1, 31, 32, 1000):
+        t = rows_zero_padded(3, n, torch.device("cpu"))
+        assert t.shape == (3, padded(n)) and t.dtype == torch.float64
+        assert bool((t[:, n:] == 0).all())
+    m = rows_zero_padded(2, 5, torch.device("cpu"), torch.uint8)
+    assert m.dtype == torch.uint8 and bool((m[:, 5:] == 0).all())
