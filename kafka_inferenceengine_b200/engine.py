@@ -95,13 +95,13 @@ class _Slot(object):
 
 class StagedDate(object):
     """Hand-over between ``stage`` and ``finish``."""
-    __slots__ = ("slot", "n_bands", "device_data", "raw", "one_event", "bhr")
+    __slots__ = ("slot", "n_bands", "device_data", "raw", "one_event", "sources")
 
-    def __init__(self, slot, n_bands, device_data=None, raw=None, one_event=False, bhr=None):
-        # bhr: band -> ("bhr", kernel_type, kernels, mask, qa) or ("s1", raw_type, sigma0, marker), device tensors
+    def __init__(self, slot, n_bands, device_data=None, raw=None, one_event=False, sources=None):
+        # sources: band -> ("bhr", kernel_type, kernels, mask, qa) or ("s1", raw_type, sigma0, marker), device tensors
         self.slot, self.n_bands, self.device_data = slot, n_bands, device_data
         self.raw = raw or {}                 # band -> (raw_type, ScaledReflectance, has_mask)
-        self.bhr = bhr or {}                 # bands ingested from source rasters uploaded as they are
+        self.sources = sources or {}         # bands ingested from source rasters uploaded as they are
         self.one_event = one_event           # all bands went up in one copy: only copied[n_bands-1] was recorded
 
 
@@ -189,13 +189,13 @@ class ObservationStager(object):
             self._copy_stream.wait_event(slot.gathered)           # device rasters no longer being gathered
         parts = max(1, min(self.N_THREADS, n // (1 << 20)))       # split big rasters across the pool
         raw = {}
-        bhr = {}
+        sources = {}
         for b, d in enumerate(current_data):
             if isinstance(d.uncertainty, BHRKernelWeights):
-                bhr[b] = self._upload_bhr(d, n)
+                sources[b] = self._upload_bhr(d, n)
                 continue
             if isinstance(d.uncertainty, BackscatterSigma0):
-                bhr[b] = self._upload_backscatter(d, n)
+                sources[b] = self._upload_backscatter(d, n)
                 continue
             if isinstance(d.uncertainty, ScaledReflectance):
                 dt_ = np.asarray(d.observations).dtype
@@ -206,12 +206,12 @@ class ObservationStager(object):
             slot.h_raw = torch.empty((slot.cap, n), dtype=torch.int32).pin_memory()
             slot.d_raw = torch.empty((slot.cap, n), dtype=torch.int32, device=self.device)
             slot.np_raw = slot.h_raw.numpy()
-        holders = [None if (b in raw or b in bhr) else _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
+        holders = [None if (b in raw or b in sources) else _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
                    for b, d in enumerate(current_data)]
         futures = []
         small = n < (1 << 18)                          # tiny rasters: the pool's hand-over costs more than the copy
         for b, d in enumerate(current_data):
-            if small or b in bhr:
+            if small or b in sources:
                 futures.append([])
             elif b in raw:
                 futures.append([self._pool.submit(self._stage_raw, slot, b, d, raw[b], n * k // parts,
@@ -219,7 +219,7 @@ class ObservationStager(object):
             else:
                 futures.append([self._pool.submit(self._stage_part, slot, b, holders[b], n * k // parts,
                                                   n * (k + 1) // parts) for k in range(parts)])
-        if small and not raw and not bhr:
+        if small and not raw and not sources:
             # tiny rasters, the reference's float rasters: launch overhead is all there is, so
             # stage every band inline and queue ONE copy per array instead of three per band
             for b in range(nb):
@@ -232,7 +232,7 @@ class ObservationStager(object):
             self.h2d_bytes += nb * n * 17
             return StagedDate(slot, nb, raw=raw, one_event=True)
         for b in range(nb):
-            if b in bhr:
+            if b in sources:
                 slot.copied[b].record(self._copy_stream)           # uploaded above, on the copy stream
                 continue
             if small:
@@ -258,7 +258,7 @@ class ObservationStager(object):
                     slot.d_msk[b].copy_(slot.h_msk[b], non_blocking=True)
                     self.h2d_bytes += n * 17
                 slot.copied[b].record(self._copy_stream)
-        return StagedDate(slot, nb, raw=raw, bhr=bhr)
+        return StagedDate(slot, nb, raw=raw, sources=sources)
 
     def _upload_bhr(self, d, n):
         """Kernel weights (3, ny, nx), quality level and mask of one MODIS band to the device
@@ -310,8 +310,8 @@ class ObservationStager(object):
             return out
         for b in range(nb):
             main.wait_event(slot.copied[b])
-            if b in token.bhr and token.bhr[b][0] == "s1":
-                _, rtype, rt, marker = token.bhr[b]
+            if b in token.sources and token.sources[b][0] == "s1":
+                _, rtype, rt, marker = token.sources[b]
                 with torch.cuda.device(self.device):
                     _lib.check(lib.kafka_gather_backscatter_band(_lib.ptr(rt), rtype, _lib.ptr(pix.idx), pix.n_pix,
                                                                  marker.missing_value, marker.rel_sigma,
@@ -320,8 +320,8 @@ class ObservationStager(object):
                                "kafka_gather_backscatter_band")
                 rt.record_stream(main)           # allocated on the copy stream, read on the main stream
                 continue
-            if b in token.bhr:
-                _, ktype, kt, mt, qt = token.bhr[b]
+            if b in token.sources:
+                _, ktype, kt, mt, qt = token.sources[b]
                 with torch.cuda.device(self.device):
                     _lib.check(lib.kafka_gather_bhr_band(_lib.ptr(kt), ktype, kt.stride(0), _lib.ptr(mt), _lib.ptr(qt),
                                                          _lib.ptr(pix.idx), pix.n_pix, _lib.ptr(out.y[b]),
