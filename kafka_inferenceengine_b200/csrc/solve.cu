@@ -126,13 +126,13 @@ __device__ __forceinline__ void band_row(const SolveBandDev& bd, int64_t ld, int
     }
 }
 
-template <int P>
+template <int P, bool kAllIdentity = false>
 __device__ __forceinline__ void band_row_staged(const SolveBandDev& bd, const double* __restrict__ st, int n_dim_max,
                                                 const double* __restrict__ uni, const double (&xp)[P], double w,
                                                 double (&J)[P], double& h0, bool round32, bool& domain_bad) {
     // stage layout: [w | y | h0 | jac plane 0 .. n_dim-1], kSolveThreads doubles each
-    if (bd.kind == KAFKA_BAND_ARRAYS) {
-        if (bd.identity) {                                  // the usual case: literal offsets, no mapper look-ups
+    if (kAllIdentity || bd.kind == KAFKA_BAND_ARRAYS) {
+        if (kAllIdentity || bd.identity) {                                  // the usual case: literal offsets, no mapper look-ups
 #pragma unroll
             for (int p = 0; p < P; ++p) J[p] = st[(3 + p) * kSolveThreads + threadIdx.x];
         } else {
@@ -179,7 +179,9 @@ struct SolveBlock {
     using type = typename std::conditional<R == L, RegBlock<L>, SplitBlock<L, R, kSolveThreads>>::type;
 };
 
-template <int P>
+// kAllIdentity: every band is a per-pixel array band whose P Jacobian planes map one-to-one onto the state
+// (the emulator-in-the-loop and supplied-Jacobian cases): no band-kind dispatch, no plane-count predicates.
+template <int P, bool kAllIdentity = false>
 __global__ void __launch_bounds__(kSolveThreads)
 solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     constexpr int L = tri_count(P);
@@ -201,7 +203,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
             double* st = stages + (b % kAsyncStages) * stage_doubles + threadIdx.x;
             cp_async8(st, bd.w + i);
             cp_async8(st + kSolveThreads, bd.y + i);
-            if (bd.kind == KAFKA_BAND_ARRAYS) {
+            if (kAllIdentity || bd.kind == KAFKA_BAND_ARRAYS) {
                 cp_async8(st + 2 * kSolveThreads, bd.h0 + i);
                 // running pointers and a predicated, fully unrolled loop (a band has at most P planes): the
                 // rolled loop cost a 64-bit multiply and a branch per copy (ncu: 17 % of the stall samples)
@@ -209,7 +211,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
                 double* dst = st + 3 * kSolveThreads;
 #pragma unroll
                 for (int d = 0; d < P; ++d, src += ld, dst += kSolveThreads)
-                    if (d < bd.n_planes) cp_async8(dst, src);
+                    if (kAllIdentity || d < bd.n_planes) cp_async8(dst, src);
             }
         }
         cp_async_commit();                                          // one group per band, even when empty
@@ -218,7 +220,8 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     for (int b = 0; b < kAsyncStages - 1; ++b) issue(b);
 
     bool any_uniform = false;
-    for (int b = 0; b < prm.n_bands; ++b) any_uniform |= prm.bands[b].kind == KAFKA_BAND_UNIFORM;
+    if (!kAllIdentity)
+        for (int b = 0; b < prm.n_bands; ++b) any_uniform |= prm.bands[b].kind == KAFKA_BAND_UNIFORM;
     if (any_uniform) {                                              // same decision in every thread
         for (int k = threadIdx.x; k < prm.n_bands * (P + 1); k += kSolveThreads) {
             const int b = k / (P + 1), p = k - b * (P + 1);
@@ -262,7 +265,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
         const double w = in_ld ? st[threadIdx.x] : 0.0;
         const double y = in_ld ? st[kSolveThreads + threadIdx.x] : 0.0;
         double J[P], h0;
-        band_row_staged<P>(bd, st, n_dim_max, s_uni[b], xp, w, J, h0, round32, domain_bad);
+        band_row_staged<P, kAllIdentity>(bd, st, n_dim_max, s_uni[b], xp, w, J, h0, round32, domain_bad);
         double yp = y - h0;
 #pragma unroll
         for (int p = 0; p < P; ++p) yp = fma(J[p], xp[p], yp);
@@ -506,8 +509,10 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
         return launch_status("reduce_partials_kernel");
     }
+    bool all_identity = n_bands > 0;
+    for (int b = 0; b < n_bands; ++b) all_identity = all_identity && prm.bands[b].identity;
     KAFKA_DISPATCH_P(n_params, {
-        auto kern = solve_bands_kernel<kP>;
+        auto kern = all_identity ? solve_bands_kernel<kP, true> : solve_bands_kernel<kP, false>;
         const size_t smem = ring + (size_t)(SolveBlock<kP>::L - SolveBlock<kP>::R) * kSolveThreads * sizeof(double);
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
