@@ -126,12 +126,16 @@ __device__ __forceinline__ void band_row(const SolveBandDev& bd, int64_t ld, int
     }
 }
 
-template <int P, bool kAllIdentity = false>
+// kMode: 0 = any mix of band kinds; 1 = every band a per-pixel array band with the identity mapper;
+// 2 = every band shares one linearisation (KAFKA_BAND_UNIFORM).  1 and 2 are chosen by the host and drop the
+// band-kind dispatch, the plane-count predicates and the mapper look-ups from the band loop.
+template <int P, int kMode = 0>
 __device__ __forceinline__ void band_row_staged(const SolveBandDev& bd, const double* __restrict__ st, int n_dim_max,
                                                 const double* __restrict__ uni, const double (&xp)[P], double w,
                                                 double (&J)[P], double& h0, bool round32, bool& domain_bad) {
     // stage layout: [w | y | h0 | jac plane 0 .. n_dim-1], kSolveThreads doubles each
-    if (kAllIdentity || bd.kind == KAFKA_BAND_ARRAYS) {
+    constexpr bool kAllIdentity = kMode == 1;
+    if (kMode != 2 && (kAllIdentity || bd.kind == KAFKA_BAND_ARRAYS)) {
         if (kAllIdentity || bd.identity) {                                  // the usual case: literal offsets, no mapper look-ups
 #pragma unroll
             for (int p = 0; p < P; ++p) J[p] = st[(3 + p) * kSolveThreads + threadIdx.x];
@@ -141,7 +145,7 @@ __device__ __forceinline__ void band_row_staged(const SolveBandDev& bd, const do
                 J[p] = bd.src[p] >= 0 ? st[(3 + bd.src[p]) * kSolveThreads + threadIdx.x] : 0.0;
         }
         h0 = st[2 * kSolveThreads + threadIdx.x];
-    } else if (bd.kind == KAFKA_BAND_UNIFORM) {
+    } else if (kMode == 2 || bd.kind == KAFKA_BAND_UNIFORM) {
         // one linearisation for the whole image, already laid out by state slot in shared memory
         // (uni = {J[0..P-1], h0}): warp-wide broadcast reads, no branch; unobserved pixels keep
         // an empty row (utils.py:199-215)
@@ -179,11 +183,13 @@ struct SolveBlock {
     using type = typename std::conditional<R == L, RegBlock<L>, SplitBlock<L, R, kSolveThreads>>::type;
 };
 
-// kAllIdentity: every band is a per-pixel array band whose P Jacobian planes map one-to-one onto the state
-// (the emulator-in-the-loop and supplied-Jacobian cases): no band-kind dispatch, no plane-count predicates.
-template <int P, bool kAllIdentity = false>
+// kMode 1: every band is a per-pixel array band whose P Jacobian planes map one-to-one onto the state (the
+// emulator-in-the-loop and supplied-Jacobian cases); kMode 2: every band shares one linearisation (the first
+// iteration after a prior reset); see band_row_staged.
+template <int P, int kMode = 0>
 __global__ void __launch_bounds__(kSolveThreads)
 solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
+    constexpr bool kAllIdentity = kMode == 1;
     constexpr int L = tri_count(P);
     constexpr int R = SolveBlock<P>::R;
     extern __shared__ __align__(16) double stages[];               // kAsyncStages x (3 + n_dim_max) x 128 [+ (L-R) x 128]
@@ -203,7 +209,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
             double* st = stages + (b % kAsyncStages) * stage_doubles + threadIdx.x;
             cp_async8(st, bd.w + i);
             cp_async8(st + kSolveThreads, bd.y + i);
-            if (kAllIdentity || bd.kind == KAFKA_BAND_ARRAYS) {
+            if (kMode != 2 && (kAllIdentity || bd.kind == KAFKA_BAND_ARRAYS)) {
                 cp_async8(st + 2 * kSolveThreads, bd.h0 + i);
                 // running pointers and a predicated, fully unrolled loop (a band has at most P planes): the
                 // rolled loop cost a 64-bit multiply and a branch per copy (ncu: 17 % of the stall samples)
@@ -219,8 +225,8 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
 #pragma unroll
     for (int b = 0; b < kAsyncStages - 1; ++b) issue(b);
 
-    bool any_uniform = false;
-    if (!kAllIdentity)
+    bool any_uniform = kMode == 2;
+    if (kMode == 0)
         for (int b = 0; b < prm.n_bands; ++b) any_uniform |= prm.bands[b].kind == KAFKA_BAND_UNIFORM;
     if (any_uniform) {                                              // same decision in every thread
         for (int k = threadIdx.x; k < prm.n_bands * (P + 1); k += kSolveThreads) {
@@ -265,7 +271,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
         const double w = in_ld ? st[threadIdx.x] : 0.0;
         const double y = in_ld ? st[kSolveThreads + threadIdx.x] : 0.0;
         double J[P], h0;
-        band_row_staged<P, kAllIdentity>(bd, st, n_dim_max, s_uni[b], xp, w, J, h0, round32, domain_bad);
+        band_row_staged<P, kMode>(bd, st, n_dim_max, s_uni[b], xp, w, J, h0, round32, domain_bad);
         double yp = y - h0;
 #pragma unroll
         for (int p = 0; p < P; ++p) yp = fma(J[p], xp[p], yp);
@@ -494,8 +500,10 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
     const size_t ring = (size_t)kAsyncStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
     int rc = KAFKA_E_UNSUPPORTED;
     if (n_params >= kPairFromParams || (flags & KAFKA_SOLVE_PAIR)) {
+        bool all_identity_pair = n_bands > 0;
+        for (int b = 0; b < n_bands; ++b) all_identity_pair = all_identity_pair && prm.bands[b].identity;
         KAFKA_DISPATCH_P(n_params, {
-            auto kern = solve_bands_pair_kernel<kP>;
+            auto kern = all_identity_pair ? solve_bands_pair_kernel<kP, true> : solve_bands_pair_kernel<kP, false>;
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring);
             if (e != cudaSuccess) {
                 set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
@@ -509,10 +517,13 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
         return launch_status("reduce_partials_kernel");
     }
-    bool all_identity = n_bands > 0;
-    for (int b = 0; b < n_bands; ++b) all_identity = all_identity && prm.bands[b].identity;
+    bool all_identity = n_bands > 0, all_uniform = n_bands > 0;
+    for (int b = 0; b < n_bands; ++b) {
+        all_identity = all_identity && prm.bands[b].identity;
+        all_uniform = all_uniform && prm.bands[b].kind == KAFKA_BAND_UNIFORM;
+    }
     KAFKA_DISPATCH_P(n_params, {
-        auto kern = all_identity ? solve_bands_kernel<kP, true> : solve_bands_kernel<kP, false>;
+        auto kern = all_identity ? solve_bands_kernel<kP, 1> : all_uniform ? solve_bands_kernel<kP, 2> : solve_bands_kernel<kP, 0>;
         const size_t smem = ring + (size_t)(SolveBlock<kP>::L - SolveBlock<kP>::R) * kSolveThreads * sizeof(double);
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {

@@ -40,7 +40,8 @@ __device__ __forceinline__ double at_or_zero(const double (&v)[P], int idx) {
 
 __device__ __forceinline__ double pair_bcast(double v, unsigned lane) { return __shfl_sync(0xffffffffu, v, lane); }
 
-template <int P>
+// kAllIdentity: every band is a per-pixel array band with the identity mapper (see solve_bands_kernel).
+template <int P, bool kAllIdentity = false>
 __global__ void __launch_bounds__(kPairThreads, 1)
 solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     constexpr int K = (P + 1) / 2;
@@ -69,12 +70,12 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
             const SolveBandDev& bd = prm.bands[b];
             double* st = stages + (b % kAsyncStages) * stage_doubles + slot;
             cp_async8(st + g * kPairPix, (g ? bd.y : bd.w) + i);
-            if (bd.kind == KAFKA_BAND_ARRAYS) {
+            if (kAllIdentity || bd.kind == KAFKA_BAND_ARRAYS) {
                 cp_async8(st + (2 + g) * kPairPix, (g ? bd.jac : bd.h0) + i);
                 // running pointers and a predicated, fully unrolled loop: no 64-bit multiply and no branch per copy
                 const double* src = bd.jac + (int64_t)(1 + g) * ld + i;
                 double* dst = st + (4 + g) * kPairPix;
-                const int n_mine = (bd.n_planes - g) / 2;                    // planes 1+g, 3+g, ...
+                const int n_mine = ((kAllIdentity ? P : bd.n_planes) - g) / 2;    // planes 1+g, 3+g, ...
 #pragma unroll
                 for (int t = 0; t < KAFKA_MAX_DIM / 2; ++t, src += 2 * ld, dst += 2 * kPairPix)
                     if (t < n_mine) cp_async8(dst, src);
@@ -86,7 +87,8 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
     for (int b = 0; b < kAsyncStages - 1; ++b) issue(b);
 
     bool any_uniform = false;
-    for (int b = 0; b < prm.n_bands; ++b) any_uniform |= prm.bands[b].kind == KAFKA_BAND_UNIFORM;
+    if (!kAllIdentity)
+        for (int b = 0; b < prm.n_bands; ++b) any_uniform |= prm.bands[b].kind == KAFKA_BAND_UNIFORM;
     if (any_uniform) {
         for (int k = threadIdx.x; k < prm.n_bands * (P + 1); k += kPairThreads) {
             const int b = k / (P + 1), p = k - b * (P + 1);
@@ -163,8 +165,8 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
         const double w = in_ld ? st[slot] : 0.0;
         const double y = in_ld ? st[kPairPix + slot] : 0.0;
         double J[P], h0;
-        if (bd.kind == KAFKA_BAND_ARRAYS) {
-            if (bd.identity) {
+        if (kAllIdentity || bd.kind == KAFKA_BAND_ARRAYS) {
+            if (kAllIdentity || bd.identity) {
 #pragma unroll
                 for (int p = 0; p < P; ++p) J[p] = st[(3 + p) * kPairPix + slot];
             } else {
