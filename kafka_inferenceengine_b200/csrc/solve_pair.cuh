@@ -3,8 +3,8 @@
 // parking rows in shared memory costs more than sharing the block).  Measured on B200, 4 M px,
 // supplied Jacobians, % of the HBM peak at 1 / 10 bands (bench.py --workload c5):
 //     n_params        13        14        15        16
-//     this kernel   57 / 61   59 / 62   58 / 61   61 / 64
-//     one thread    76 / 79   63 / 55   49 / 44   33 / 29 (spills)
+//     this kernel   57 / 61   60 / 67   60 / 67   61 / 68
+//     one thread    75 / 81   63 / 55   49 / 44   33 / 29 (spills)
 // so the pair kernel is the default from 14 and selectable at any size (KAFKA_SOLVE_PAIR, used by
 // the tests).  ncu: 254 registers, 8 warps per SM, stalls on dependent-instruction latency (wait,
 // scoreboards) -- two warps per scheduler cannot hide the factorisation's chain.
