@@ -38,6 +38,7 @@ TILE = 10980
 SHARD_ROWS = 1373                     # ceil(10980 / 8)
 BYTES_PER_PIXEL_DATE = 16 * P + 8 * P * (P + 1) + 17 * B          # 1210
 FLOPS_PER_PIXEL_ITER = B * T * (5 * P + 28) + B * (P * P + 3 * P) + P ** 3 / 3 + 2 * P * P
+REF_CHUNK_SIDE = 64          # reference chunks: REF_CHUNK_SIDE^2 px, one LinearKalman each (drivers use <= 256^2)
 
 
 def parse():
@@ -48,9 +49,13 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=SHARD_ROWS, help="raster rows per GPU (x 10980 columns)")
     ap.add_argument("--cols", type=int, default=TILE)
-    ap.add_argument("--cpu-sample", type=int, default=131072, help="pixels of the workload timed on the host")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-chunk", type=int, default=REF_CHUNK_SIDE,
+                    help="side of the square chunks the CPU legs hand to the reference (<= 256, its drivers' practice)")
+    ap.add_argument("--port-sample", type=int, default=65536, help="pixels the numpy port is timed on (cpu_baseline.port)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--host-sources", default="pinned", choices=["pinned", "pageable"],
+                    help="memory the e2e legs' host rasters live in (see e2e.api)")
     ap.add_argument("--workload", default="c4shard", choices=["c4shard", "c2", "c3", "c5"],
                     help="c4shard (default, the bench line): 1/8 of the full S2 tile per GPU; the others are the "
                          "remaining BASELINE.json configs, run on request for the record (single GPU)")
@@ -108,30 +113,44 @@ class HostObservations(object):
     """Same data as host numpy rasters (the reference's data contract:
     observations (ny,nx) float64, inverse-variance raster, boolean mask)."""
 
-    def __init__(self, dates, gps, rho, inv, mask, shape):
+    def __init__(self, dates, gps, rho, inv, mask, shape, pinned=True):
         from kafka_inferenceengine_b200 import synthetic as syn
         self.dates = list(dates)
         self.bands_per_observation = {d: B for d in self.dates}
-        self._bands = [syn.BandData(rho[b].cpu().numpy().reshape(shape), inv[b].cpu().numpy().reshape(shape),
-                                    mask[b].cpu().numpy().reshape(shape).astype(bool), {"band": b}, gps[b])
+        self._bands = [syn.BandData(_host_raster(rho[b], shape, np.float64, pinned),
+                                    _host_raster(inv[b], shape, np.float64, pinned),
+                                    _host_raster(mask[b] != 0, shape, np.bool_, pinned), {"band": b}, gps[b])
                        for b in range(B)]
 
     def get_band_data(self, date, band):
         return self._bands[band]
 
 
+def _host_raster(t, shape, dtype, pinned):
+    """Host copy of a device row as a (ny, nx) numpy raster: in page-locked memory obtained from
+    the package (kb.pinned_raster -- what a reader fills when it wants the DMA engine to fetch its
+    rasters in place) or in ordinary pageable memory."""
+    if not pinned:
+        return t.cpu().numpy().reshape(shape).astype(dtype, copy=False)
+    import torch
+    from kafka_inferenceengine_b200 import pinned_raster
+    a = pinned_raster(shape, dtype)
+    torch.from_numpy(a.reshape(-1)).copy_(t.reshape(-1))
+    return a
+
+
 class RawObservations(object):
     """Raw scaled-integer reflectance as the S2 granule holds it (int16 = rho * 10000, <= 0 where
     there is no data): the ingest arithmetic of Sentinel2Observations.get_band_data runs on the device."""
 
-    def __init__(self, dates, gps, rho, mask, shape):
+    def __init__(self, dates, gps, rho, mask, shape, pinned=True):
         from kafka_inferenceengine_b200 import synthetic as syn
         from kafka_inferenceengine_b200 import ScaledReflectance
         self.dates = list(dates)
         self.bands_per_observation = {d: B for d in self.dates}
         raw = torch_round_i16(rho, mask)
-        self._bands = [syn.BandData(raw[b].cpu().numpy().reshape(shape), ScaledReflectance(10000.0, 0.05), None,
-                                    {"band": b}, gps[b]) for b in range(B)]
+        self._bands = [syn.BandData(_host_raster(raw[b], shape, np.int16, pinned), ScaledReflectance(10000.0, 0.05),
+                                    None, {"band": b}, gps[b]) for b in range(B)]
 
     def get_band_data(self, date, band):
         return self._bands[band]
@@ -213,93 +232,157 @@ class ClockSampler(object):
 
 
 # --------------------------------------------------------------------------
-# CPU baseline: the reference's algorithm restated (oracle A', scipy sparse +
-# float32 SuperLU; GP by numpy) on a bounded sample of the same workload
+# CPU legs.  Nothing below imports kafka_inferenceengine_b200 (no CUDA library is mapped by
+# the processes that time the CPU code): the workload comes from oracle/synthetic.py, the
+# timed code is the UNMODIFIED reference (oracle/ref_runner.py -> baseline/_ref or
+# /root/reference) and, beside it, the numpy port (oracle A': scipy sparse + float32 SuperLU).
 # --------------------------------------------------------------------------
-def _cpu_chunk(args):
-    gp_arrays, y, w, m, chunk = args
+def _port_chunk(args):
+    gp_arrays, y, w, m = args
     from oracle import kafka_cpu as kc
+    from oracle import synthetic as osyn
     from oracle.gp import GaussianProcess
-    from kafka_inferenceengine_b200 import synthetic as syn
     gps = [GaussianProcess(a[0], a[1], a[2]) for a in gp_arrays]
     n = y.shape[1]
-    inv = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
+    inv = osyn.sail_prior_block().astype(np.float64)
     blocks = np.repeat(inv[None], n, axis=0)
-    x0 = np.tile(syn.SAIL_MEAN, n)
+    x0 = np.tile(osyn.SAIL_MEAN, n)
     ops = [(lambda xp, gp=gps[b], mm=m[b]: kc.emulator_operator(gp, xp, P, mm)) for b in range(B)]
     t0 = time.perf_counter()
     x, A, _, iters, _ = kc.do_all_bands(ops, [y[b] for b in range(B)], [w[b] for b in range(B)],
                                         [m[b] for b in range(B)], x0, blocks, P, mode="sparse32")
-    return time.perf_counter() - t0, iters, n
+    return time.perf_counter() - t0, n, iters
 
 
-def cpu_baseline(gps, rho, inv, mask, n_sample, procs=1, chunk=16384):
-    """Time the CPU port on `n_sample` pixels of the workload, chunked like the
-    reference's drivers (<= 256 x 256 px per LinearKalman, kafka_test_Py36.py:241)."""
-    n_sample = int(min(n_sample, rho.shape[1]))
-    y = rho[:, :n_sample].cpu().numpy()
-    m = mask[:, :n_sample].cpu().numpy().astype(bool)
-    w = np.where(m, inv[:, :n_sample].cpu().numpy(), 0.0)
+def _ref_chunk(args):
+    from oracle import ref_runner
+    return ref_runner.time_do_all_bands(args)
+
+
+def _port_job(args):
+    """A reference-style job tuple through the numpy port (stand-in where the reference package
+    is not installed: kind "port")."""
+    gp_arrays, y, inv, m, side = args
+    return _port_chunk((gp_arrays, y, np.where(m, inv, 0.0), m))
+
+
+def _reference_installed():
+    from oracle import ref_shim
+    return ref_shim.available()
+
+
+def _ref_solve_chunk(args):
+    from oracle import ref_runner
+    return ref_runner.time_multiband_solve(args)
+
+
+def _cpu_workload(n_chunks, side, seed=99):
+    """Chunks of the benchmark workload for the CPU legs, from the numpy generator."""
+    from oracle import synthetic as osyn
+    gps = osyn.make_emulators(B, T)
     gp_arrays = [(g.inputs, g.targets, g.theta) for g in gps]
-    jobs = [(gp_arrays, y[:, s:s + chunk], w[:, s:s + chunk], m[:, s:s + chunk], chunk)
-            for s in range(0, n_sample, chunk)]
-    t0 = time.perf_counter()
-    if procs > 1:
-        import multiprocessing as mp
-        for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
-            os.environ[var] = "1"          # one BLAS thread per worker process (spawned children inherit)
-        with mp.get_context("spawn").Pool(procs) as pool:
-            res = pool.map(_cpu_chunk, jobs)
-    else:
-        res = [_cpu_chunk(j) for j in jobs]
-    wall = time.perf_counter() - t0
-    return n_sample / wall, wall, [r[1] for r in res]
+    n = side * side
+    y, inv, m = osyn.synth_observations(gps, n_chunks * n, seed)
+    return [(gp_arrays, y[:, k * n:(k + 1) * n], inv[:, k * n:(k + 1) * n], m[:, k * n:(k + 1) * n], side)
+            for k in range(n_chunks)]
+
+
+def _single_thread_env():
+    for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[var] = "1"              # one BLAS thread per worker process (spawned children inherit)
+
+
+def cpu_baseline_leg(side=REF_CHUNK_SIDE, port_sample=65536):
+    """cpu_baseline of the N=1 line: a bounded sample on ONE host core, run in a freshly spawned
+    interpreter (no CUDA library in that process): (A) the unmodified reference's
+    LinearKalman.do_all_bands on one chunk, (B) its variational_kalman_multiband alone on the same
+    chunk, and the numpy port on a larger sample."""
+    import multiprocessing as mp
+    _single_thread_env()
+    jobs = _cpu_workload(1, side)
+    have_ref = _reference_installed()
+    with mp.get_context("spawn").Pool(1) as pool:
+        if have_ref:
+            t_a, n_a, it_a = pool.apply(_ref_chunk, (jobs[0],))
+            t_b, n_b = pool.apply(_ref_solve_chunk, (jobs[0],))
+        gp_arrays = jobs[0][0]
+        from oracle import synthetic as osyn
+        gps = osyn.make_emulators(B, T)
+        y, inv, m = osyn.synth_observations(gps, port_sample, 98)
+        w = np.where(m, inv, 0.0)
+        res = [pool.apply(_port_chunk, ((gp_arrays, y[:, k:k + 16384], w[:, k:k + 16384], m[:, k:k + 16384]),))
+               for k in range(0, port_sample, 16384)]
+    t_p = sum(r[0] for r in res)
+    port = {"value": port_sample / t_p, "unit": "pixel-dates/s", "cores": 1, "kind": "port",
+            "sample": "%d px in chunks of 16384 px, %.1f s; oracle A' = numpy GP + scipy.sparse build + "
+                      "float32 SuperLU as solvers.py:100-145 (%s solves)"
+                      % (port_sample, t_p, sorted(set(r[2] for r in res)))}
+    if not have_ref:
+        return port                                  # no reference package on this machine (baseline/_ref absent)
+    return {"value": n_a / t_a, "unit": "pixel-dates/s", "cores": 1, "kind": "reference",
+            "sample": "one %dx%d px chunk of the same workload (all bands, iterated to convergence: %d solves) "
+                      "through the UNMODIFIED reference's LinearKalman.do_all_bands (kafka/linear_kf.py:245-323, "
+                      "operators by create_prosail_observation_operator, emulator class = oracle.gp), %.1f s on one "
+                      "core" % (side, side, it_a, t_a),
+            "solve_only": {"value": n_b / t_b, "unit": "pixels/s", "seconds": t_b,
+                           "what": "the unmodified variational_kalman_multiband (kafka/inference/solvers.py:100-145) "
+                                   "alone on the same chunk, operators pre-built: the 'scipy spsolve path'"},
+            "port": port}
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU algorithm (oracle port; the reference is
-    pure Python and cannot travel to the GPU box) on all host cores, each step a
-    bounded sample of the same workload."""
+    """--impl reference: the UNMODIFIED reference (LinearKalman.do_all_bands from baseline/_ref) on all
+    host cores, one chunk per core per step, one LinearKalman per chunk like the reference's dask fan-out
+    (kafka_test_Py36.py:241-255).  Runs on rank 0 only; no GPU, no CUDA library, none of the product code."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
+    import multiprocessing as mp
+    _single_thread_env()
     cores = os.cpu_count() or 1
-    procs = max(1, min(cores, 32))
-    gps = make_emulators()
-    dev = torch.device("cuda", 0) if torch.cuda.is_available() else None
-    n_sample = procs * 4 * 8192 if args.cpu_sample == 131072 else max(8192, args.cpu_sample // 8192 * 8192)
-    procs = min(procs, n_sample // 8192)
-    if dev is not None:
-        rho, inv, mask = synth_on_device(gps, n_sample, 99, dev)
-    else:                                   # no GPU: numpy forward model from the oracle
-        from oracle.gp import GaussianProcess
-        from kafka_inferenceengine_b200 import synthetic as syn
-        rng = np.random.default_rng(99)
-        xt = syn.SAIL_MEAN + syn.SAIL_SIGMA * rng.standard_normal((n_sample, P))
-        r = np.array([GaussianProcess(g.inputs, g.targets, g.theta).predict(xt, do_unc=False)[0] for g in gps])
-        r = r * (1 + 0.05 * rng.standard_normal(r.shape))
-        mk = (r > 0) & (rng.random(r.shape) < 0.9)
-        r = np.where(mk, r, 0.0)
-        with np.errstate(divide="ignore"):
-            iv = np.where(mk, 1.0 / (0.05 * r) ** 2, np.inf)
-        rho, inv, mask = torch.from_numpy(r), torch.from_numpy(iv), torch.from_numpy(mk.astype(np.uint8))
-    times = []
-    for s in range(args.warmup + args.steps):
-        rate, wall, iters = cpu_baseline(gps, rho, inv, mask, n_sample, procs=procs, chunk=8192)
-        if s >= args.warmup:
-            times.append(wall)
+    procs = max(1, min(cores, 64))
+    side = args.ref_chunk
+    jobs = _cpu_workload(procs, side)
+    n_sample = procs * side * side
+    times, iters = [], []
+    have_ref = _reference_installed()
+    step_fn = _ref_chunk if have_ref else _port_job
+    with mp.get_context("spawn").Pool(procs) as pool:
+        if have_ref:
+            pool.map(_ref_solve_chunk, jobs)              # imports + first-call costs, outside every step
+        for s in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            res = pool.map(step_fn, jobs, chunksize=1)
+            wall = time.perf_counter() - t0
+            if s >= args.warmup:
+                times.append(wall)
+                iters += [r[2] for r in res]
+        # side figures: the slowest process's own timer (inputs and operators are built outside it)
+        wall_b = max(r[0] for r in pool.map(_ref_solve_chunk, jobs, chunksize=1)) if have_ref else float("nan")
+        w_jobs = [(j[0], j[1], np.where(j[3], j[2], 0.0), j[3]) for j in jobs]
+        wall_p = max(r[0] for r in pool.map(_port_chunk, w_jobs, chunksize=1))
     ms = 1e3 * float(np.mean(times))
     value = n_sample / (ms * 1e-3)
+    sample = ("per step %d chunks of %dx%d px of the same workload (one per process, %d processes = all host "
+              "cores, BLAS pinned to one thread each), every chunk through the UNMODIFIED reference's "
+              "LinearKalman.do_all_bands (kafka/linear_kf.py:245-323; %s solves per chunk); rate per pixel, "
+              "the workload itself is %d px per GPU" % (procs, side, side, procs, sorted(set(iters)),
+                                                         args.rows * args.cols))
     line = {"impl": "reference", "metric": "pixel-dates/sec", "value": value, "unit": "pixel-dates/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 build, f32 sparse LU",
-            "data": "synthetic",
-            "config": workload_config(args, note="bounded sample per step: %d px in %d chunks of 8192 px on %d "
-                                      "processes" % (n_sample, n_sample // 8192, procs)),
-            "cpu_baseline": {"value": value, "unit": "pixel-dates/s", "cores": procs, "kind": "port",
-                             "sample": "%d px per step, all bands, iterated to convergence (%s solves)"
-                                       % (n_sample, sorted(set(iters)))},
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args),
+            "cpu_baseline": {"value": value, "unit": "pixel-dates/s", "cores": procs,
+                             "kind": "reference" if have_ref else "port",
+                             "sample": sample if have_ref else sample.replace(
+                                 "UNMODIFIED reference's LinearKalman.do_all_bands",
+                                 "numpy port (oracle A'; the reference package is not installed here) of do_all_bands"),
+                             "arithmetic": "the reference builds in float64 and solves in float32 (solvers.py:127-134)",
+                             "solve_only": {"value": n_sample / wall_b, "unit": "pixels/s",
+                                            "what": "unmodified variational_kalman_multiband alone, same chunks, "
+                                                    "operators pre-built, all cores"},
+                             "port": {"value": n_sample / wall_p, "unit": "pixel-dates/s", "kind": "port",
+                                      "what": "numpy port (oracle A') on the same chunks, all cores"}},
             "e2e": {"value": value, "unit": "pixel-dates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(json.dumps(line))
 
@@ -616,12 +699,14 @@ def main():
     # processes a time series: per date the host rasters go host->device (pageable numpy,
     # staged through pinned memory), the state is reset to the prior (kafka_test_S2.py:177-178),
     # the date is assimilated and the float32 mean / uncertainty rasters are read back.
-    e2e = None
+    e2e = e2e_raw = None
     if not args.no_e2e:
         from kafka_inferenceengine_b200.output import RasterOutput
         n_warm = max(2, args.warmup)
         all_dates = [base + dt.timedelta(days=d, hours=12) for d in range(n_warm + args.steps)]
-        obs_host = HostObservations(all_dates, gps, rho, inv, mask, shape)
+        grid_warm = [base + dt.timedelta(days=d) for d in range(n_warm + 1)]
+        grid_timed = [base + dt.timedelta(days=n_warm + d) for d in range(args.steps + 1)]
+
         class TimedRasterOutput(RasterOutput):
             """RasterOutput that notes when each date is handed over (host clock)."""
             stamps = None
@@ -631,60 +716,61 @@ def main():
                     self.stamps.append(time.perf_counter())
                 return RasterOutput.dump_data(self, *a, **k)
 
-        out = TimedRasterOutput(syn.S2_PARAMETERS)     # float32 mean + 1/sqrt(diag) rasters, read back to the host
-        kf2, prior2 = make_filter(obs_host, out)
-        out.pixels = kf2.pixels
-        kf2.set_trajectory_uncertainty(0.0)
-        # the prior (one mean vector, one block for all pixels) is a constant of the run and
-        # stays on the device; the per-step inputs -- the date's rasters -- come from the host
-        x0h, Pinv0h = prior2.process_prior(None)
-        grid_warm = [base + dt.timedelta(days=d) for d in range(n_warm + 1)]
-        grid_timed = [base + dt.timedelta(days=n_warm + d) for d in range(args.steps + 1)]
-        kf2.run(grid_warm, x0h, None, Pinv0h, iter_obs_op=True)
-        barrier()
-        h2d0, d2h0 = kf2._stager.h2d_bytes, out.d2h_bytes
-        out.stamps = []
-        t0 = time.perf_counter()
-        kf2.run(grid_timed, x0h, None, Pinv0h, iter_obs_op=True)
-        torch.cuda.synchronize()
-        ms_e2e = max_over_ranks(1e3 * (time.perf_counter() - t0)) / args.steps
-        gaps = np.diff(out.stamps)
-        ms_steady = max_over_ranks(1e3 * float(np.median(gaps))) if len(gaps) else None
-        out.stamps = None
-        barrier()
-        e2e = {"value": world * n_pix / (ms_e2e * 1e-3), "unit": "pixel-dates/s", "ms_per_step": ms_e2e,
-               "h2d_bytes_per_step": (kf2._stager.h2d_bytes - h2d0) // args.steps,
-               "d2h_bytes_per_step": (out.d2h_bytes - d2h0) // args.steps,
-               "steady_state_ms_per_step": ms_steady,
-               "steady_state_note": "median interval between successive dates inside the same run(); value/ms_per_step "
+        def run_e2e(obs):
+            out = TimedRasterOutput(syn.S2_PARAMETERS)     # float32 mean + 1/sqrt(diag) rasters, read back to the host
+            kf2, prior2 = make_filter(obs, out)
+            out.pixels = kf2.pixels
+            kf2.set_trajectory_uncertainty(0.0)
+            # the prior (one mean vector, one block for all pixels) is a constant of the run and
+            # stays on the device; the per-step inputs -- the date's rasters -- come from the host
+            x0h, Pinv0h = prior2.process_prior(None)
+            kf2.run(grid_warm, x0h, None, Pinv0h, iter_obs_op=True)
+            barrier()
+            h2d0, d2h0 = kf2._stager.h2d_bytes, out.d2h_bytes
+            out.stamps = []
+            t0 = time.perf_counter()
+            kf2.run(grid_timed, x0h, None, Pinv0h, iter_obs_op=True)
+            torch.cuda.synchronize()
+            ms = max_over_ranks(1e3 * (time.perf_counter() - t0)) / args.steps
+            gaps = np.diff(out.stamps)
+            ms_steady = max_over_ranks(1e3 * float(np.median(gaps))) if len(gaps) else None
+            out.stamps = None
+            barrier()
+            return {"value": world * n_pix / (ms * 1e-3), "unit": "pixel-dates/s", "ms_per_step": ms,
+                    "h2d_bytes_per_step": (kf2._stager.h2d_bytes - h2d0) // args.steps,
+                    "d2h_bytes_per_step": (out.d2h_bytes - d2h0) // args.steps,
+                    "steady_state_ms_per_step": ms_steady,
+                    "host_sources": args.host_sources}
+
+        pinned = args.host_sources == "pinned"
+        src_note = ("page-locked numpy rasters from kb.pinned_raster (what a reader fills when the DMA engine "
+                    "is to fetch its rasters in place)" if pinned else
+                    "ordinary pageable numpy rasters, staged through the package's pinned buffers by a thread pool")
+        # ONE run() call over a time grid with one observation date per interval, as a user
+        # processes a time series: per date the host rasters go host->device, the state is reset
+        # to the prior (kafka_test_S2.py:177-178), the date is assimilated and the float32 mean /
+        # uncertainty rasters are read back.
+        obs_host = HostObservations(all_dates, gps, rho, inv, mask, shape, pinned=pinned)
+        e2e = run_e2e(obs_host)
+        del obs_host
+        e2e["steady_state_note"] = ("median interval between successive dates inside the same run(); value/ms_per_step "
                                     "are the WHOLE call / K and also carry the first date's staging, which nothing can "
-                                    "hide behind, and the last date's read-back",
-               "api": "one LinearKalman.run(time_grid, x_forecast, None, P_forecast_inverse) over %d dates: host numpy "
-                      "rasters from observations.get_band_data (pageable, float64 obs + inverse variance + bool mask) "
-                      "copied host->device every date, prior-only advance, output.dump_data = RasterOutput "
-                      "(float32 mean and 1/sqrt(diag P^-1) rasters read back to the host every date, as "
-                      "KafkaOutput.dump_data writes them)" % args.steps}
+                                    "hide behind, and the last date's read-back")
+        e2e["api"] = ("one LinearKalman.run(time_grid, x_forecast, None, P_forecast_inverse) over %d dates: host numpy "
+                      "rasters from observations.get_band_data (float64 obs + float64 inverse variance + bool mask = "
+                      "17 B per pixel and band; %s) copied host->device every date, prior-only advance, "
+                      "output.dump_data = RasterOutput (float32 mean and 1/sqrt(diag P^-1) rasters read back to the "
+                      "host every date, as KafkaOutput.dump_data writes them)" % (args.steps, src_note))
         # same run fed with the RAW int16 reflectance rasters (what the granule holds): the reader's
         # arithmetic (mask = raw > 0, /10000, sigma = 5 %, 1/sigma^2; Sentinel2_Observations.py:166-179)
         # runs on the device fused with the gather, 2 B/px/band cross PCIe instead of 17
-        obs_raw = RawObservations(all_dates, gps, rho, mask, shape)
-        out3 = RasterOutput(syn.S2_PARAMETERS)
-        kf3, prior3 = make_filter(obs_raw, out3)
-        out3.pixels = kf3.pixels
-        kf3.set_trajectory_uncertainty(0.0)
-        kf3.run(grid_warm, x0h, None, Pinv0h, iter_obs_op=True)
-        barrier()
-        h2d0 = kf3._stager.h2d_bytes
-        t0 = time.perf_counter()
-        kf3.run(grid_timed, x0h, None, Pinv0h, iter_obs_op=True)
-        torch.cuda.synchronize()
-        ms_raw = max_over_ranks(1e3 * (time.perf_counter() - t0)) / args.steps
-        barrier()
-        e2e["raw_ingest"] = {"value": world * n_pix / (ms_raw * 1e-3), "unit": "pixel-dates/s", "ms_per_step": ms_raw,
-                             "h2d_bytes_per_step": (kf3._stager.h2d_bytes - h2d0) // args.steps,
-                             "note": "same run() with raw int16 reflectance rasters + ScaledReflectance marker "
-                                     "(observation ingest on the device)"}
-        del kf2, obs_host, kf3, obs_raw
+        obs_raw = RawObservations(all_dates, gps, rho, mask, shape, pinned=pinned)
+        e2e_raw = run_e2e(obs_raw)
+        del obs_raw
+        e2e_raw["api"] = ("same LinearKalman.run() fed with the raw int16 reflectance rasters the Sentinel-2 granule "
+                          "holds + a ScaledReflectance marker: the reader's arithmetic "
+                          "(Sentinel2_Observations.py:166-179) runs on the device fused with the compaction gather; "
+                          "%s; same float32 output rasters read back every date" % src_note)
 
     if rank != 0:
         if world > 1:
@@ -707,10 +793,12 @@ def main():
     except OSError:
         pass
     # DRAM traffic per pixel of each kernel from the committed ncu --set full capture
-    # (profiles/r01_ncu_kernels.json, written by profiles/summarize_ncu.py)
+    # (profiles/r0N_ncu_kernels.json, written by profiles/summarize_ncu.py)
     ncu_bpp = {}
+    ncu_file = next((f for f in ("r02_ncu_kernels.json", "r01_ncu_kernels.json")
+                     if os.path.exists(os.path.join(ROOT, "profiles", f))), "r01_ncu_kernels.json")
     try:
-        for k in json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_kernels.json")))["kernels"]:
+        for k in json.load(open(os.path.join(ROOT, "profiles", ncu_file)))["kernels"]:
             if "dram_bytes_per_pixel" in k:
                 ncu_bpp[k["kernel"].split("<")[0].replace("void ", "")] = k["dram_bytes_per_pixel"]
     except Exception:
@@ -725,27 +813,29 @@ def main():
     # ONE block shared by all pixels in this workload (KAFKA_PRIOR_BROADCAST), so it is not counted.
     sv_bytes = n_pix * (3 * 8 * P + B * 8 * (3 + P) + 4 * P * (P + 1) + 8 * B)
     gp_tf = gp_flops / (gp_ms * 1e-3) / 1e12
+    # the kernel EXECUTES 2D+8 fp64 instructions (2 flops each) per training point where the textbook
+    # form counts 5D+28; "achieved" is in executed flops so that frac stays a fraction of the pipe
+    gp_exec_tf = gp_tf * (2.0 * (2 * P + 8)) / (5 * P + 28)
     roofline = {
         "kernel": "gp_linearize_kernel<10,2> (GP emulator mean+Jacobian, all bands, one launch per iteration)",
-        "bound": "hbm",
-        "achieved": gp_bytes / (gp_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-        "frac": gp_bytes / (gp_ms * 1e-3) / 1e9 / hbm_peak,
-        "traffic": (ncu_bpp["gp_linearize_kernel"] * n_pix) if "gp_linearize_kernel" in ncu_bpp else None,
-        "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per pixel from profiles/r01_ncu_kernels.json "
-                          "(ncu --set full, 2.196 M px launch) x pixels of this launch",
-        "peak_source": peak_src,
-        "algorithmic_bytes_per_launch": gp_bytes, "ms_per_launch": gp_ms,
+        "bound": "fp64",
+        "achieved": gp_exec_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+        "frac": (gp_exec_tf / fp64_peak) if fp64_peak else None,
+        "peak_source": "fp64 DFMA probe measured in this run (benchmarks/probe.cu); MEASURED_PEAKS.json has no fp64 figure",
+        "flops_counted": "executed: 2 x (2D+8) fp64 instructions per (pixel, band, training point)",
+        "ms_per_launch": gp_ms,
         "share_of_step": float(np.sum(prof.get("gp_linearize", [0.0]))) / args.steps / ms_step,
-        "note": "this kernel is fp64-pipe bound, not HBM bound (SURVEY 8d: ~195 kflop vs ~1 kB per pixel-iteration); "
-                "the binding roofline is 'fp64' below",
-        "fp64": {"achieved": gp_tf, "peak": fp64_peak, "unit": "TFLOP/s (algorithmic: B*T*(5D+28) per pixel)",
-                 "frac": (gp_tf / fp64_peak) if fp64_peak else None,
-                 "peak_source": "DFMA probe measured in this run (benchmarks/probe.cu)",
-                 # the kernel EXECUTES 2D+8 fp64 instructions (2 flops each) per training point where the
-                 # textbook count is 5D+28, which is how the algorithmic fraction can pass 1.0
-                 "executed": {"achieved": gp_tf * (2.0 * (2 * P + 8)) / (5 * P + 28),
-                              "frac": (gp_tf * (2.0 * (2 * P + 8)) / (5 * P + 28) / fp64_peak) if fp64_peak else None,
-                              "unit": "TFLOP/s (2 x fp64 instructions issued: 2D+8 per training point)"}},
+        "algorithmic": {"achieved": gp_tf, "frac": (gp_tf / fp64_peak) if fp64_peak else None,
+                        "unit": "TFLOP/s by SURVEY 8d's count B*T*(5D+28) per pixel-iteration",
+                        "flops_per_launch": gp_flops},
+        "traffic": (ncu_bpp["gp_linearize_kernel"] * n_pix) if "gp_linearize_kernel" in ncu_bpp else None,
+        "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per pixel from profiles/%s "
+                          "(ncu --set full) x pixels of this launch" % ncu_file,
+        "hbm": {"achieved": gp_bytes / (gp_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                "frac": gp_bytes / (gp_ms * 1e-3) / 1e9 / hbm_peak, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": gp_bytes,
+                "note": "for the record: this kernel is bound by the fp64 pipe, not by HBM "
+                        "(SURVEY 8d: ~195 kflop vs ~1 kB per pixel-iteration)"},
         "solve_kernel": {"kernel": "solve_bands_kernel<10> (normal equations + Cholesky + partial norm; per-pixel "
                                    "operators, i.e. the launches of iteration >= 2) + reduce_partials_kernel",
                          "bound": "hbm", "achieved": sv_bytes / (sv_ms * 1e-3) / 1e9, "peak": hbm_peak,
@@ -761,11 +851,7 @@ def main():
 
     cpu = None
     if not args.no_cpu_baseline:
-        rate, wall, its = cpu_baseline(gps, rho, inv, mask, args.cpu_sample, procs=1)
-        cpu = {"value": rate, "unit": "pixel-dates/s", "cores": 1, "kind": "port",
-               "sample": "%d px of the same workload in chunks of 16384 px, all bands, iterated to convergence "
-                         "(%s solves), %.1f s; oracle A' = numpy GP + scipy.sparse build + float32 SuperLU as "
-                         "solvers.py:100-145" % (min(args.cpu_sample, n_pix), sorted(set(its)), wall)}
+        cpu = cpu_baseline_leg(args.ref_chunk, args.port_sample)
 
     line = {"metric": "pixel-dates/sec", "value": value, "unit": "pixel-dates/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
@@ -775,7 +861,8 @@ def main():
                                "and shared (reference: run_emulator single-unique-vector branch, utils.py:72-74); "
                                "later iterations evaluate every pixel",
             "value_without_shared_first_linearisation": world * n_pix / (ms_nodedup * 1e-3),
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+            "clocks": clocks, "e2e": e2e, "e2e_raw_ingest": e2e_raw, "gpu_launches": launches, "roofline": roofline,
+            "cpu_baseline": cpu}
     if world == 1 and not args.no_e2e and args.rows == SHARD_ROWS:
         # BASELINE configs[1] (the Barrax mask on one GPU) beside the headline workload: a parity-test size
         # at which a B200 is launch-bound, reported for completeness, measured after the timed region

@@ -1,13 +1,17 @@
 """Where does the host thread of the end-to-end run spend its time?
 
-    python benchmarks/e2e_timeline.py [raw|host] [rows]
+    python benchmarks/e2e_timeline.py [raw|host] [pinned|pageable] [rows]
+    python -m torch.distributed.run --nproc-per-node N ... benchmarks/e2e_timeline.py raw pinned
 
 Wraps the phases of LinearKalman.run (read bands, stage, finish, norm wait, output, advance)
 with wall-clock timers -- no extra synchronisation, so the overlap is the one bench.py sees --
 and prints milliseconds per date.  A phase that waits for the GPU (norm) shows the GPU time
-the host could not hide behind."""
+the host could not hide behind.  Under torchrun every rank runs its own shard with the global
+convergence norm (as bench.py does); rank 0 prints the per-phase mean and maximum over ranks
+and, with KAFKA_TIMELINE_OUT=<file>, writes the table as JSON."""
 import collections
 import datetime as dt
+import json
 import os
 import sys
 import time
@@ -44,24 +48,35 @@ def timed(cls, name, tag):
 
 
 def main():
+    import torch.distributed as dist
     mode = sys.argv[1] if len(sys.argv) > 1 else "raw"
-    rows = int(sys.argv[2]) if len(sys.argv) > 2 else bench.SHARD_ROWS
-    device = torch.device("cuda", 0)
+    pinned = (sys.argv[2] if len(sys.argv) > 2 else "pinned") == "pinned"
+    rows = int(sys.argv[3]) if len(sys.argv) > 3 else bench.SHARD_ROWS
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    comm = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+        comm = dist.group.WORLD
     shape = (rows, bench.TILE)
     n_pix = rows * bench.TILE
     gps = bench.make_emulators()
-    rho, inv, mask = bench.synth_on_device(gps, n_pix, 1234, device)
+    rho, inv, mask = bench.synth_on_device(gps, n_pix, 1234 + rank, device)
     base = dt.datetime(2017, 7, 3)
-    n_warm, steps = 2, 5
+    n_warm, steps = 2, int(os.environ.get("KAFKA_TIMELINE_STEPS", "6"))
     dates = [base + dt.timedelta(days=d, hours=12) for d in range(n_warm + steps)]
-    obs = (bench.RawObservations(dates, gps, rho, mask, shape) if mode == "raw"
-           else bench.HostObservations(dates, gps, rho, inv, mask, shape))
+    obs = (bench.RawObservations(dates, gps, rho, mask, shape, pinned=pinned) if mode == "raw"
+           else bench.HostObservations(dates, gps, rho, inv, mask, shape, pinned=pinned))
+    del rho, inv, mask
     out = RasterOutput(syn.S2_PARAMETERS)
     inv_block = np.diag(1.0 / syn.SAIL_SIGMA ** 2).astype(np.float32).astype(np.float64)
     prior = syn.BroadcastPrior(syn.SAIL_MEAN, inv_block, n_pix, lambda blk, n: BlockDiag.from_block(blk, n, device),
                                lambda m, n: DeviceVector.broadcast(m, n, device))
     kf = kb.LinearKalman(obs, out, np.ones(shape, dtype=bool), kb.create_prosail_observation_operator,
-                         syn.S2_PARAMETERS, state_propagation=None, prior=prior, linear=False, device=device)
+                         syn.S2_PARAMETERS, state_propagation=None, prior=prior, linear=False, device=device, comm=comm)
     kf.set_trajectory_model()
     kf.set_trajectory_uncertainty(0.0)
     out.pixels = kf.pixels
@@ -87,7 +102,7 @@ def main():
     timed(kb.LinearKalman, "_read_bands", "read_bands")
     timed(engine.ObservationStager, "stage", "stage (host copies + queue H2D)")
     timed(engine.ObservationStager, "finish", "finish (queue gathers)")
-    timed(kb.LinearKalman, "_global_norm", "norm (.item(): waits for the GPU)")
+    timed(kb.LinearKalman, "_global_norm", "norm (waits for the GPU / all ranks)")
     timed(kb.LinearKalman, "advance", "advance")
     timed(RasterOutput, "dump_data", "dump_data (incl. wait for previous D2H)")
     timed(RasterOutput, "_deliver", "  of which _deliver")
@@ -98,6 +113,9 @@ def main():
         import cProfile
         prof = cProfile.Profile()
         prof.enable()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
     t0 = time.perf_counter()
     kf.run([base + dt.timedelta(days=n_warm + d) for d in range(steps + 1)], x0, None, Pinv0, iter_obs_op=True)
     torch.cuda.synchronize()
@@ -106,22 +124,48 @@ def main():
         import pstats
         prof.disable()
         pstats.Stats(prof).sort_stats("tottime").print_stats(18)
-    print("mode %s, %d px: %.1f ms per date" % (mode, n_pix, 1e3 * total / steps))
+    table = {"total ms per date": 1e3 * total / steps}
     for k, v in ACC.items():
-        print("  %-44s %8.2f ms/date" % (k, 1e3 * v / steps))
-    print("  iterations", kf.last_iterations[-steps:])
-    if os.environ.get("KAFKA_TIMELINE_LOG"):
+        table[k] = 1e3 * v / steps
+    h2d = []
+    for e_gp, e_end in marks:
+        try:
+            h2d.append(e_gp.elapsed_time(e_end))
+        except Exception:
+            pass
+    if h2d:
+        table["H2D of the next date done .. ms after the current date's kernels (negative: before)"] = float(np.mean(h2d))
+    for k, v in kf.profile.items():
+        table["GPU " + k + " (CUDA events)"] = sum(a.elapsed_time(b) for a, b in v) / steps
+    tables = [table]
+    if world > 1:
+        tables = [None] * world
+        dist.all_gather_object(tables, table)
+    if rank == 0:
+        head = "mode %s, %s sources, %d ranks x %d px, %d staging threads per rank, %d dates" % (
+            mode, "pinned" if pinned else "pageable", world, n_pix, engine.ObservationStager.N_THREADS, steps)
+        print(head)
+        rows_ = []
+        for k in table:
+            vals = [t.get(k, float("nan")) for t in tables]
+            rows_.append({"phase": k, "mean_ms": float(np.mean(vals)), "max_ms": float(np.max(vals)),
+                          "min_ms": float(np.min(vals))})
+            print("  %-84s mean %8.2f  min %8.2f  max %8.2f ms/date" % (k, np.mean(vals), np.min(vals), np.max(vals)))
+        print("  iterations", kf.last_iterations[-steps:])
+        path = os.environ.get("KAFKA_TIMELINE_OUT")
+        if path:
+            with open(path, "a") as f:
+                f.write(json.dumps({"what": head, "mode": mode, "pinned_sources": pinned, "n_ranks": world,
+                                    "pixels_per_rank": n_pix, "staging_threads": engine.ObservationStager.N_THREADS,
+                                    "cpu_count": os.cpu_count(), "dates": steps, "phases": rows_,
+                                    "pixel_dates_per_s": world * n_pix / (max(t["total ms per date"] for t in tables) * 1e-3)})
+                        + "\n")
+    if os.environ.get("KAFKA_TIMELINE_LOG") and rank == 0:
         z = LOG[0][1]
         for tag, a, b in LOG:
             print("    %8.2f -> %8.2f ms  %s" % (1e3 * (a - z), 1e3 * (b - z), tag))
-    for e_gp, e_end in marks:
-        try:
-            print("  H2D of the next date done %.1f ms after the main stream finished the current date's kernels"
-                  % e_gp.elapsed_time(e_end))
-        except Exception as exc:
-            print("  (no mark: %s)" % exc)
-    for k, v in kf.profile.items():
-        print("  GPU %-40s %8.2f ms/date (CUDA events)" % (k, sum(a.elapsed_time(b) for a, b in v) / steps))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -11,6 +11,29 @@ from . import _lib
 from .device import padded, rows_zero_padded
 
 
+def pinned_raster(shape, dtype=np.float64):
+    """Numpy array in page-locked host memory.  A reader that fills such arrays
+    (e.g. GDAL's ``ReadAsArray(buf_obj=...)``) and hands them out through
+    ``get_band_data`` lets the device read the rasters straight from them: the
+    staging copy through this module's own pinned buffers -- one extra read and
+    write of every byte by the host cores -- is skipped.  The array must stay
+    untouched until the date it belongs to has been assimilated."""
+    dtype = np.dtype(dtype)
+    tdt = torch.bool if dtype == np.bool_ else getattr(torch, dtype.name)
+    return torch.empty(tuple(np.atleast_1d(shape)), dtype=tdt).pin_memory().numpy()
+
+
+def _pinned_view(a, dtype):
+    """Flat torch view of a numpy raster when the device can read it where it lies
+    (C-contiguous, of ``dtype``, page-locked), else None."""
+    if not isinstance(a, np.ndarray) or a.dtype != dtype or not a.flags.c_contiguous or a.size == 0:
+        return None
+    if not a.flags.writeable:
+        return None
+    t = torch.from_numpy(a.reshape(-1))
+    return t if t.is_pinned() else None
+
+
 class BandBuffers(object):
     """Compacted per-band observation rows on the device."""
 
@@ -76,28 +99,43 @@ class _Slot(object):
     """One set of pinned staging buffers + device rasters."""
 
     def __init__(self, n_bands, n, device):
-        self.cap = n_bands
-        self.h_obs = torch.empty((n_bands, n), dtype=torch.float64).pin_memory()
-        self.h_inv = torch.empty((n_bands, n), dtype=torch.float64).pin_memory()
-        self.h_msk = torch.empty((n_bands, n), dtype=torch.uint8).pin_memory()
+        self.cap, self.n, self.device = n_bands, n, device
         self.d_obs = torch.empty((n_bands, n), dtype=torch.float64, device=device)
         self.d_inv = torch.empty((n_bands, n), dtype=torch.float64, device=device)
         self.d_msk = torch.empty((n_bands, n), dtype=torch.uint8, device=device)
+        # page-locked staging buffers: allocated when the first raster arrives that has to be staged
+        # (rasters handed over in page-locked memory never need them)
+        self.h_obs = self.h_inv = self.h_msk = None
+        self.np_obs = self.np_inv = self.np_msk = None
         self.h_raw = self.d_raw = None        # (n_bands, n) 4-byte cells for raw rasters, allocated on first use
-        # numpy views of the pinned buffers, made once (a fresh .numpy() per band and date is
-        # measurable on small rasters)
-        self.np_obs, self.np_inv = self.h_obs.numpy(), self.h_inv.numpy()
-        self.np_msk = self.h_msk.numpy().view(np.bool_)
         self.np_raw = None
         self.copied = [torch.cuda.Event() for _ in range(n_bands)]   # H2D of band b done
         self.gathered = None                                         # main stream finished reading d_*
 
+    def ensure_host(self, floats=True):
+        if floats and self.h_obs is None:
+            self.h_obs = torch.empty((self.cap, self.n), dtype=torch.float64).pin_memory()
+            self.h_inv = torch.empty((self.cap, self.n), dtype=torch.float64).pin_memory()
+            # numpy views made once (a fresh .numpy() per band and date is measurable on small rasters)
+            self.np_obs, self.np_inv = self.h_obs.numpy(), self.h_inv.numpy()
+        if self.h_msk is None:
+            self.h_msk = torch.empty((self.cap, self.n), dtype=torch.uint8).pin_memory()
+            self.np_msk = self.h_msk.numpy().view(np.bool_)
+
+    def ensure_raw(self, host):
+        if self.d_raw is None:
+            self.d_raw = torch.empty((self.cap, self.n), dtype=torch.int32, device=self.device)
+        if host and self.h_raw is None:
+            self.h_raw = torch.empty((self.cap, self.n), dtype=torch.int32).pin_memory()
+            self.np_raw = self.h_raw.numpy()
+
 
 class StagedDate(object):
     """Hand-over between ``stage`` and ``finish``."""
-    __slots__ = ("slot", "n_bands", "device_data", "raw", "one_event", "sources")
+    __slots__ = ("slot", "n_bands", "device_data", "raw", "one_event", "sources", "keep")
 
-    def __init__(self, slot, n_bands, device_data=None, raw=None, one_event=False, sources=None):
+    def __init__(self, slot, n_bands, device_data=None, raw=None, one_event=False, sources=None, keep=None):
+        self.keep = keep                     # host views the queued copies read from: alive until finish()
         # sources: band -> ("bhr", kernel_type, kernels, mask, qa) or ("s1", raw_type, sigma0, marker), device tensors
         self.slot, self.n_bands, self.device_data = slot, n_bands, device_data
         self.raw = raw or {}                 # band -> (raw_type, ScaledReflectance, has_mask)
@@ -149,6 +187,8 @@ class ObservationStager(object):
         """Main diagonal of the reference's (ny*nx)^2 sparse inverse-variance
         matrix (Sentinel2_Observations.py:176-179), or a plain raster of it."""
         if sp.issparse(unc):
+            if unc.format == "dia" and len(unc.offsets) == 1 and unc.offsets[0] == 0 and unc.shape[0] == unc.shape[1]:
+                return unc.data[0]                # the stored diagonal itself, no copy
             return unc.diagonal()
         a = np.asarray(unc)
         if a.ndim == 2 and a.shape == (n, n):
@@ -202,16 +242,20 @@ class ObservationStager(object):
                 if dt_ not in ScaledReflectance.RAW_TYPES:
                     raise TypeError("raw reflectance rasters must be int16, uint16 or float32, not %s" % dt_)
                 raw[b] = (ScaledReflectance.RAW_TYPES[dt_], d.uncertainty, d.mask is not None, dt_)
-        if raw and slot.h_raw is None:
-            slot.h_raw = torch.empty((slot.cap, n), dtype=torch.int32).pin_memory()
-            slot.d_raw = torch.empty((slot.cap, n), dtype=torch.int32, device=self.device)
-            slot.np_raw = slot.h_raw.numpy()
         holders = [None if (b in raw or b in sources) else _Staged(d.observations, d.mask, self._inv_var(d.uncertainty, n))
                    for b, d in enumerate(current_data)]
         futures = []
         small = n < (1 << 18)                          # tiny rasters: the pool's hand-over costs more than the copy
+        # rasters that already lie in page-locked memory (pinned_raster) are read by the DMA engine
+        # where they are: no staging copy, the host cores do not touch the data at all
+        direct = {} if small else self._direct_sources(current_data, holders, raw, sources, n)
+        staged_bands = [b for b in range(nb) if b not in sources and b not in direct]
+        if raw:
+            slot.ensure_raw(host=any(b in raw for b in staged_bands))
+        if staged_bands:
+            slot.ensure_host(floats=any(b not in raw for b in staged_bands))
         for b, d in enumerate(current_data):
-            if small or b in sources:
+            if small or b in sources or b in direct:
                 futures.append([])
             elif b in raw:
                 futures.append([self._pool.submit(self._stage_raw, slot, b, d, raw[b], n * k // parts,
@@ -243,7 +287,20 @@ class ObservationStager(object):
             for f in futures[b]:
                 f.result()
             with torch.cuda.stream(self._copy_stream):
-                if b in raw:
+                if b in direct:
+                    t_obs, t_inv, t_msk = direct[b]
+                    if b in raw:
+                        nbytes = n * raw[b][3].itemsize
+                        slot.d_raw[b].view(torch.uint8)[:nbytes].copy_(t_obs.view(torch.uint8), non_blocking=True)
+                        self.h2d_bytes += nbytes
+                    else:
+                        slot.d_obs[b].copy_(t_obs, non_blocking=True)
+                        slot.d_inv[b].copy_(t_inv, non_blocking=True)
+                        self.h2d_bytes += n * 16
+                    if t_msk is not None:
+                        slot.d_msk[b].copy_(t_msk.view(torch.uint8), non_blocking=True)
+                        self.h2d_bytes += n
+                elif b in raw:
                     item = raw[b][3].itemsize
                     nbytes = n * item
                     src = slot.h_raw[b].view(torch.uint8)[:nbytes]
@@ -258,7 +315,34 @@ class ObservationStager(object):
                     slot.d_msk[b].copy_(slot.h_msk[b], non_blocking=True)
                     self.h2d_bytes += n * 17
                 slot.copied[b].record(self._copy_stream)
-        return StagedDate(slot, nb, raw=raw, sources=sources)
+        return StagedDate(slot, nb, raw=raw, sources=sources, keep=direct)
+
+    @staticmethod
+    def _direct_sources(current_data, holders, raw, sources, n):
+        """band -> (obs, inverse variance or None, mask or None) as flat torch views of the
+        caller's own page-locked arrays, for the bands whose rasters can all be read in place."""
+        direct = {}
+        for b, d in enumerate(current_data):
+            if b in sources:
+                continue
+            if b in raw:
+                t_obs = _pinned_view(np.asarray(d.observations), raw[b][3])
+                t_msk = None
+                if raw[b][2]:
+                    t_msk = _pinned_view(np.asarray(d.mask), np.dtype(np.bool_))
+                    if t_msk is None:
+                        continue
+                if t_obs is not None and t_obs.numel() == n:
+                    direct[b] = (t_obs, None, t_msk)
+                continue
+            h = holders[b]
+            t_obs = _pinned_view(h.observations, np.dtype(np.float64))
+            t_inv = _pinned_view(h._kafka_inv_var, np.dtype(np.float64))
+            t_msk = _pinned_view(h.mask, np.dtype(np.bool_))
+            if t_obs is not None and t_inv is not None and t_msk is not None and \
+                    t_obs.numel() == t_inv.numel() == t_msk.numel() == n:
+                direct[b] = (t_obs, t_inv, t_msk)
+        return direct
 
     def _upload_bhr(self, d, n):
         """Kernel weights (3, ny, nx), quality level and mask of one MODIS band to the device

@@ -1,9 +1,14 @@
 """Import the UNMODIFIED reference behind stub modules (TEST INFRASTRUCTURE).
 
-Works only where ``/root/reference`` exists (the build container).  Nothing in
-``-m gpu`` tests, ``smoke()`` or ``bench.py`` calls this; it is used by
-``oracle/make_golden.py`` and by the container-only validation tests, which skip
-when the path is absent.
+The package is taken from ``/root/reference`` (the build container) or, where
+that path does not exist (the GPU box), from ``baseline/_ref``: the same files,
+installed there by ``oracle/install_ref.py`` (``pip install --target``) when
+``__graft_entry__.build()`` runs in the build container; that directory is
+git-ignored and travels with the working tree.  Used by ``oracle/make_golden.py``,
+by the validation tests that compare the oracle with the reference (they skip
+when neither location exists) and by ``oracle/ref_runner.py``, which times the
+reference for ``bench.py``'s CPU legs.  Nothing in the product package, the
+``-m gpu`` parity tests or ``smoke()`` needs it.
 
 The reference does not import as-is here (no gdal / matplotlib /
 BRDF_descriptors / SIAC; NumPy 2 and SciPy 1.18 dropped names it uses).  Recipe
@@ -21,7 +26,11 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = "/root/reference"
+_REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# the source tree in the build container; elsewhere (the GPU box) the unmodified package as
+# ``oracle/install_ref.py`` installed it with pip into the git-ignored baseline/_ref
+_CANDIDATES = ("/root/reference", os.path.join(_REPO, "baseline", "_ref"))
+REFERENCE_ROOT = next((c for c in _CANDIDATES if os.path.isdir(os.path.join(c, "kafka"))), _CANDIDATES[0])
 
 
 def available():
@@ -39,7 +48,7 @@ def _stub(name, **attrs):
 
 
 def load():
-    """Return the reference's ``kafka`` package (imported from /root/reference)."""
+    """Return the reference's ``kafka`` package (imported from REFERENCE_ROOT)."""
     if not available():
         raise RuntimeError("reference tree not present at %s" % REFERENCE_ROOT)
     import numpy as np
@@ -84,5 +93,5 @@ def load():
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
     import kafka  # noqa: the reference package
-    assert os.path.realpath(kafka.__file__).startswith(REFERENCE_ROOT)
+    assert os.path.realpath(kafka.__file__).startswith(os.path.realpath(REFERENCE_ROOT))
     return kafka

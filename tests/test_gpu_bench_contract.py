@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def _run(*extra):
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--gpus", "1", "--steps", "2", "--warmup", "3",
-                          "--rows", "40", "--cpu-sample", "2048"] + list(extra),
+                          "--rows", "40", "--ref-chunk", "12", "--port-sample", "2048"] + list(extra),
                          capture_output=True, text=True, cwd=ROOT, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
     lines = [l for l in out.stdout.splitlines() if l.strip()]
@@ -24,7 +24,8 @@ def _run(*extra):
 def test_bench_line_has_the_contract_keys():
     d = _run()
     for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
-                "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"):
+                "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "e2e_raw_ingest", "gpu_launches", "roofline",
+                "cpu_baseline"):
         assert key in d, key
     assert d["metric"] == "pixel-dates/sec" and d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 3
     assert d["dtype"] == "f64" and d["scaling"] == "weak" and d["higher_is_better"] is True
@@ -32,13 +33,17 @@ def test_bench_line_has_the_contract_keys():
     e = d["e2e"]
     assert e["value"] > 0 and e["h2d_bytes_per_step"] == 40 * 10980 * 10 * 17 and e["d2h_bytes_per_step"] == 40 * 10980 * 10 * 8
     assert e["value"] < d["value"] * 1.05                     # never faster than the resident number (noise margin)
+    raw = d["e2e_raw_ingest"]
+    assert raw["value"] > 0 and raw["h2d_bytes_per_step"] == 40 * 10980 * 10 * 2 and raw["d2h_bytes_per_step"] == e["d2h_bytes_per_step"]
     r = d["roofline"]
     for key in ("bound", "achieved", "peak", "unit", "frac", "traffic"):
         assert key in r, key
-    assert r["bound"] in ("hbm", "tensor") and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-12
-    assert 0.0 < r["solve_kernel"]["frac"] < 1.2 and r["fp64"]["frac"] > 0
+    # the dominant kernel is bound by the fp64 pipe; its HBM figure and the HBM-bound solve kernel are nested
+    assert r["bound"] == "fp64" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-12
+    assert r["hbm"]["frac"] > 0 and r["solve_kernel"]["bound"] == "hbm" and 0.0 < r["solve_kernel"]["frac"] < 1.2
     c = d["cpu_baseline"]
-    assert c["kind"] == "port" and c["cores"] == 1 and c["value"] > 0 and "sample" in c
+    assert c["kind"] == "reference" and c["cores"] == 1 and c["value"] > 0 and "sample" in c
+    assert c["port"]["kind"] == "port" and c["port"]["value"] > c["value"]
     assert set(("sm_mhz", "sm_max_mhz", "reasons")) <= set(d["clocks"])
 
 

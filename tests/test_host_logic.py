@@ -117,23 +117,54 @@ def test_global_norm_gloo_world2(tmp_path):
 
 
 def test_bench_reference_arm_prints_contract_line():
-    """bench.py --impl reference: the CPU arm (oracle port on the host cores) prints
-    one JSON line with the contract's keys; here on a small bounded sample."""
+    """bench.py --impl reference: the CPU arm (the unmodified reference on the host cores)
+    prints one JSON line with the contract's keys; here on small chunks.  The processes of
+    that arm never import the product package, so no CUDA library is mapped in them."""
     import json
+    from oracle import ref_shim
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1",
-                          "--warmup", "0", "--cpu-sample", "16384"], capture_output=True, text=True, timeout=600,
+                          "--warmup", "0", "--ref-chunk", "12"], capture_output=True, text=True, timeout=600,
                          env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
     assert out.returncode == 0, out.stderr[-2000:]
     line = json.loads(out.stdout.strip().splitlines()[-1])
     for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
                 "scaling", "config", "cpu_baseline", "e2e"):
         assert key in line, key
-    assert line["impl"] == "reference" and line["value"] > 0 and line["cpu_baseline"]["kind"] == "port"
+    assert line["impl"] == "reference" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == ("reference" if ref_shim.available() else "port")
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["value"] == line["value"]
+    assert "note" not in line["config"]                 # same config dict as the GPU arm's line
     # ranks other than 0 print nothing and exit 0 (torchrun, N > 1)
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
                          capture_output=True, text=True, timeout=120, env=dict(os.environ, RANK="1", WORLD_SIZE="2"))
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+def test_cpu_legs_do_not_import_the_product_package():
+    """The functions bench.py runs in the CPU legs' worker processes leave
+    kafka_inferenceengine_b200 (and with it libkafka_b200.so) unimported."""
+    code = ("import sys; sys.path.insert(0, %r); import bench; "
+            "jobs = bench._cpu_workload(1, 6); bench._port_job(jobs[0]); "
+            "r = bench._ref_chunk(jobs[0]) if bench._reference_installed() else None; "
+            "assert not any(m.startswith('kafka_inferenceengine_b200') for m in sys.modules), 'product imported'; "
+            "assert not any('libkafka_b200' in l for l in open('/proc/self/maps')), 'library mapped'; print('OK')" % ROOT)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
+
+
+def test_oracle_synthetic_restates_the_package_constants():
+    """oracle/synthetic.py (used by the CPU legs instead of the product package) and
+    kafka_inferenceengine_b200/synthetic.py describe the same workload."""
+    from kafka_inferenceengine_b200 import synthetic as syn
+    from oracle import synthetic as osyn
+    assert np.array_equal(osyn.SAIL_MEAN, syn.SAIL_MEAN) and np.array_equal(osyn.SAIL_SIGMA, syn.SAIL_SIGMA)
+    assert osyn.S2_PARAMETERS == syn.S2_PARAMETERS
+    a = osyn.make_emulators(3, 40)
+    rng = np.random.default_rng(1234)
+    b = [syn.make_emulator(rng, syn.SAIL_MEAN, syn.SAIL_SIGMA, n_train=40) for _ in range(3)]
+    for ga, gb in zip(a, b):
+        assert np.array_equal(ga.inputs, gb.inputs) and np.array_equal(ga.targets, gb.targets)
+        assert np.array_equal(ga.theta, gb.theta)
 
 
 def test_get_chunks_matches_reference_tiling():
