@@ -670,6 +670,12 @@ int kafka_gp_pack_host(const double* inputs, const double* theta, const double* 
         // 2^29 leaves room for the zero-weight rows' offset of -2^29.
         const double bound = kL * (fabs(theta[D]) + 0.5 * c + fabs(lshift) + sqrt(1200.0 * c));
         if (!(bound < 536870912.0) || fabs(lshift) > 100.0) wide = 1.0;
+        // ... and its unshifted value must stay a finite double: with the per-pixel factor exp(-x'.x'/2)
+        // hoisted out of the loop the exponent reaches ln s_f + (ln|alpha| - cbar) + max(z.x' - c/2), where
+        // z.x' <= sqrt(1200 c) on the near path, i.e. at most +600 at c = 1200.  Past ~ln(DBL_MAX) = 709.8
+        // the unchecked exponent insert would wrap; such a table keeps the factor inside the exponent.
+        const double zmax = c >= 1200.0 ? 600.0 : sqrt(1200.0 * c) - 0.5 * c;
+        if (!(theta[D] + lshift + zmax < 700.0)) wide = 1.0;
     }
     table[2 * DP + 2] = wide;
     return 0;

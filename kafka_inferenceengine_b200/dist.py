@@ -44,20 +44,28 @@ def shard_pixels(n_pix, rank, world_size):
     return i0, min(n_pix, i0 + per)
 
 
-def global_norm(sum_sq_local, n_elems_local, comm=None):
+def global_norm(sum_sq_local, n_elems_local, comm=None, n_bad_local=None):
     """``(sqrt(sum of squares over all ranks) / total element count)`` and the
     total count.  ``sum_sq_local`` may be a python float or a 0-d/1-element
-    tensor on any device."""
+    tensor on any device.  With ``n_bad_local`` (same kinds) the bad-pixel count
+    of the solve rides in the same all-reduce and its total is returned as a
+    third value."""
     import torch.distributed as dist
     if comm is None and not (dist.is_available() and dist.is_initialized()):
         s = float(sum_sq_local)
-        return np.sqrt(s) / float(n_elems_local), float(n_elems_local)
+        res = (np.sqrt(s) / float(n_elems_local), float(n_elems_local))
+        return res if n_bad_local is None else res + (int(n_bad_local),)
     if isinstance(sum_sq_local, torch.Tensor):
         dev = sum_sq_local.device
-        buf = torch.stack([sum_sq_local.reshape(-1)[0].to(torch.float64),
-                           torch.tensor(float(n_elems_local), dtype=torch.float64, device=dev)])
+        parts = [sum_sq_local.reshape(-1)[0].to(torch.float64),
+                 torch.tensor(float(n_elems_local), dtype=torch.float64, device=dev)]
+        if n_bad_local is not None:
+            parts.append(n_bad_local.reshape(-1)[0].to(torch.float64) if isinstance(n_bad_local, torch.Tensor)
+                         else torch.tensor(float(n_bad_local), dtype=torch.float64, device=dev))
+        buf = torch.stack(parts)
     else:
-        buf = torch.tensor([float(sum_sq_local), float(n_elems_local)], dtype=torch.float64)
+        buf = torch.tensor([float(sum_sq_local), float(n_elems_local)]
+                           + ([] if n_bad_local is None else [float(n_bad_local)]), dtype=torch.float64)
     backend = dist.get_backend(comm)
     if backend == "gloo" and buf.is_cuda:
         buf = buf.cpu()
@@ -68,7 +76,8 @@ def global_norm(sum_sq_local, n_elems_local, comm=None):
             tot = _lib.read_small(buf)           # no device->host memcpy: see kafka_read_small
     else:
         tot = buf.numpy()
-    return float(np.sqrt(tot[0]) / tot[1]), float(tot[1])
+    res = (float(np.sqrt(tot[0]) / tot[1]), float(tot[1]))
+    return res if n_bad_local is None else res + (int(round(float(tot[2]))),)
 
 
 def gather_interleaved(x_local, comm=None, dst=None):

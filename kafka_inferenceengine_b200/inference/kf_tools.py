@@ -261,12 +261,23 @@ def blend_prior(prior_mean, prior_cov_inverse, x_forecast, P_forecast_inverse):
         cp_t = Cp.materialise().data
     x_out = DeviceVector.empty(n, P, dev)
     c_out = BlockDiag.empty(n, P, dev)
-    n_bad = torch.zeros(1, dtype=torch.int32, device=dev)
+    n_bad = torch.zeros(2, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         _lib.check(lib.kafka_blend_prior(_lib.ptr(mu_t), _lib.ptr(cp_t), _lib.ptr(xf.data), _lib.ptr(Pf.data),
                                          Pf.ld, n, P, _lib.ptr(x_out.data), _lib.ptr(c_out.data),
                                          _lib.ptr(n_bad), flags, _lib.stream_ptr()), "kafka_blend_prior")
+        _warn_bad(n_bad, "blend_prior: %d pixels have a combined inverse covariance that is not positive definite; "
+                         "their mean is left at the forecast")
     return x_out, c_out
+
+
+def _warn_bad(n_bad, message):
+    """Read a kernel's failed-pixel counter back (kafka_read_small: no device->host memcpy) and
+    log it the way do_all_bands does; the reference's LU never notices such blocks."""
+    n = int(_lib.read_small(n_bad)[0])
+    if n:
+        LOG.warning(message, n)
+    return n
 
 
 def propagate_and_blend_prior(x_analysis, P_analysis, P_analysis_inverse, M_matrix, Q_matrix,
@@ -315,10 +326,12 @@ def propagate_information_filter_SLOW(x_analysis, P_analysis, P_analysis_inverse
     x_f = _apply_model(xa, _model_diag(M_matrix, P, n * P, dev))
     q = _diag_vector(Q_matrix, P, dev)
     out = BlockDiag.empty(n, P, dev)
-    n_bad = torch.zeros(1, dtype=torch.int32, device=dev)
+    n_bad = torch.zeros(2, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         _lib.check(lib.kafka_advance_exact(_lib.ptr(Pi.data), _lib.ptr(q.data), Pi.ld, n, P, _lib.ptr(out.data),
                                            _lib.ptr(n_bad), _lib.stream_ptr()), "kafka_advance_exact")
+        _warn_bad(n_bad, "propagate_information_filter_SLOW: %d pixels have an inflated block that is not positive "
+                         "definite; their inverse covariance is carried over unchanged")
     return x_f, None, out
 
 

@@ -276,8 +276,8 @@ class LinearKalman(object):
             ssq, self._n_bad_last = ws.read_scalars()
             return float(np.sqrt(ssq) / float(n_elems)), float(n_elems)
         from .dist import global_norm
-        self._n_bad_last = None
-        return global_norm(ws.norm2, n_elems, self.comm)
+        norm, count, self._n_bad_last = global_norm(ws.norm2, n_elems, self.comm, n_bad_local=ws.n_bad)
+        return norm, count
 
     def do_all_bands(self, timestep, current_data, x_forecast, P_forecast,
                      P_forecast_inverse, convergence_tolerance=1e-3,
@@ -320,6 +320,8 @@ class LinearKalman(object):
 
         x_prev = x_forecast
         n_iter = 1
+        n_bad = n_bad_max = 0                 # pixels the solve left at the forecast: last iteration / worst
+        is_wcm = self._create_observation_operator.kind == "wcm"
         norms = []
         not_converged = True
         x_analysis = None
@@ -356,6 +358,13 @@ class LinearKalman(object):
                     # a full emulator pass is now queued: use the wait to stage the next date
                     self._prefetch_next()
                 convergence_norm, count = self._global_norm(ws)   # linear_kf.py:293
+                n_bad = self._n_bad_last
+                n_bad_max = max(n_bad_max, n_bad)
+                if n_bad and is_wcm:
+                    # the reference's forward model refuses such a linearisation point in the iteration
+                    # that meets it (sar_forward_model.py:66-71)
+                    raise ValueError("%d pixels left the Water-Cloud model's domain (LAI <= 0 or SM <= 0) or have "
+                                     "a non positive-definite information matrix (iteration %d)" % (n_bad, n_iter))
                 x_analysis = x_new
                 x_analysis._uniform = False      # a solved state: skip the shared-vector test next iteration
             else:
@@ -375,13 +384,10 @@ class LinearKalman(object):
             x_prev = x_analysis
             n_iter += 1
 
-        n_bad = self._n_bad_last if self._n_bad_last is not None else ws.read_scalars()[1]
-        if n_bad and self._create_observation_operator.kind == "wcm":
-            # the reference's forward model refuses such states (sar_forward_model.py:66-71)
-            raise ValueError("%d pixels left the Water-Cloud model's domain (LAI <= 0 or SM <= 0) or have a "
-                             "non positive-definite information matrix" % n_bad)
-        if n_bad:
-            LOG.warning("%d pixels had a non positive-definite information matrix; left at the forecast", n_bad)
+        if n_bad_max:
+            # the count of the last solve; an earlier linearisation point may have lost more
+            LOG.warning("%d pixels had a non positive-definite information matrix; left at the forecast"
+                        "%s", n_bad, "" if n_bad == n_bad_max else " (%d in an earlier iteration)" % n_bad_max)
         if (self.hessian_correction or getattr(self, "_force_hessian", False)) and groups:
             # P_analysis_inverse - P_correction (linear_kf.py:319,416), evaluated at x_analysis
             for group in groups:
