@@ -56,6 +56,11 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--host-sources", default="pinned", choices=["pinned", "pageable"],
                     help="memory the e2e legs' host rasters live in (see e2e.api)")
+    ap.add_argument("--comm", default="native", choices=["native", "torch"],
+                    help="who carries the per-iteration convergence all-reduce at N > 1: the library's own NCCL "
+                         "communicator behind the C ABI (kafka_ctx_create / kafka_allreduce_norm) or torch.distributed")
+    ap.add_argument("--c3-days", type=int, default=365, help="daily steps of the c3 workload")
+    ap.add_argument("--c3-side", type=int, default=2400, help="side of the square c3 tile per GPU")
     ap.add_argument("--workload", default="c4shard", choices=["c4shard", "c2", "c3", "c5"],
                     help="c4shard (default, the bench line): 1/8 of the full S2 tile per GPU; the others are the "
                          "remaining BASELINE.json configs, run on request for the record (single GPU)")
@@ -445,108 +450,243 @@ def measure_c2(device, reps):
             "iterations": kf.last_iterations[-n_dates:], "n_gpus": 1}
 
 
-def run_other_workload(args):
+def _dist_setup(args):
+    """(world, rank, device, comm, barrier, max_over_ranks) for the per-rank workloads."""
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1:
+        raise SystemExit("launch with torch.distributed.run --nproc-per-node %d" % args.gpus)
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    comm = None
+    if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        dist.init_process_group("nccl", device_id=device)
+        comm = _make_comm(args, device)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return world, rank, local, device, comm, barrier, max_over_ranks
+
+
+def _make_comm(args, device):
+    """torch.distributed is the plumbing (rendezvous, barrier, max over ranks); the hot path's all-reduce
+    goes through the library's own communicator unless --comm torch asks otherwise."""
+    import torch.distributed as dist
+    if args.comm == "torch":
+        return dist.group.WORLD
+    from kafka_inferenceengine_b200.dist import NativeComm
+    return NativeComm.from_process_group(dist.group.WORLD, device)
+
+
+def _hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_c3(args):
+    """BASELINE configs[2]: MODIS tile 2400 x 2400 (5.76 M px) per GPU, 7-parameter TIP state, 2 broadbands
+    through per-band state mappers (D=4, T=500), --c3-days daily steps (365) with an observation every 8th
+    day, propagate_information_filter_LAI with Q[6::7] = 0.04 (kafka_test.py:156-217,
+    kafka/inference/kf_tools.py:292-314).  End to end: ONE LinearKalman.run() fed with HOST rasters on the
+    observation days, RasterOutput reading the float32 mean / uncertainty rasters back EVERY day.  Weak
+    scaling: one tile per rank, global convergence norm."""
     import torch
     import kafka_inferenceengine_b200 as kb
-    from kafka_inferenceengine_b200 import _lib
     from kafka_inferenceengine_b200 import synthetic as syn
-    from kafka_inferenceengine_b200.device import BlockDiag, DeviceVector, padded, tri_count
-    torch.cuda.set_device(0)
-    device = torch.device("cuda", 0)
+    from kafka_inferenceengine_b200.device import DeviceVector
+    from kafka_inferenceengine_b200.inference.utils import emulator_table, linearize_bands
+    from kafka_inferenceengine_b200.output import RasterOutput
+    world, rank, local, device, comm, barrier, max_over_ranks = _dist_setup(args)
     base = dt.datetime(2017, 1, 1)
+    ny = nx = args.c3_side
+    N = ny * nx
+    rng = np.random.default_rng(3)
+    mappers = [np.array([0, 1, 6, 2]), np.array([3, 4, 6, 5])]
+    gps = [syn.make_emulator(rng, syn.TIP_MEAN[m], syn.TIP_SIGMA[m], n_train=500, w_scale=0.15) for m in mappers]
+    gen = torch.Generator(device=device).manual_seed(11 + rank)
+    xt = DeviceVector.empty(N, 7, device)
+    xt.data.copy_(torch.from_numpy(syn.TIP_MEAN).to(device)[:, None] + 0.5 * torch.from_numpy(syn.TIP_SIGMA).to(device)[:, None]
+                  * torch.randn(xt.data.shape, generator=gen, dtype=torch.float64, device=device))
+    rho = torch.empty((2, xt.ld), dtype=torch.float64, device=device)
+    linearize_bands(xt, [(emulator_table(g_, device), m) for g_, m in zip(gps, mappers)], None, False, h0=rho,
+                    want_jac=False)
+    rho = rho[:, :N].contiguous()
+    sig = torch.clamp(0.05 * rho.abs(), min=2.5e-3)
+    rho = rho + sig * torch.randn(rho.shape, generator=gen, dtype=torch.float64, device=device)
+    msk = torch.rand(rho.shape, generator=gen, device=device) < 0.9
+    inv = torch.where(msk, 1.0 / sig ** 2, torch.full_like(rho, float("inf")))
+    n_steps = args.c3_days
+    dates = [base + dt.timedelta(days=d, hours=12) for d in range(0, n_steps, 8)]
+    pinned = args.host_sources == "pinned"
+    obs = HostObservationsGeneric(dates, gps, rho, inv, msk, (ny, nx), pinned)
+    del rho, inv, xt
+    out = RasterOutput(syn.TIP_PARAMETERS)
+    kf = kb.LinearKalman(obs, out, np.ones((ny, nx), dtype=bool), kb.create_nonlinear_observation_operator,
+                         syn.TIP_PARAMETERS, state_propagation=kb.propagate_information_filter_LAI, prior=None,
+                         device=device, comm=comm)
+    out.pixels = kf.pixels
+    kf.set_trajectory_model()
+    q = DeviceVector.empty(N, 7, device)
+    q.data.zero_()
+    q.data[6] = 0.04
+    kf.trajectory_uncertainty = kb.DiagonalMatrix(q, 7, device)
+    mean, prior_inv = kb.tip_prior_full({"n_pixels": N})
+    grid = [base + dt.timedelta(days=d) for d in range(n_steps + 1)]
+    kf.run(grid[:10], mean, None, prior_inv, iter_obs_op=True)          # warm-up: two observation dates
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    kf.last_iterations = []
+    h2d0, d2h0 = kf._stager.h2d_bytes, out.d2h_bytes
+    t0 = time.perf_counter()
+    kf.run(grid, mean, None, prior_inv, iter_obs_op=True)
+    torch.cuda.synchronize()
+    ms = max_over_ranks(1e3 * (time.perf_counter() - t0))
+    clocks = sampler.stop() if sampler else None
+    barrier()
+    iters = list(kf.last_iterations)
 
-    def timed(fn, reps, warm):
-        for _ in range(warm):
-            fn()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(reps):
-            fn()
-        e1.record()
-        torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / reps
-
-    if args.workload == "c2":
-        emit(json.dumps(measure_c2(device, args.steps)))
-    elif args.workload == "c3":
-        # configs[2]: MODIS tile 2400 x 2400, 7-param TIP state, 2 bands through state mappers (D=4, T=500),
-        # daily steps, an observation every 8th day, propagate_information_filter_LAI with Q[6::7] = 0.04
-        ny = nx = 2400
-        N = ny * nx
-        rng = np.random.default_rng(3)
-        mappers = [np.array([0, 1, 6, 2]), np.array([3, 4, 6, 5])]
-        gps = [syn.make_emulator(rng, syn.TIP_MEAN[m], syn.TIP_SIGMA[m], n_train=500, w_scale=0.15) for m in mappers]
-        from kafka_inferenceengine_b200.inference.utils import emulator_table, linearize_bands
-        gen = torch.Generator(device=device).manual_seed(11)
-        xt = DeviceVector.empty(N, 7, device)
-        xt.data.copy_(torch.from_numpy(syn.TIP_MEAN).to(device)[:, None] + 0.5 * torch.from_numpy(syn.TIP_SIGMA).to(device)[:, None]
-                      * torch.randn(xt.data.shape, generator=gen, dtype=torch.float64, device=device))
-        rho = torch.empty((2, xt.ld), dtype=torch.float64, device=device)
-        linearize_bands(xt, [(emulator_table(g_, device), m) for g_, m in zip(gps, mappers)], None, False, h0=rho,
-                        want_jac=False)
-        rho = rho[:, :N].contiguous()
-        sig = torch.clamp(0.05 * rho.abs(), min=2.5e-3)
-        rho = rho + sig * torch.randn(rho.shape, generator=gen, dtype=torch.float64, device=device)
-        msk = torch.rand(rho.shape, generator=gen, device=device) < 0.9
-        inv = torch.where(msk, 1.0 / sig ** 2, torch.full_like(rho, float("inf")))
-        n_steps = 32
-        dates = [base + dt.timedelta(days=d, hours=12) for d in range(0, n_steps, 8)]
-        obs = DeviceObservationsGeneric(dates, gps, rho, inv, msk.to(torch.uint8), (ny, nx))
-        kf = kb.LinearKalman(obs, NullOutput(), np.ones((ny, nx), dtype=bool), kb.create_nonlinear_observation_operator,
-                             syn.TIP_PARAMETERS, state_propagation=kb.propagate_information_filter_LAI, prior=None,
-                             device=device)
-        kf.set_trajectory_model()
-        q = DeviceVector.empty(N, 7, device)
-        q.data.zero_()
-        q.data[6] = 0.04
-        kf.trajectory_uncertainty = kb.DiagonalMatrix(q, 7, device)
-        mean, prior_inv = kb.tip_prior_full({"n_pixels": N})
-        grid = [base + dt.timedelta(days=d) for d in range(n_steps + 1)]
-        kf.run(grid[:9], mean, None, prior_inv, iter_obs_op=True)          # warm-up
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        kf.last_iterations = []
-        kf.run(grid, mean, None, prior_inv, iter_obs_op=True)
-        torch.cuda.synchronize()
-        ms = 1e3 * (time.perf_counter() - t0)
-        # the advance kernel on its own (propagate_information_filter_LAI, SURVEY 8d: 24 B in, 8P + 4P(P+1) out)
-        xa = DeviceVector.broadcast(syn.TIP_MEAN, N, device)
-        Aa = prior_inv.materialise()
-        adv_ms = timed(lambda: kb.propagate_information_filter_LAI(xa, None, Aa, None, q), 10, 3)
+    # parity inside the bench: the first 2048 pixels of this rank's tile, first observation date, against
+    # oracle B with the iteration count the GPU run took on that date (the global norm decided it)
+    parity = None
+    if rank == 0:
+        from oracle import kafka_cpu as kc
+        from oracle.gp import GaussianProcess
+        ns = 2048
+        d0 = dates[0]
+        bd = [obs.get_band_data(d0, b) for b in range(2)]
+        ys = [np.asarray(b.observations).reshape(-1)[:ns] for b in bd]
+        ms_ = [np.asarray(b.mask).reshape(-1)[:ns] for b in bd]
+        ws = [kc.gate_inverse_variance(np.asarray(b.uncertainty).reshape(-1)[:ns], m_) for b, m_ in zip(bd, ms_)]
+        ogps = [GaussianProcess(g_.inputs, g_.targets, g_.theta) for g_ in gps]
+        ops = [(lambda xp, gp=ogps[b], m_=ms_[b], mp=mappers[b]: kc.emulator_operator(gp, xp, 7, m_, state_mapper=mp))
+               for b in range(2)]
+        x0n, _, inv_n = kc.tip_prior()
+        xo, Ao, _, _, _ = kc.do_all_bands(ops, ys, ws, ms_, np.tile(x0n, ns), np.repeat(inv_n[None].astype(np.float64), ns, axis=0),
+                                          7, fixed_iterations=iters[0])
+        sub = [b._replace(observations=np.asarray(b.observations).reshape(-1)[:ns].reshape(1, ns),
+                          uncertainty=np.asarray(b.uncertainty).reshape(-1)[:ns].reshape(1, ns),
+                          mask=np.asarray(b.mask).reshape(-1)[:ns].reshape(1, ns)) for b in bd]
+        kf_s = kb.LinearKalman(None, None, np.ones((1, ns), dtype=bool), kb.create_nonlinear_observation_operator,
+                               syn.TIP_PARAMETERS, prior=None, device=device)
+        m_s, p_s = kb.tip_prior_full({"n_pixels": ns})
+        xg, _, Ag, _ = kf_s.do_all_bands(d0, sub, m_s, None, p_s, min_iterations=iters[0],
+                                         convergence_tolerance=float("inf"))
+        ex = float(np.max(np.abs(np.asarray(xg) - xo) / np.maximum(np.abs(xo), 1e-3)))
+        idx = np.arange(7)
+        ed = float(np.max(np.abs(Ag.blocks()[:, idx, idx] - Ao[:, idx, idx]) / Ao[:, idx, idx]))
+        assert ex < 1e-6 and ed < 1e-6, (ex, ed)
+        parity = {"pixels": ns, "date": 0, "solves": iters[0], "max_rel_err_x": ex, "max_rel_err_diag": ed,
+                  "against": "oracle B (fp64), same number of solves"}
+    if rank == 0:
         adv_bytes = N * (24 + 8 * 7 + 4 * 7 * 8)
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
-            os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
-        hbm = float(peaks.get("hbm_gbs", 6650.0))
-        emit(json.dumps({"workload": "c3: MODIS tile 2400x2400 (5.76 M px), TIP P=7, B=2 (D=4, T=500), %d daily steps, "
-                                      "observations every 8th day, LAI propagator; device-resident rasters" % n_steps,
-                          "metric": "pixel-steps/sec", "value": N * n_steps / (ms * 1e-3), "ms_per_step": ms / n_steps,
-                          "pixel_dates_per_s": N * len(dates) / (ms * 1e-3), "iterations": kf.last_iterations,
-                          "advance_kernel": {"kernel": "advance_carry_kernel (propagate_information_filter_LAI)",
-                                             "ms_per_call": adv_ms, "algorithmic_bytes": adv_bytes,
-                                             "GBs": adv_bytes / (adv_ms * 1e-3) / 1e9,
-                                             "frac_of_hbm_peak": adv_bytes / (adv_ms * 1e-3) / 1e9 / hbm,
-                                             "note": "CUDA events around the python call: includes two output "
-                                                     "allocations and the launch"},
-                          "n_gpus": 1}))
-    else:
-        # configs[4]: batched update with SUPPLIED Jacobians, n_params x bands sweep at 4 M pixels
-        lib = _lib.get_lib()
-        n = 4_000_000
-        ld = padded(n)
-        gen = torch.Generator(device=device).manual_seed(3)
-        rows = []
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
-            os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
-        hbm = float(peaks.get("hbm_gbs", 6650.0))
-        c5_flags = _lib.SOLVE_PAIR if os.environ.get("KAFKA_C5_PAIR") else 0     # force the two-lanes-per-pixel kernel
-        for Pn in [int(v) for v in os.environ.get("KAFKA_C5_PARAMS", "2,4,7,10,12,16").split(",")]:
-            for Bn in (1, 4, 10, 13):
-                Lp = tri_count(Pn)
-                rnd = lambda r: torch.randn((r, ld), generator=gen, dtype=torch.float64, device=device)
-                J, h0, y = [rnd(Pn) for _ in range(Bn)], [rnd(1) for _ in range(Bn)], [rnd(1) for _ in range(Bn)]
+        hbm, _ = _hbm_peak()
+        emit(json.dumps({
+            "workload": "c3: MODIS tile %dx%d (%.2f M px) per GPU, TIP P=7, B=2 (D=4, T=500), %d daily steps, "
+                        "observations every 8th day (%d dates), LAI propagator with Q[6::7]=0.04; one "
+                        "LinearKalman.run(): host rasters in on observation days (%s), float32 mean/uncertainty "
+                        "rasters read back EVERY day" % (ny, nx, N / 1e6, n_steps, len(dates), args.host_sources),
+            "metric": "pixel-steps/sec", "value": world * N * n_steps / (ms * 1e-3), "unit": "pixel-steps/s",
+            "n_gpus": world, "scaling": "weak", "ms_per_run": ms, "ms_per_step": ms / n_steps,
+            "pixel_dates_per_s": world * N * len(dates) / (ms * 1e-3), "iterations": iters,
+            "h2d_bytes_per_run": kf._stager.h2d_bytes - h2d0, "d2h_bytes_per_run": out.d2h_bytes - d2h0,
+            "d2h_gbs_per_rank": (out.d2h_bytes - d2h0) / (ms * 1e-3) / 1e9,
+            "advance_algorithmic_bytes_per_step": adv_bytes, "clocks": clocks, "parity": parity}))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+C5_BANDS = (1, 4, 10, 13)
+
+
+def _c5_cpu_arm(params, bands, procs):
+    """Arm (B) beside the sweep: the UNMODIFIED variational_kalman_multiband (kafka/inference/solvers.py:100-145:
+    sparse build, float32 cast, SuperLU) with supplied Jacobians, on chunks of 128 x 128 px (<= 256^2), three
+    chunks on one core and one chunk per core on all cores; the rate per pixel is what the sweep's pixel
+    counts are extrapolated with."""
+    import multiprocessing as mp
+    _single_thread_env()
+    rows = []
+    with mp.get_context("spawn").Pool(procs) as pool:
+        pool.map(_c5_cpu_chunk, [(2, 1, 8, 0)] * procs)            # imports, outside the timing
+        for Pn in params:
+            for Bn in bands:
+                one = [pool.apply(_c5_cpu_chunk, ((Pn, Bn, 128, k),)) for k in range(3)]
+                t0 = time.perf_counter()
+                allc = pool.map(_c5_cpu_chunk, [(Pn, Bn, 128, 10 + k) for k in range(procs)], chunksize=1)
+                wall = time.perf_counter() - t0
+                rows.append({"n_params": Pn, "n_bands": Bn, "chunk_px": 128 * 128,
+                             "px_per_s_one_core": 3 * 128 * 128 / sum(r[0] for r in one),
+                             "px_per_s_all_cores": procs * 128 * 128 / max(r[0] for r in allc), "cores": procs,
+                             "wall_s_all_cores": wall})
+    return rows
+
+
+def _c5_cpu_chunk(args):
+    Pn, Bn, side, seed = args
+    from oracle import ref_runner
+    return ref_runner.time_supplied_jacobian_solve(Pn, Bn, side, seed)
+
+
+def run_c5(args):
+    """BASELINE configs[4]: batched update with SUPPLIED Jacobians (the solve kernels alone), n_params 2-16 x
+    bands {1,4,10,13} x pixels 1e4..1e8 (or what fits in memory) per GPU; with --gpus N every rank solves its
+    own pixel range and the convergence norm is all-reduced after every launch, as do_all_bands does."""
+    import torch
+    import torch.distributed as dist
+    from kafka_inferenceengine_b200 import _lib
+    from kafka_inferenceengine_b200.device import padded, tri_count
+    world, rank, local, device, comm, barrier, max_over_ranks = _dist_setup(args)
+    lib = _lib.get_lib()
+    hbm, peak_src = _hbm_peak()
+    params = [int(v) for v in os.environ.get("KAFKA_C5_PARAMS", ",".join(str(k) for k in range(2, 17))).split(",")]
+    sizes = [int(float(v)) for v in os.environ.get("KAFKA_C5_PIXELS", "1e4,1e5,1e6,1e7,1e8").split(",")]
+    c5_flags = _lib.SOLVE_PAIR if os.environ.get("KAFKA_C5_PAIR") else 0     # force the two-lanes-per-pixel kernel
+    budget = float(os.environ.get("KAFKA_C5_MEM_GB", "120")) * 1e9
+    gen = torch.Generator(device=device).manual_seed(3 + rank)
+    sampler = ClockSampler(local) if rank == 0 else None
+    rows, parity_worst = [], 0.0
+    tot = torch.zeros(2, dtype=torch.float64, device=device)
+
+    def fill(t):
+        # one random plane per tensor, the others scaled and shifted copies of it: the kernel sees distinct
+        # addresses and values, generating them costs one pass of writes instead of a normal variate per element
+        base_ = torch.randn(t.shape[-1], generator=gen, dtype=torch.float64, device=device)
+        for k in range(t.shape[0]):
+            torch.mul(base_.roll(1 + 7 * k), 1.0 + 0.03 * k, out=t[k])
+        return t
+
+    for n_req in sizes:
+        for Pn in params:
+            Lp = tri_count(Pn)
+            for Bn in C5_BANDS:
+                bytes_pp = 16 * Pn + 8 * Pn * (Pn + 1) + 8 * Pn + Bn * 8 * (3 + Pn)   # x_f,x_prev,x ; Pinv in + A out ; bands
+                n = int(min(n_req, budget // bytes_pp // 1024 * 1024))
+                if n < n_req and any(r["n_params"] == Pn and r["n_bands"] == Bn and r["pixels"] == n for r in rows):
+                    continue                                   # the capped size was already measured
+                ld = padded(n)
+                J = [fill(torch.empty((Pn, ld), dtype=torch.float64, device=device)) for _ in range(Bn)]
+                h0 = [fill(torch.empty((1, ld), dtype=torch.float64, device=device)) for _ in range(Bn)]
+                y = [fill(torch.empty((1, ld), dtype=torch.float64, device=device)) for _ in range(Bn)]
                 w = [torch.full((1, ld), 400.0, dtype=torch.float64, device=device) for _ in range(Bn)]
-                xp, xf = rnd(Pn), rnd(Pn)
+                xp = fill(torch.empty((Pn, ld), dtype=torch.float64, device=device))
+                xf = fill(torch.empty((Pn, ld), dtype=torch.float64, device=device))
                 pinv = torch.zeros((Lp, ld), dtype=torch.float64, device=device)
                 r_, c_ = np.tril_indices(Pn)
                 for k in range(Lp):
@@ -559,21 +699,99 @@ def run_other_workload(args):
                         arr[b].mapper[k] = k
                     arr[b].jac, arr[b].h0, arr[b].y, arr[b].w = J[b].data_ptr(), h0[b].data_ptr(), y[b].data_ptr(), w[b].data_ptr()
                 xo, ao = torch.empty_like(xp), torch.empty_like(pinv)
-                n2 = torch.zeros(1, dtype=torch.float64, device=device)
-                nb = torch.zeros(1, dtype=torch.int32, device=device)
+                scal = torch.zeros(2, dtype=torch.float64, device=device)
+                n2, nb = scal[0:1], scal[1:2].view(torch.int32)[0:1]
                 scratch = torch.empty(int(lib.kafka_solve_scratch_doubles(n)), dtype=torch.float64, device=device)
 
                 def call():
                     _lib.check(lib.kafka_solve_bands(n, ld, Pn, arr, Bn, _lib.ptr(xp), _lib.ptr(xf), _lib.ptr(pinv),
                                                      _lib.ptr(xo), _lib.ptr(ao), None, None, _lib.ptr(n2), _lib.ptr(nb),
                                                      _lib.ptr(scratch), c5_flags, _lib.stream_ptr()), "kafka_solve_bands")
-                ms = timed(call, 5, 2)
-                bytes_pp = 16 * Pn + 8 * Pn * (Pn + 1) + 8 * Pn + Bn * 8 * (3 + Pn)     # x_f,x_prev,x ; Pinv in + A out ; bands
-                rows.append({"n_params": Pn, "n_bands": Bn, "ms": ms, "Mpx_per_s": n / ms / 1e3,
-                             "GBs": n * bytes_pp / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": n * bytes_pp / (ms * 1e-3) / 1e9 / hbm})
-                del J, h0, y, w, xp, xf, pinv, xo, ao
-        emit(json.dumps({"workload": "c5: batched update with supplied Jacobians, 4 M px, per-pixel prior blocks",
-                          "metric": "pixels/sec", "rows": rows, "n_gpus": 1}))
+                    if world > 1:                               # the global convergence norm of do_all_bands
+                        tot[0] = n2[0]
+                        tot[1] = float(n * Pn)
+                        if args.comm == "native":
+                            comm.all_reduce_sums(tot)
+                        else:
+                            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+                reps = 5 if n >= 100000 else 20
+                for _ in range(2):
+                    call()
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(reps):
+                    call()
+                e1.record()
+                barrier()
+                ms = max_over_ranks(e0.elapsed_time(e1) / reps)
+                if n_req == sizes[0] and rank == 0:
+                    # parity inside the sweep: the first 512 pixels against oracle B (fp64, dense blocks)
+                    from oracle import kafka_cpu as kc
+                    ns = min(512, n)
+                    Pm = np.zeros((ns, Pn, Pn))
+                    Pm[:, np.arange(Pn), np.arange(Pn)] = 4.0
+                    hx = lambda t: t[:, :ns].t().contiguous().cpu().numpy()
+                    xo_, Ao_, _, _ = kc.solve_dense64([hx(v)[:, 0] for v in y], [hx(v)[:, 0] for v in w],
+                                                      [hx(v)[:, 0] for v in h0], [hx(v) for v in J],
+                                                      hx(xp).ravel(), hx(xf).ravel(), Pm)
+                    got = hx(xo).ravel()
+                    err = float(np.max(np.abs(got - xo_) / np.maximum(np.abs(xo_), 1e-6 * np.abs(xo_).max())))
+                    assert err < 1e-6, (Pn, Bn, err)
+                    parity_worst = max(parity_worst, err)
+                rows.append({"pixels": n, "pixels_requested": n_req, "n_params": Pn, "n_bands": Bn, "ms": ms,
+                             "Mpx_per_s": world * n / ms / 1e3, "GBs_per_gpu": n * bytes_pp / (ms * 1e-3) / 1e9,
+                             "frac_of_hbm_peak": n * bytes_pp / (ms * 1e-3) / 1e9 / hbm})
+                del J, h0, y, w, xp, xf, pinv, xo, ao, scratch
+        torch.cuda.empty_cache()
+    clocks = sampler.stop() if sampler else None
+    if rank == 0:
+        line = {"workload": "c5: batched update with supplied Jacobians, per-pixel prior blocks: n_params %s x bands %s x "
+                            "pixels %s per GPU (capped at what fits %d GB)" % (params, list(C5_BANDS), sizes, budget / 1e9),
+                "metric": "pixels/sec", "n_gpus": world, "scaling": "weak", "hbm_peak": hbm, "peak_source": peak_src,
+                "algorithmic_bytes_per_pixel": "16P + 8P(P+1) + 8P + B*8*(3+P)", "rows": rows, "clocks": clocks,
+                "parity": {"checked": "first 512 pixels of every (n_params, bands) at the smallest size vs oracle B",
+                           "max_rel_err_x": parity_worst}}
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            cpu_params = [int(v) for v in os.environ.get("KAFKA_C5_CPU_PARAMS", "2,7,10,16").split(",")]
+            line["cpu_arm"] = {"what": "unmodified reference variational_kalman_multiband (scipy sparse build + float32 "
+                                       "SuperLU, kafka/inference/solvers.py:100-145), supplied Jacobians, chunks of 128x128 px; "
+                                       "rates per pixel, EXTRAPOLATED linearly to the sweep's pixel counts (SuperLU runs "
+                                       "out of memory at 1e6 px in one piece, SURVEY section 6)",
+                               "kind": "reference" if _reference_installed() else "unavailable",
+                               "rows": _c5_cpu_arm(cpu_params, C5_BANDS, min(cores, 64)) if _reference_installed() else []}
+        emit(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_other_workload(args):
+    if args.workload == "c3":
+        return run_c3(args)
+    if args.workload == "c5":
+        return run_c5(args)
+    import torch
+    torch.cuda.set_device(0)
+    emit(json.dumps(measure_c2(torch.device("cuda", 0), args.steps)))
+
+
+class HostObservationsGeneric(object):
+    """Host numpy rasters (float64 observations, float64 inverse-variance raster, bool mask) of any number
+    of bands, in page-locked or pageable memory."""
+
+    def __init__(self, dates, gps, rho, inv, mask, shape, pinned=True):
+        from kafka_inferenceengine_b200 import synthetic as syn
+        self.dates = list(dates)
+        nb = len(gps)
+        self.bands_per_observation = {d: nb for d in self.dates}
+        self._bands = [syn.BandData(_host_raster(rho[b], shape, np.float64, pinned),
+                                    _host_raster(inv[b], shape, np.float64, pinned),
+                                    _host_raster(mask[b] != 0, shape, np.bool_, pinned), {"band": b}, gps[b])
+                       for b in range(nb)]
+
+    def get_band_data(self, date, band):
+        return self._bands[band]
 
 
 class DeviceObservationsGeneric(object):
@@ -616,7 +834,7 @@ def main():
         # stdout carries exactly one JSON line: NCCL's own banner / debug lines go to stderr
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=device)
-        comm = dist.group.WORLD
+        comm = _make_comm(args, device)
 
     shape = (args.rows, args.cols)
     n_pix = args.rows * args.cols
@@ -861,6 +1079,9 @@ def main():
                                "and shared (reference: run_emulator single-unique-vector branch, utils.py:72-74); "
                                "later iterations evaluate every pixel",
             "value_without_shared_first_linearisation": world * n_pix / (ms_nodedup * 1e-3),
+            "collective": None if world == 1 else ("2-3 double NCCL all-reduce per solver iteration through %s"
+                                                   % ("the library's communicator (kafka_allreduce_norm)"
+                                                      if args.comm == "native" else "torch.distributed")),
             "clocks": clocks, "e2e": e2e, "e2e_raw_ingest": e2e_raw, "gpu_launches": launches, "roofline": roofline,
             "cpu_baseline": cpu}
     if world == 1 and not args.no_e2e and args.rows == SHARD_ROWS:

@@ -60,7 +60,8 @@ def main():
     comm = None
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
-        comm = dist.group.WORLD
+        from kafka_inferenceengine_b200.dist import NativeComm
+        comm = NativeComm.from_process_group(dist.group.WORLD, device)
     shape = (rows, bench.TILE)
     n_pix = rows * bench.TILE
     gps = bench.make_emulators()

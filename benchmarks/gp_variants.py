@@ -18,24 +18,29 @@ CSRC = os.path.join(ROOT, "kafka_inferenceengine_b200", "csrc")
 OUT = os.path.join(HERE, "variants")
 VARIANTS = {
     "default": [],
+    # round 2: what separates 73 % fp64-pipe activity from 100 %?
+    "rot": ["-DKAFKA_GP_ROTATE=1"],                                   # next row's operands fetched behind the G sums
+    "split": ["-DKAFKA_GP_SPLIT_DOT=1"],                              # two half-length dot-product chains per pixel
+    "split_rot": ["-DKAFKA_GP_SPLIT_DOT=1", "-DKAFKA_GP_ROTATE=1"],
+    "insfirst": ["-DKAFKA_EXP_INSERT_FIRST=1"],                       # exponent + sign into the table value, before the multiply
+    "prehead": ["-DKAFKA_GP_PREFETCH_HEAD=1"],                        # {e2, sgn, zh[0..1]} of the next row fetched a trip early
+    "insfirst_prehead": ["-DKAFKA_EXP_INSERT_FIRST=1", "-DKAFKA_GP_PREFETCH_HEAD=1"],
+    "ppt3_mb3": ["-DKAFKA_GP_PPT_BIG=3", "-DKAFKA_GP_MINBLOCKS=3"],
+    "tab256": ["-DKAFKA_EXP_LOG2N=8"],
+    "repl256": ["-DKAFKA_EXP_LOG2N=8", "-DKAFKA_EXP_REPL=16"],        # conflict-free 2^(k/256) look-ups, degree 4
+    "ppt1_mb5": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=5"],  # one pixel per thread, 20 warps per SM
+    "ppt1_mb5_split": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=5", "-DKAFKA_GP_SPLIT_DOT=1"],
+    "ppt1_mb6": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=6"],
+    "ppt1_mb4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=4"],
+    # round 1 (kept for the record; see DESIGN.md section 3.1 for their results)
     "tab64": ["-DKAFKA_EXP_LOG2N=6"],
     "f2i": ["-DKAFKA_EXP_F2I=1"],
-    "u1": ["-DKAFKA_GP_UNROLL=1"],
     "u4": ["-DKAFKA_GP_UNROLL=4"],
-    "ppt1_u4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_UNROLL=4"],
     "t256": ["-DKAFKA_GP_THREADS=256"],
-    "tab256_checked": ["-DKAFKA_EXP_CLAMP=0", "-DKAFKA_EXP_LOG2N=8"],
-    "tab256": ["-DKAFKA_EXP_LOG2N=8"],
     "checked": ["-DKAFKA_EXP_CLAMP=0"],
     "u1_mb4": ["-DKAFKA_GP_UNROLL=1", "-DKAFKA_GP_MINBLOCKS=4"],
-    "u2_mb4": ["-DKAFKA_GP_UNROLL=2", "-DKAFKA_GP_MINBLOCKS=4"],
-    "u4_mb4": ["-DKAFKA_GP_UNROLL=4", "-DKAFKA_GP_MINBLOCKS=4"],
-    "u8": ["-DKAFKA_GP_UNROLL=8"],
-    "u5": ["-DKAFKA_GP_UNROLL=5"],
     "ppt3": ["-DKAFKA_GP_PPT_BIG=3"],
-    "ppt3_t96": ["-DKAFKA_GP_PPT_BIG=3", "-DKAFKA_GP_THREADS=96"],
     "ppt4": ["-DKAFKA_GP_PPT_BIG=4"],
-    "ppt4_t64": ["-DKAFKA_GP_PPT_BIG=4", "-DKAFKA_GP_THREADS=64"],
 }
 if os.environ.get("KAFKA_GP_VARIANTS"):
     VARIANTS = {k: v for k, v in VARIANTS.items() if k in os.environ["KAFKA_GP_VARIANTS"].split(",")}
@@ -46,12 +51,17 @@ def build():
     procs = []
     for name, flags in VARIANTS.items():
         cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler",
-               "-fPIC", "--expt-relaxed-constexpr", "-shared", "-o", os.path.join(OUT, name + ".so"),
+               "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v", "-shared", "-o", os.path.join(OUT, name + ".so"),
                os.path.join(CSRC, "layout.cu"), os.path.join(CSRC, "gp.cu")] + flags
         procs.append((name, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
     for name, p in procs:
         out = p.communicate()[0].decode()
+        lines = out.splitlines()
+        info = [lines[k + 2].strip() + " | " + lines[k + 1].strip() for k, l in enumerate(lines)
+                if "gp_linearize_kernelILi10ELi" in l and "Compiling" in l and k + 2 < len(lines)]
         print(name, "ok" if p.returncode == 0 else "FAILED\n" + out)
+        for i in info:
+            print("    ", i)
 
 
 def run():

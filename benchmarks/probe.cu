@@ -56,7 +56,56 @@ __global__ void __launch_bounds__(128) planar_stream_probe(const double* __restr
     for (int w = 0; w < W; ++w) __stcs(out + (long long)w * ld + i, acc + w);
 }
 
+// Dependent-issue latency of DFMA: one CTA per SM, `warps` warps per scheduler, CH independent
+// chains per thread; clock64 around a long run of dependent FMAs.  cycles / (steps) = how often a
+// warp can issue the next FMA of ONE chain set, i.e. max(latency, CH * 2 * warps-sharing-the-pipe).
+template <int CH>
+__global__ void dfma_latency_probe(double* out, long long* cycles, int iters, double a, double b) {
+    double v[CH];
+#pragma unroll
+    for (int c = 0; c < CH; ++c) v[c] = threadIdx.x * 1e-9 + c * 1e-3;
+    __syncthreads();
+    long long t0 = clock64();
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 32; ++k)
+#pragma unroll
+            for (int c = 0; c < CH; ++c) v[c] = fma(v[c], a, b);
+    }
+    long long t1 = clock64();
+    double s = 0;
+#pragma unroll
+    for (int c = 0; c < CH; ++c) s += v[c];
+    if (s == 123.456) out[0] = s;
+    if (threadIdx.x == 0 && blockIdx.x == 0) cycles[0] = t1 - t0;
+}
+
 extern "C" {
+// cycles between successive dependent steps of a thread's CH chains with `warps` warps per scheduler
+double kafka_probe_dfma_step_cycles(int chains, int warps) {
+    double* out = nullptr;
+    long long* cyc = nullptr;
+    if (cudaMalloc(&out, 8) != cudaSuccess || cudaMalloc(&cyc, 8) != cudaSuccess) return -1.0;
+    const int iters = 2000, threads = 128 * warps;
+    for (int rep = 0; rep < 2; ++rep) {
+        switch (chains) {
+            case 1: dfma_latency_probe<1><<<1, threads>>>(out, cyc, iters, 0.999999, 1e-7); break;
+            case 2: dfma_latency_probe<2><<<1, threads>>>(out, cyc, iters, 0.999999, 1e-7); break;
+            case 3: dfma_latency_probe<3><<<1, threads>>>(out, cyc, iters, 0.999999, 1e-7); break;
+            case 4: dfma_latency_probe<4><<<1, threads>>>(out, cyc, iters, 0.999999, 1e-7); break;
+            case 6: dfma_latency_probe<6><<<1, threads>>>(out, cyc, iters, 0.999999, 1e-7); break;
+            case 8: dfma_latency_probe<8><<<1, threads>>>(out, cyc, iters, 0.999999, 1e-7); break;
+            default: return -2.0;
+        }
+        if (cudaDeviceSynchronize() != cudaSuccess) return -1.0;
+    }
+    long long h = 0;
+    cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
+    cudaFree(out);
+    cudaFree(cyc);
+    return (double)h / ((double)iters * 32);
+}
+
 double kafka_probe_planar_stream_gbs(long long n, int R, int W, int reps) {
     double *in = nullptr, *out = nullptr;
     long long ld = n;

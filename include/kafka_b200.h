@@ -361,6 +361,38 @@ int kafka_blend_prior(const double* prior_mean, const double* prior_inv, const d
                       const double* pinv_f, int64_t ld, int64_t n_pix, int n_params, double* x_out,
                       double* c_out, int32_t* n_bad, uint32_t flags, void* stream);
 
+/* ---- e: multi-GPU (one process per GPU, the image sharded by pixel) --------
+ * Replaces the reference's fan-out of chunks over dask workers
+ * (kafka_test_Py36.py:241-255: client.map(wrapper, chunks) + gather) for a binder
+ * that has no torch.distributed: an opaque per-rank context holding an NCCL
+ * communicator over NVLink.  Pixels never talk to each other; the one coupling
+ * is the scalar convergence norm of kafka/linear_kf.py:293, which the reference
+ * computes per chunk and which here is made global by one small all-reduce per
+ * iteration.  libnccl.so.2 is opened when the first context is created (the copy
+ * already loaded in the process if there is one); status codes >= 1000 are
+ * 1000 + ncclResult_t.
+ *
+ * kafka_comm_unique_id   rank 0 fills id128_host (KAFKA_COMM_ID_BYTES bytes) and hands it to
+ *                        the other ranks by whatever means the host application has
+ * kafka_ctx_create       collective over all ranks; the communicator is bound to the CUDA
+ *                        device that is current in the calling thread
+ * kafka_allreduce_norm   in-place SUM over ranks of `count` doubles on the device, queued on
+ *                        `stream`: [sum of squares of the step, element count, bad pixels]
+ *                        as kafka_solve_bands leaves them -> every rank forms
+ *                        sqrt(sums[0]) / sums[1] and takes the same stop decision
+ * kafka_gather_outputs   concatenation, in rank order, of every rank's `counts_host[rank]`
+ *                        doubles (state planes, diag(P^-1), ...) into recv on every rank:
+ *                        the final output gather; shards may differ in size */
+#define KAFKA_COMM_ID_BYTES 128
+typedef struct kafka_ctx kafka_ctx;
+int kafka_comm_unique_id(void* id128_host);
+int kafka_ctx_create(int rank, int n_ranks, const void* id128_host, kafka_ctx** ctx);
+int kafka_ctx_destroy(kafka_ctx* ctx);
+int kafka_ctx_info(const kafka_ctx* ctx, int* rank, int* n_ranks, int* nccl_version);
+int kafka_allreduce_norm(kafka_ctx* ctx, double* sums, int count, void* stream);
+int kafka_gather_outputs(kafka_ctx* ctx, const double* send, const int64_t* counts_host, double* recv,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,6 +22,7 @@ RAW_I16, RAW_U16, RAW_F32, RAW_F64 = 0, 1, 2, 3
 ROUND_F32 = 1
 PRIOR_BROADCAST = 2
 SOLVE_PAIR = 4
+COMM_ID_BYTES = 128
 STATIC_SCRATCH_DOUBLES = 262144
 STATIC_MAX_PIXELS = 16777088
 
@@ -81,6 +82,12 @@ SIGNATURES = {
     "kafka_advance_exact": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p, _p]),
     "kafka_advance_standard": (C.c_int, [_p, _p, _p, _p, _i64, _i64, _i32, _p, _p, _p]),
     "kafka_blend_prior": (C.c_int, [_p, _p, _p, _p, _i64, _i64, _i32, _p, _p, _p, _u32, _p]),
+    "kafka_comm_unique_id": (C.c_int, [_p]),
+    "kafka_ctx_create": (C.c_int, [_i32, _i32, _p, C.POINTER(C.c_void_p)]),
+    "kafka_ctx_destroy": (C.c_int, [_p]),
+    "kafka_ctx_info": (C.c_int, [_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "kafka_allreduce_norm": (C.c_int, [_p, _p, _i32, _p]),
+    "kafka_gather_outputs": (C.c_int, [_p, _p, C.POINTER(C.c_int64), _p, _p]),
 }
 
 _lib = None
@@ -107,7 +114,10 @@ def get_lib():
 # kernels launched by one successful call of each entry point (for bench.py's
 # gpu_launches count; the set of kernels is in csrc/*.cu)
 KERNELS_PER_CALL = {"kafka_compact_mask": 3, "kafka_solve_bands": 2, "kafka_solve_bands_static": 3,
-                    "kafka_assimilate_iter": 3}
+                    "kafka_assimilate_iter": 3,
+                    # NCCL's kernels, not this library's
+                    "kafka_comm_unique_id": 0, "kafka_ctx_create": 0, "kafka_ctx_destroy": 0, "kafka_ctx_info": 0,
+                    "kafka_allreduce_norm": 0, "kafka_gather_outputs": 0}
 launch_count = 0
 
 

@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libkafka_b200.so")
-SOURCES = ["layout.cu", "gp.cu", "solve.cu", "advance.cu", "assimilate.cu", "noalloc.cu"]
+SOURCES = ["layout.cu", "gp.cu", "solve.cu", "advance.cu", "assimilate.cu", "noalloc.cu", "comm.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
@@ -55,7 +55,8 @@ def build_library(force=False, verbose=False):
     if verbose:
         for _, log in results:
             sys.stderr.write(log)
-    cmd = [_nvcc()] + ARCH + ["-shared", "-o", LIB] + [o for o, _ in results] + ["-lcudart"]
+    # NCCL is opened at run time by comm.cu (dlopen), not linked
+    cmd = [_nvcc()] + ARCH + ["-shared", "-o", LIB] + [o for o, _ in results] + ["-lcudart", "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))

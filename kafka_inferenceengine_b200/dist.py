@@ -44,6 +44,81 @@ def shard_pixels(n_pix, rank, world_size):
     return i0, min(n_pix, i0 + per)
 
 
+class NativeComm(object):
+    """The multi-GPU step behind the C ABI (include/kafka_b200.h: kafka_ctx_create,
+    kafka_allreduce_norm, kafka_gather_outputs): an NCCL communicator owned by
+    libkafka_b200.so, one rank per GPU, usable by a binder that has no
+    torch.distributed.  ``LinearKalman(comm=NativeComm(...))`` then takes its
+    convergence all-reduce through it.
+
+    ``NativeComm(rank, n_ranks, unique_id, device)`` is collective; ``unique_id``
+    is the KAFKA_COMM_ID_BYTES blob rank 0 got from ``NativeComm.unique_id()`` and
+    passed to the others by any means (``from_process_group`` uses
+    torch.distributed for exactly that and nothing else)."""
+
+    def __init__(self, rank, n_ranks, unique_id, device=None):
+        import ctypes as C
+        from . import _lib
+        self._lib = _lib
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.rank, self.n_ranks = int(rank), int(n_ranks)
+        if len(unique_id) != _lib.COMM_ID_BYTES:
+            raise ValueError("unique_id must be %d bytes" % _lib.COMM_ID_BYTES)
+        buf = C.create_string_buffer(bytes(unique_id), _lib.COMM_ID_BYTES)
+        ctx = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.get_lib().kafka_ctx_create(self.rank, self.n_ranks, buf, C.byref(ctx)), "kafka_ctx_create")
+        self._ctx = ctx
+
+    @staticmethod
+    def unique_id():
+        import ctypes as C
+        from . import _lib
+        buf = C.create_string_buffer(_lib.COMM_ID_BYTES)
+        _lib.check(_lib.get_lib().kafka_comm_unique_id(buf), "kafka_comm_unique_id")
+        return buf.raw
+
+    @classmethod
+    def from_process_group(cls, group=None, device=None):
+        """One NativeComm per rank of an initialised torch.distributed group (which only
+        carries the unique id from rank 0 to the others)."""
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        box = [cls.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        return cls(rank, world, box[0], device)
+
+    def all_reduce_sums(self, sums):
+        """In-place SUM over ranks of a small contiguous float64 CUDA tensor, on the current stream."""
+        if not (sums.is_cuda and sums.dtype == torch.float64 and sums.is_contiguous()):
+            raise ValueError("all_reduce_sums needs a contiguous float64 CUDA tensor")
+        with torch.cuda.device(self.device):
+            self._lib.check(self._lib.get_lib().kafka_allreduce_norm(self._ctx, self._lib.ptr(sums), sums.numel(),
+                                                                     self._lib.stream_ptr()), "kafka_allreduce_norm")
+        return sums
+
+    def gather(self, local, counts):
+        """Concatenation in rank order of every rank's 1-D float64 CUDA tensor (``counts[r]``
+        elements from rank r) on every rank."""
+        import ctypes as C
+        counts = [int(c) for c in counts]
+        if len(counts) != self.n_ranks or counts[self.rank] != local.numel():
+            raise ValueError("counts must list every rank's element count")
+        local = local.contiguous()
+        out = torch.empty(sum(counts), dtype=torch.float64, device=self.device)
+        arr = (C.c_int64 * self.n_ranks)(*counts)
+        with torch.cuda.device(self.device):
+            self._lib.check(self._lib.get_lib().kafka_gather_outputs(self._ctx, self._lib.ptr(local), arr,
+                                                                     self._lib.ptr(out), self._lib.stream_ptr()),
+                            "kafka_gather_outputs")
+        return out
+
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            ctx, self._ctx = self._ctx, None
+            self._lib.check(self._lib.get_lib().kafka_ctx_destroy(ctx), "kafka_ctx_destroy")
+
+
 def global_norm(sum_sq_local, n_elems_local, comm=None, n_bad_local=None):
     """``(sqrt(sum of squares over all ranks) / total element count)`` and the
     total count.  ``sum_sq_local`` may be a python float or a 0-d/1-element
@@ -51,6 +126,20 @@ def global_norm(sum_sq_local, n_elems_local, comm=None, n_bad_local=None):
     of the solve rides in the same all-reduce and its total is returned as a
     third value."""
     import torch.distributed as dist
+    if isinstance(comm, NativeComm):
+        from . import _lib
+        dev = comm.device
+        parts = [sum_sq_local.reshape(-1)[0].to(device=dev, dtype=torch.float64)
+                 if isinstance(sum_sq_local, torch.Tensor) else torch.tensor(float(sum_sq_local), dtype=torch.float64, device=dev),
+                 torch.tensor(float(n_elems_local), dtype=torch.float64, device=dev)]
+        if n_bad_local is not None:
+            parts.append(n_bad_local.reshape(-1)[0].to(device=dev, dtype=torch.float64) if isinstance(n_bad_local, torch.Tensor)
+                         else torch.tensor(float(n_bad_local), dtype=torch.float64, device=dev))
+        buf = comm.all_reduce_sums(torch.stack(parts))
+        with torch.cuda.device(dev):
+            tot = _lib.read_small(buf)
+        res = (float(np.sqrt(tot[0]) / tot[1]), float(tot[1]))
+        return res if n_bad_local is None else res + (int(round(float(tot[2]))),)
     if comm is None and not (dist.is_available() and dist.is_initialized()):
         s = float(sum_sq_local)
         res = (np.sqrt(s) / float(n_elems_local), float(n_elems_local))
@@ -83,6 +172,11 @@ def global_norm(sum_sq_local, n_elems_local, comm=None, n_bad_local=None):
 def gather_interleaved(x_local, comm=None, dst=None):
     """Concatenate per-rank 1-D tensors in rank order (all ranks, or only ``dst``)."""
     import torch.distributed as dist
+    if isinstance(comm, NativeComm):
+        cnt = torch.zeros(comm.n_ranks, dtype=torch.float64, device=comm.device)
+        cnt[comm.rank] = float(x_local.numel())
+        counts = [int(c) for c in comm.all_reduce_sums(cnt).cpu().tolist()]
+        return comm.gather(x_local.to(device=comm.device, dtype=torch.float64).reshape(-1), counts)
     if comm is None and not (dist.is_available() and dist.is_initialized()):
         return x_local
     world = dist.get_world_size(comm)

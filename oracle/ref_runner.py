@@ -112,3 +112,33 @@ class _IterCounter(logging.Handler):
     def emit(self, record):
         if "convergence norm" in record.getMessage():
             self.n += 1
+
+
+def time_supplied_jacobian_solve(n_params, n_bands, side, seed):
+    """BASELINE configs[4]'s CPU arm: the unmodified variational_kalman_multiband on one chunk of
+    ``side x side`` pixels with SUPPLIED random Jacobians in the solver's (H0, H csr) tuple form
+    (J ~ N(0,1), inverse variance 400, P_f^-1 = 4 I; the synthetic inputs of SURVEY section 8d).
+    Returns (seconds, pixels)."""
+    kafka = reference()
+    rng = np.random.default_rng(seed)
+    n = side * side
+    P = n_params
+    state_mask = np.ones((side, side), dtype=bool)
+    indptr = np.arange(0, (n + 1) * P, P)
+    indices = np.arange(n * P)
+    Hs, obs, unc, masks = [], [], [], []
+    for _ in range(n_bands):
+        J = rng.standard_normal((n, P)).astype(np.float32)
+        Hs.append((rng.standard_normal(n).astype(np.float32), sp.csr_matrix((J.ravel(), indices, indptr), shape=(n, n * P))))
+        obs.append(rng.standard_normal((side, side)))
+        unc.append(sp.diags(np.full(n, 400.0), format="csr"))
+        masks.append(state_mask)
+    x_lin = rng.standard_normal(n * P)
+    x_f = rng.standard_normal(n * P)
+    Pinv = sp.diags(np.full(n * P, 4.0), format="csr").astype(np.float32)
+    t0 = time.perf_counter()
+    x, _, A, innov, fwd = kafka.inference.solvers.variational_kalman_multiband(
+        obs, masks, state_mask, unc, Hs, P, x_lin, x_f, None, Pinv, None)
+    dt_ = time.perf_counter() - t0
+    assert np.all(np.isfinite(x)) and x.shape == (n * P,)
+    return dt_, n
