@@ -657,7 +657,8 @@ def run_c5(args):
     hbm, peak_src = _hbm_peak()
     params = [int(v) for v in os.environ.get("KAFKA_C5_PARAMS", ",".join(str(k) for k in range(2, 17))).split(",")]
     sizes = [int(float(v)) for v in os.environ.get("KAFKA_C5_PIXELS", "1e4,1e5,1e6,1e7,1e8").split(",")]
-    c5_flags = _lib.SOLVE_PAIR if os.environ.get("KAFKA_C5_PAIR") else 0     # force the two-lanes-per-pixel kernel
+    # KAFKA_C5_FLAGS: kafka_solve_bands flags, e.g. 4 / 8 to force the two- / four-lanes-per-pixel kernel
+    c5_flags = int(os.environ.get("KAFKA_C5_FLAGS", "0")) | (_lib.SOLVE_PAIR if os.environ.get("KAFKA_C5_PAIR") else 0)
     budget = float(os.environ.get("KAFKA_C5_MEM_GB", "120")) * 1e9
     gen = torch.Generator(device=device).manual_seed(3 + rank)
     sampler = ClockSampler(local) if rank == 0 else None

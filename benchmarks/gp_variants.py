@@ -33,8 +33,6 @@ VARIANTS = {
     "ppt1_mb6": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=6"],
     "ppt1_mb4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=4"],
     # round 1 (kept for the record; see DESIGN.md section 3.1 for their results)
-    "tab64": ["-DKAFKA_EXP_LOG2N=6"],
-    "f2i": ["-DKAFKA_EXP_F2I=1"],
     "u4": ["-DKAFKA_GP_UNROLL=4"],
     "t256": ["-DKAFKA_GP_THREADS=256"],
     "checked": ["-DKAFKA_EXP_CLAMP=0"],

@@ -67,7 +67,9 @@ extern "C" {
                                    (kafka/inference/utils.py:193-195)                  */
 #define KAFKA_PRIOR_BROADCAST 2u /* pinv_f is ONE packed block shared by all pixels    */
 #define KAFKA_SOLVE_PAIR 4u       /* kafka_solve_bands: use the two-lanes-per-pixel kernel at any size
-                                    (it is the default at 16 parameters; for tests) */
+                                    (default from 14 parameters when a band is LINEAR or WCM; for tests) */
+#define KAFKA_SOLVE_QUAD 8u       /* kafka_solve_bands: use the four-lanes-per-pixel kernel at any size
+                                    (default from 13 parameters for array / shared-linearisation bands; for tests) */
 
 const char* kafka_last_error(void);
 int kafka_version(void);
@@ -293,6 +295,36 @@ int kafka_assimilate_iter(int64_t n_pix, int64_t ld, int n_params, const kafka_g
                           double* h0_work, double* jac_work, double* x_out, double* a_out,
                           double* innovations, double* fwd, double* norm2, int32_t* n_bad,
                           double* scratch, uint32_t flags, void* stream);
+
+/* The whole of LinearKalman.do_all_bands (kafka/linear_kf.py:245-323) for one date when every
+ * band is a GP emulator: kafka_assimilate_iter in the reference's loop with the reference's
+ * stop rule (norm = ||x - x_prev||_2 / len(x) < tol and n_iter >= min_iterations, or the 26th
+ * solve; linear_kf.py:293-304), for images so small that per-call overhead is all there is.
+ * x_work: [2][n_params*ld] doubles, the iterates ping-pong between the halves and *x_index
+ * says which holds the analysis; scalars: 2 doubles on the device; pinned_host16: 16 bytes of
+ * page-locked host memory (the per-iteration sum of squares and bad-pixel count land there);
+ * norms_host: >= 26 doubles, one norm per solve; *n_solves = solves taken; *n_bad_last /
+ * *n_bad_max = pixels left at the forecast in the last / the worst iteration.  a_out,
+ * innovations and fwd (may be NULL) are written by iterations that can be the last one.
+ * x_uniform (may be NULL): n_params contiguous doubles on the device -- the state shared by ALL
+ * pixels of x_f (e.g. after a prior reset); the first iteration then evaluates the emulators once
+ * for that vector, the reference's single-unique-vector branch (kafka/inference/utils.py:72-74).
+ * Synchronises `stream` once per iteration. */
+int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, const kafka_gp_band* gp_bands_host,
+                          int n_bands, const double* y, const double* w, const uint8_t* obs_mask,
+                          const double* x_f, const double* pinv_f, double* h0_work, double* jac_work,
+                          double* x_work, double* a_out, double* innovations, double* fwd,
+                          double* scalars, void* pinned_host16, double* scratch, double tol,
+                          int min_iterations, uint32_t flags, void* stream, double* norms_host,
+                          int* n_solves, int* n_bad_last, int* n_bad_max, int* x_index,
+                          const double* x_uniform);
+
+/* n host->device copies queued on `stream` by one call: the upload of one date's rasters
+ * (observations.get_band_data, kafka/linear_kf.py:225-227, hands over three rasters per band) for
+ * images so small that the cost per copy call rivals the transfer.  src_host[k] should be
+ * page-locked (then the copies are asynchronous). */
+int kafka_upload_rasters(int n, const void* const* src_host, void* const* dst_dev, const int64_t* n_bytes,
+                         void* stream);
 
 /* Same update as kafka_solve_bands for callers that cannot allocate device memory
  * and therefore cannot pass `scratch`.  It has no counterpart in the reference

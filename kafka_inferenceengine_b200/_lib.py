@@ -22,6 +22,7 @@ RAW_I16, RAW_U16, RAW_F32, RAW_F64 = 0, 1, 2, 3
 ROUND_F32 = 1
 PRIOR_BROADCAST = 2
 SOLVE_PAIR = 4
+SOLVE_QUAD = 8
 COMM_ID_BYTES = 128
 STATIC_SCRATCH_DOUBLES = 262144
 STATIC_MAX_PIXELS = 16777088
@@ -76,6 +77,9 @@ SIGNATURES = {
                                            _p, _p, _u32, _p]),
     "kafka_assimilate_iter": (C.c_int, [_i64, _i64, _i32, C.POINTER(GpBand), _i32, _p, _p, _p, _p, _p, _p, _p, _p,
                                         _p, _p, _p, _p, _p, _p, _p, _u32, _p]),
+    "kafka_assimilate_date": (C.c_int, [_i64, _i64, _i32, C.POINTER(GpBand), _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p,
+                                        _p, _p, _p, _p, C.c_double, _i32, _u32, _p, _p, _p, _p, _p, _p, _p]),
+    "kafka_upload_rasters": (C.c_int, [_i32, _p, _p, _p, _p]),
     "kafka_wcm_forward": (C.c_int, [_p, _i64, _i64, _p, _p, _p, _p]),
     "kafka_advance_carry_slot": (C.c_int, [_p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _p, _p, _p]),
     "kafka_advance_approx": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _p]),
@@ -114,7 +118,7 @@ def get_lib():
 # kernels launched by one successful call of each entry point (for bench.py's
 # gpu_launches count; the set of kernels is in csrc/*.cu)
 KERNELS_PER_CALL = {"kafka_compact_mask": 3, "kafka_solve_bands": 2, "kafka_solve_bands_static": 3,
-                    "kafka_assimilate_iter": 3,
+                    "kafka_assimilate_iter": 3, "kafka_assimilate_date": 0, "kafka_upload_rasters": 0,     # counted by the caller: 4 per solve
                     # NCCL's kernels, not this library's
                     "kafka_comm_unique_id": 0, "kafka_ctx_create": 0, "kafka_ctx_destroy": 0, "kafka_ctx_info": 0,
                     "kafka_allreduce_norm": 0, "kafka_gather_outputs": 0}

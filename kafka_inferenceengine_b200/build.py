@@ -28,17 +28,27 @@ def _sources():
     return [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
 
 
-def _stale():
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".inc"))]
+def _headers():
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".inc"))]
     deps.append(os.path.join(os.path.dirname(HERE), "include", "kafka_b200.h"))
-    return any(os.path.getmtime(d) > t for d in deps)
+    return deps
+
+
+def _obj(src):
+    return os.path.join(CSRC, "build", src.replace(".cu", ".o"))
+
+
+def _object_stale(src):
+    """An object is rebuilt when its own source or any shared header is newer than it."""
+    obj = _obj(src)
+    if not os.path.exists(obj):
+        return True
+    t = os.path.getmtime(obj)
+    return any(os.path.getmtime(d) > t for d in [os.path.join(CSRC, src)] + _headers())
 
 
 def _compile(src, verbose):
-    obj = os.path.join(CSRC, "build", src.replace(".cu", ".o"))
+    obj = _obj(src)
     cmd = [_nvcc()] + ARCH + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
@@ -47,16 +57,17 @@ def _compile(src, verbose):
 
 
 def build_library(force=False, verbose=False):
-    if not force and not _stale():
-        return LIB
     os.makedirs(os.path.join(CSRC, "build"), exist_ok=True)
-    with concurrent.futures.ThreadPoolExecutor(max_workers=len(_sources())) as ex:
-        results = list(ex.map(lambda s: _compile(s, verbose), _sources()))
+    todo = [s for s in _sources() if force or _object_stale(s)]
+    if not todo and os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(_obj(s)) for s in _sources()):
+        return LIB
+    with concurrent.futures.ThreadPoolExecutor(max_workers=max(1, len(todo))) as ex:
+        results = list(ex.map(lambda s: _compile(s, verbose), todo))
     if verbose:
         for _, log in results:
             sys.stderr.write(log)
     # NCCL is opened at run time by comm.cu (dlopen), not linked
-    cmd = [_nvcc()] + ARCH + ["-shared", "-o", LIB] + [o for o, _ in results] + ["-lcudart", "-ldl"]
+    cmd = [_nvcc()] + ARCH + ["-shared", "-o", LIB] + [_obj(s) for s in _sources()] + ["-lcudart", "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))

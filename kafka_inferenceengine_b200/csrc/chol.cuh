@@ -112,6 +112,13 @@ __device__ __forceinline__ void symv(const double (&S)[tri_count(P)], const doub
     symv_blk<P>(reinterpret_cast<const RegBlock<tri_count(P)>&>(S), x, y);
 }
 
+#ifdef KAFKA_DEV_ONLY_P      /* development builds: instantiate one state size only (fast compile, SASS inspection) */
+#define KAFKA_DISPATCH_P(P_, ...) \
+    switch (P_) { \
+        case KAFKA_DEV_ONLY_P: { constexpr int kP = KAFKA_DEV_ONLY_P; __VA_ARGS__; } break; \
+        default: break; \
+    }
+#else
 #define KAFKA_DISPATCH_P(P_, ...) \
     switch (P_) { \
         case 1: { constexpr int kP = 1; __VA_ARGS__; } break; \
@@ -132,5 +139,6 @@ __device__ __forceinline__ void symv(const double (&S)[tri_count(P)], const doub
         case 16: { constexpr int kP = 16; __VA_ARGS__; } break; \
         default: break; \
     }
+#endif
 
 }  // namespace kafka

@@ -26,18 +26,18 @@
 
 namespace kafka {
 
-// exponent granularity: 2^(1/64) (64-entry table + degree-5 polynomial), 2^(1/256)
-// (256 entries + degree 4) or 2^(1/1024) (1024 entries + degree 3): one DFMA fewer per
-// evaluation with every step
+// exponent granularity: 2^(1/1024) (1024-entry table + degree-3 polynomial).  benchmarks/gp_variants.py
+// can still build the 256-entry / degree-4 variant (KAFKA_EXP_LOG2N=8, table under benchmarks/exp_tables/):
+// on B200 it is 6 % slower, and the 64-entry / degree-5 one measured in round 1 another 4.5 %.
 #ifndef KAFKA_EXP_LOG2N
-#define KAFKA_EXP_LOG2N 10  // B200, benchmarks/gp_variants.py: 8 is 4.5 % faster than 6, 10 another 1.6 %
+#define KAFKA_EXP_LOG2N 10
+#endif
+#if KAFKA_EXP_LOG2N != 10 && KAFKA_EXP_LOG2N != 8
+#error "KAFKA_EXP_LOG2N must be 10 (product) or 8 (benchmark variant)"
 #endif
 // unchecked exponent insert in the hot loop (see exp_scaled); with LOG2N 10: 5.3 % faster than 8 + checked
 #ifndef KAFKA_EXP_CLAMP
 #define KAFKA_EXP_CLAMP 1
-#endif
-#ifndef KAFKA_EXP_F2I
-#define KAFKA_EXP_F2I 0
 #endif
 // copies of the 2^(k/N) table in shared memory, interleaved entry-major: lane l reads copy l mod R, so
 // with R = 16 the 16 lanes of a half-warp always hit 16 different bank pairs (no replays whatever the
@@ -61,10 +61,8 @@ constexpr int kExpRepl = KAFKA_EXP_REPL;
 // in global memory (not __constant__): every CTA copies it to shared memory, and constant
 // loads at 32 different addresses per warp would serialise
 __device__ __align__(16) const double g_exp2_tab[kExpN] = {
-#if KAFKA_EXP_LOG2N == 6
-#include "exp_table.inc"
-#elif KAFKA_EXP_LOG2N == 8
-#include "exp_table256.inc"
+#if KAFKA_EXP_LOG2N == 8
+#include "../../benchmarks/exp_tables/exp_table256.inc"
 #else
 #include "exp_table1024.inc"
 #endif
@@ -81,16 +79,7 @@ __host__ __device__ constexpr int tab_hdr(int D) { return 2 * dpad(D) + 4; }   /
 __host__ __device__ constexpr int tab_row(int D) { return dpad(D) + 4; }
 
 // ---- exp in base 2^(1/N): argument already scaled by L = N/ln2 ----------------------
-#if KAFKA_EXP_LOG2N == 6
-constexpr double kL = 9.23324826168936567683e+01;        // 64/ln2
-constexpr double kInvL = 1.08304246962491450973e-02;     // ln2/64
-constexpr uint32_t kHiUnder = 0x40efeb6cu;               // high word of 708 L
-// Polynomial coefficients live in constant memory so that the DFMAs take them as
-// c[bank][offset] operands instead of re-materialising 64-bit immediates in the loop.
-__constant__ double c_exp_poly[6] = {1.24178437017169252822e-12, 5.73285168864040188714e-10,
-                                      2.11731371554647762752e-07, 5.86490495505616996649e-05,
-                                      1.08304246962491450973e-02, 6755399441055744.0 /* 1.5 * 2^52 */};
-#elif KAFKA_EXP_LOG2N == 8
+#if KAFKA_EXP_LOG2N == 8
 constexpr double kL = 3.69329930467574627073e+02;        // 256/ln2
 constexpr double kInvL = 2.70760617406228627432e-03;     // ln2/256
 constexpr uint32_t kHiUnder = 0x410feb6cu;               // high word of 708 L
@@ -127,14 +116,9 @@ struct ExpPart {
 template <int kRepl = 1>
 __device__ __forceinline__ ExpPart exp_lookup(double a, const double* __restrict__ tab) {
     ExpPart e;
-#if KAFKA_EXP_F2I
-    e.k = __double2int_rn(a);
-    e.r = a - (double)e.k;
-#else
-    const double t = a + c_exp_poly[5];
+    const double t = a + c_exp_poly[5];              // magic-number add: rint(a) in the low word (F2I/I2F measured slower)
     e.k = __double2loint(t);
     e.r = a - (t - c_exp_poly[5]);
-#endif
     e.tv = tab[(e.k & (kExpN - 1)) * kRepl];         // kRepl > 1: tab already points at this lane's copy
     return e;
 }
@@ -144,11 +128,7 @@ template <bool kChecked>
 __device__ __forceinline__ double exp_finish(const ExpPart& e, double a, int sgn = 0) {
     const double r = e.r;
     const int k = e.k;
-#if KAFKA_EXP_LOG2N == 6
-    double p = fma(r, c_exp_poly[0], c_exp_poly[1]);
-    p = fma(p, r, c_exp_poly[2]);
-    p = fma(p, r, c_exp_poly[3]);
-#elif KAFKA_EXP_LOG2N == 8
+#if KAFKA_EXP_LOG2N == 8
     double p = fma(r, c_exp_poly[1], c_exp_poly[2]);
     p = fma(p, r, c_exp_poly[3]);
 #else

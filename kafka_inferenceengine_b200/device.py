@@ -97,8 +97,11 @@ class PixelIndex(object):
         """(n_params, ny, nx) float32 rasters of the mean and 1/sqrt(diag(P^-1))
         (input_output/observations.py:374-375,392-393)."""
         lib = _lib.get_lib()
-        mean_r = torch.zeros((n_params, self.n_raster), dtype=torch.float32, device=self.device)
-        unc_r = torch.zeros_like(mean_r) if want_unc else None
+        # one allocation for both rasters (views of it are handed out): one fill instead of two, and the
+        # output stage reads both back with one copy
+        both = torch.zeros((2 if want_unc else 1, n_params, self.n_raster), dtype=torch.float32, device=self.device)
+        mean_r = both[0]
+        unc_r = both[1] if want_unc else None
         with torch.cuda.device(self.device):
             _lib.check(lib.kafka_scatter_output(_lib.ptr(x.data), _lib.ptr(a_packed.data) if want_unc else None,
                                                 x.ld, self.n_pix, n_params, _lib.ptr(self.idx), self.n_raster,

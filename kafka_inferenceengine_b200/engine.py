@@ -34,6 +34,9 @@ def _pinned_view(a, dtype):
     return t if t.is_pinned() else None
 
 
+_F64, _BOOL = np.dtype(np.float64), np.dtype(np.bool_)
+
+
 class BandBuffers(object):
     """Compacted per-band observation rows on the device."""
 
@@ -111,6 +114,7 @@ class _Slot(object):
         self.np_raw = None
         self.copied = [torch.cuda.Event() for _ in range(n_bands)]   # H2D of band b done
         self.gathered = None                                         # main stream finished reading d_*
+        self.up = None                        # (n_bands, source / destination / size arrays) of kafka_upload_rasters
 
     def ensure_host(self, floats=True):
         if floats and self.h_obs is None:
@@ -170,6 +174,7 @@ class ObservationStager(object):
         self._next = 0
         self._pool = None
         self._copy_stream = None
+        self._pinned_cache = {}              # address -> (byte size, page-locked?)
 
     def _slot(self, n_bands):
         k = self._next
@@ -248,7 +253,11 @@ class ObservationStager(object):
         small = n < (1 << 18)                          # tiny rasters: the pool's hand-over costs more than the copy
         # rasters that already lie in page-locked memory (pinned_raster) are read by the DMA engine
         # where they are: no staging copy, the host cores do not touch the data at all
-        direct = {} if small else self._direct_sources(current_data, holders, raw, sources, n)
+        if small:
+            # tiny rasters: all in place (addresses, see below) or all through one staging copy
+            direct = self._direct_addresses(holders, n) if not raw and not sources else {}
+        else:
+            direct = self._direct_sources(current_data, holders, raw, sources, n)
         staged_bands = [b for b in range(nb) if b not in sources and b not in direct]
         if raw:
             slot.ensure_raw(host=any(b in raw for b in staged_bands))
@@ -263,6 +272,27 @@ class ObservationStager(object):
             else:
                 futures.append([self._pool.submit(self._stage_part, slot, b, holders[b], n * k // parts,
                                                   n * (k + 1) // parts) for k in range(parts)])
+        if small and not raw and not sources and direct:
+            # tiny page-locked rasters: three copies per band straight from the caller's arrays (the staging
+            # memcpy of the whole date would cost more than the copies), queued by ONE library call
+            # (kafka_upload_rasters), one event, one gather
+            import ctypes as C
+            if slot.up is None or slot.up[0] != nb:
+                dst = (C.c_void_p * (3 * nb))(*([slot.d_obs[b].data_ptr() for b in range(nb)]
+                                                + [slot.d_inv[b].data_ptr() for b in range(nb)]
+                                                + [slot.d_msk[b].data_ptr() for b in range(nb)]))
+                sizes = (C.c_int64 * (3 * nb))(*([8 * n] * (2 * nb) + [n] * nb))
+                slot.up = (nb, (C.c_void_p * (3 * nb))(), dst, sizes)
+            src = slot.up[1]
+            for b in range(nb):
+                src[b], src[nb + b], src[2 * nb + b] = direct[b]
+            with torch.cuda.device(self.device):
+                _lib.check(_lib.get_lib().kafka_upload_rasters(3 * nb, src, slot.up[2], slot.up[3],
+                                                               C.c_void_p(self._copy_stream.cuda_stream)),
+                           "kafka_upload_rasters")
+            slot.copied[nb - 1].record(self._copy_stream)
+            self.h2d_bytes += nb * n * 17
+            return StagedDate(slot, nb, one_event=True, keep=holders)
         if small and not raw and not sources:
             # tiny rasters, the reference's float rasters: launch overhead is all there is, so
             # stage every band inline and queue ONE copy per array instead of three per band
@@ -279,7 +309,7 @@ class ObservationStager(object):
             if b in sources:
                 slot.copied[b].record(self._copy_stream)           # uploaded above, on the copy stream
                 continue
-            if small:
+            if small and b not in direct:
                 if b in raw:
                     self._stage_raw(slot, b, current_data[b], raw[b], 0, n)
                 else:
@@ -316,6 +346,30 @@ class ObservationStager(object):
                     self.h2d_bytes += n * 17
                 slot.copied[b].record(self._copy_stream)
         return StagedDate(slot, nb, raw=raw, sources=sources, keep=direct)
+
+    def _direct_addresses(self, holders, n):
+        """band -> (address of obs, of the inverse variance, of the mask) when ALL bands' rasters are
+        page-locked float64 / float64 / bool arrays of n elements, else {}.  Whether an address is page
+        locked is remembered (asking the driver costs more than the rest of a small date's staging)."""
+        out = {}
+        cache = self._pinned_cache
+        for b, h in enumerate(holders):
+            trio = []
+            for a, dt_ in ((h.observations, _F64), (h._kafka_inv_var, _F64), (h.mask, _BOOL)):
+                if not isinstance(a, np.ndarray) or a.dtype != dt_ or a.size != n or not a.flags.c_contiguous:
+                    return {}
+                addr = a.ctypes.data
+                hit = cache.get(addr)
+                if hit is None or hit[0] != a.nbytes:
+                    if len(cache) > 4096:
+                        cache.clear()
+                    hit = (a.nbytes, _pinned_view(a, dt_) is not None)
+                    cache[addr] = hit
+                if not hit[1]:
+                    return {}
+                trio.append(addr)
+            out[b] = tuple(trio)
+        return out
 
     @staticmethod
     def _direct_sources(current_data, holders, raw, sources, n):

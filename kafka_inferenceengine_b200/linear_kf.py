@@ -41,7 +41,7 @@ class LinearKalman(object):
                  band_mapper=None,
                  linear=True, diagnostics=True, prior=None, *, device=None, comm=None,
                  round_operator_f32=True, dedup_uniform_state=True, prefetch_observations=True,
-                 hessian_correction=False):
+                 hessian_correction=False, small_image_path=None):
         _lib.get_lib()                                   # fail now if the CUDA library is missing
         if not isinstance(create_observation_operator, ObservationOperator):
             raise NotImplementedError(
@@ -75,6 +75,10 @@ class LinearKalman(object):
         # stage the NEXT observation date (observations.get_band_data + host->device copy)
         # while the kernels of the current date run; calls get_band_data one date early
         self.prefetch_observations = bool(prefetch_observations)
+        # one C-ABI call per date for small images (see _do_all_bands_small)
+        self.small_image_path = self.SMALL_IMAGE_PATH_DEFAULT if small_image_path is None else bool(small_image_path)
+        self._small = {}
+        self._plan_cache = {}                # emulator objects of a date -> band plan
         self._schedule = []                  # observation dates still to come in run()
         self._staged = {}                    # date -> (token, current_data)
         self.want_forward_modelled = False
@@ -229,6 +233,10 @@ class LinearKalman(object):
         (gp_groups, descs_template): gp_groups = [(band indices, [(table, mapper)])]
         sharing an emulator input size, descs_template[b] = ("linear", row, offset)
         or None for emulator bands (filled per iteration)."""
+        key = tuple(id(d.emulator) for d in current_data)
+        hit = self._plan_cache.get(key)
+        if hit is not None and all(e is d.emulator for e, d in zip(hit[2], current_data)):
+            return hit[0], list(hit[1])          # same emulator objects as before: nothing to rebuild or re-check
         op = self._create_observation_operator
         descs = [None] * len(current_data)
         groups = {}
@@ -253,6 +261,10 @@ class LinearKalman(object):
                 if len(mp) != tab.n_dim or mp.min() < 0 or mp.max() >= self.n_params:
                     raise ValueError("band %d: state mapper %s does not fit emulator/state" % (b, mp))
                 groups.setdefault(tab.n_dim, []).append((b, tab, mp))
+        if op.kind == "gp" and self.band_mapper is None:
+            if len(self._plan_cache) > 64:
+                self._plan_cache.clear()
+            self._plan_cache[key] = (list(groups.values()), list(descs), [d.emulator for d in current_data])
         return list(groups.values()), descs
 
     def _tick(self, name):
@@ -290,6 +302,12 @@ class LinearKalman(object):
         x_forecast = self._state(x_forecast)
         P_forecast_inverse = self._precision(P_forecast_inverse)
         n_bands = len(current_data)
+        token = getattr(self, "_token", None)
+        self._token = None
+        groups, descs = self._band_plan(current_data)
+        if self._small_image_ok(groups, n_bands):
+            return self._do_all_bands_small(current_data, groups[0], token, x_forecast, P_forecast_inverse,
+                                            convergence_tolerance, min_iterations)
         ws = self._workspace(n_bands)
         # the per-band outputs are handed to the caller at the end: fresh buffers per call
         # instead of a copy out of the workspace
@@ -300,10 +318,7 @@ class LinearKalman(object):
             ws.innov = torch.zeros_like(ws.innov)
         if ws.fwd is not None:
             ws.fwd = rows_zero_padded(n_bands, self.n_state_elems, self.device) if n_bands else torch.zeros_like(ws.fwd)
-        token = getattr(self, "_token", None)
-        self._token = None
         bufs = self._stager.finish(token if token is not None else self._stager.stage(current_data))
-        groups, descs = self._band_plan(current_data)
         all_linear = not groups and all(d is not None and d[0] == "linear" for d in descs)
         n, P = self.n_state_elems, self.n_params
 
@@ -402,6 +417,91 @@ class LinearKalman(object):
         innovations = DeviceBands(ws.innov, n)
         self.fwd_modelled = DeviceBands(ws.fwd, n) if self.want_forward_modelled else None
         return x_analysis, None, a_out, innovations
+
+    # ------------------------------------------------------------------
+    # Small images (the 128 x 128 .. 256 x 256 chunks the reference's drivers hand to LinearKalman,
+    # kafka_test_S2.py:202): the kernels of a date take microseconds, so what counts is how many
+    # calls the host makes.  The whole iterated linearisation of a date then goes through ONE C-ABI
+    # call (kafka_assimilate_date: the same kernels, the reference's loop and stop rule in C) on
+    # buffers kept across dates.
+    SMALL_IMAGE_PIXELS = 1 << 18
+    SMALL_IMAGE_PATH_DEFAULT = True
+
+    def _small_image_ok(self, groups, n_bands):
+        return (self.small_image_path and self.comm is None and self.profile is None
+                and len(groups) == 1 and len(groups[0]) == n_bands
+                and 0 < self.n_state_elems <= self.SMALL_IMAGE_PIXELS
+                and not self.hessian_correction and not getattr(self, "_force_hessian", False))
+
+    def _do_all_bands_small(self, current_data, group, token, x_forecast, P_forecast_inverse, tol, min_iterations):
+        import ctypes as C
+        lib = _lib.get_lib()
+        n, P, nb = self.n_state_elems, self.n_params, len(group)
+        D = group[0][1].n_dim
+        dev = self.device
+        st = self._small.get((nb, D))
+        if st is None:
+            ld = rows_zero_padded(1, n, dev).shape[1]
+            st = {"ld": ld, "bufs": engine.BandBuffers(nb, self.pixels, dev),
+                  "h0": torch.empty((nb, ld), dtype=torch.float64, device=dev),
+                  "jac": torch.empty((nb, D, ld), dtype=torch.float64, device=dev),
+                  "scalars": torch.zeros(2, dtype=torch.float64, device=dev),
+                  "pinned": torch.zeros(2, dtype=torch.float64).pin_memory(),
+                  "scratch": torch.empty(int(lib.kafka_solve_scratch_doubles(n)), dtype=torch.float64, device=dev),
+                  "norms": (C.c_double * 32)(), "ints": (C.c_int * 4)(), "arr_key": None, "arr": None}
+            st["ints_at"] = C.addressof(st["ints"])
+            self._small[(nb, D)] = st
+        ld = st["ld"]
+        key = tuple((g[1].table.data_ptr(), g[1].n_train, tuple(int(v) for v in g[2])) for g in group)
+        if st["arr_key"] != key:
+            arr = (_lib.GpBand * nb)()
+            for b, (_, tab, mp) in enumerate(group):
+                arr[b].table, arr[b].n_train, arr[b].n_dim = tab.table.data_ptr(), tab.n_train, D
+                for d in range(D):
+                    arr[b].mapper[d] = int(mp[d])
+            st["arr"], st["arr_key"] = arr, key
+        bufs = self._stager.finish(token if token is not None else self._stager.stage(current_data), out=st["bufs"])
+        self._prefetch_next()                 # the next date's rasters travel while this date is solved
+        # handed to the caller: fresh per date (the output stage may still be reading the previous ones)
+        x_work = torch.empty((2, P, ld), dtype=torch.float64, device=dev)
+        a_out = BlockDiag.empty(n, P, dev)
+        innov = torch.empty((nb, ld), dtype=torch.float64, device=dev)
+        fwd = torch.empty((nb, ld), dtype=torch.float64, device=dev) if self.want_forward_modelled else None
+        flags = (_lib.PRIOR_BROADCAST if P_forecast_inverse.is_broadcast else 0) | \
+            (_lib.ROUND_F32 if self.round_operator_f32 else 0)
+        ints = st["ints"]
+        x_uni = None
+        if self.dedup_uniform_state and isinstance(x_forecast._uniform, np.ndarray):
+            # all pixels start from one state (a prior reset): the first iteration evaluates the emulators once
+            x_uni = getattr(x_forecast, "_uniform_dev", None)
+            if x_uni is None:
+                x_uni = x_forecast._uniform_dev = x_forecast.data[:, 0].contiguous()
+        with torch.cuda.device(dev):
+            _lib.check(lib.kafka_assimilate_date(
+                n, ld, P, st["arr"], nb, _lib.ptr(bufs.y), _lib.ptr(bufs.w), _lib.ptr(bufs.m), _lib.ptr(x_forecast.data),
+                _lib.ptr(P_forecast_inverse.data), _lib.ptr(st["h0"]), _lib.ptr(st["jac"]), _lib.ptr(x_work),
+                _lib.ptr(a_out.data), _lib.ptr(innov), _lib.ptr(fwd), _lib.ptr(st["scalars"]),
+                C.c_void_p(st["pinned"].data_ptr()), _lib.ptr(st["scratch"]), float(tol), int(min_iterations), flags,
+                _lib.stream_ptr(), C.addressof(st["norms"]), st["ints_at"], st["ints_at"] + 4, st["ints_at"] + 8,
+                st["ints_at"] + 12, _lib.ptr(x_uni)),
+                "kafka_assimilate_date")
+        n_solves, n_bad, n_bad_max, idx = ints[0], ints[1], ints[2], ints[3]
+        _lib.launch_count += 4 * n_solves                # kernels of the call: (linearise, solve, reduce, read) per solve
+        norms = [st["norms"][k] for k in range(n_solves)]
+        if LOG.isEnabledFor(logging.INFO):
+            for k, v in enumerate(norms):
+                LOG.info("Band {:d}, Iteration # {:d}, convergence norm: {:g}".format(nb - 1, k + 1, v))
+        if n_solves > 25:
+            LOG.warning("Bailing out after 25 iterations!!!!!!")
+        if n_bad_max:
+            LOG.warning("%d pixels had a non positive-definite information matrix; left at the forecast"
+                        "%s", n_bad, "" if n_bad == n_bad_max else " (%d in an earlier iteration)" % n_bad_max)
+        x_analysis = DeviceVector(x_work[idx], n, P)
+        x_analysis._uniform = False
+        self.last_iterations.append(n_solves)
+        self.last_norms.append(norms)
+        self.fwd_modelled = DeviceBands(fwd, n) if self.want_forward_modelled else None
+        return x_analysis, None, a_out, DeviceBands(innov, n)
 
     # ------------------------------------------------------------------
     def assimilate(self, locate_times, x_forecast, P_forecast,

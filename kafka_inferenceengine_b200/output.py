@@ -82,14 +82,10 @@ class RasterOutput(object):
                 if pair[0].shape == shape:
                     return pair
                 self._n_alloc -= 1       # wrong shape (another state mask): drop it
-            if self._n_alloc < self.n_buffers:
+            if self._n_alloc < self.n_buffers or not self._pending:      # (no date in flight: the pair self.last holds)
                 self._n_alloc += 1
-                return (torch.empty(shape, dtype=torch.float32).pin_memory(),
-                        torch.empty(shape, dtype=torch.float32).pin_memory())
-            if not self._pending:        # every pair is held by self.last: one more than the ring
-                self._n_alloc += 1
-                return (torch.empty(shape, dtype=torch.float32).pin_memory(),
-                        torch.empty(shape, dtype=torch.float32).pin_memory())
+                both = torch.empty((2,) + tuple(shape), dtype=torch.float32).pin_memory()
+                return (both[0], both[1], both)
             # every pair is in flight: wait for the oldest date
             timestep, event, host, keep = self._pending[0]
             event.synchronize()
@@ -110,8 +106,12 @@ class RasterOutput(object):
         with torch.cuda.stream(side):
             mean_r, unc_r = pix.scatter_output(x_analysis, P_analysis_inv, n_params)
             host = self._host_pair(mean_r.shape)
-            host[0].copy_(mean_r, non_blocking=True)
-            host[1].copy_(unc_r, non_blocking=True)
+            base = mean_r._base
+            if base is not None and base is unc_r._base and base.is_contiguous() and base.numel() == host[2].numel():
+                host[2].view(base.shape).copy_(base, non_blocking=True)  # both rasters in one copy
+            else:
+                host[0].copy_(mean_r, non_blocking=True)
+                host[1].copy_(unc_r, non_blocking=True)
             event = torch.cuda.Event()
             event.record(side)
         # keep the device tensors alive until the copy has been consumed

@@ -21,6 +21,16 @@ from oracle.gp import GaussianProcess
 
 pytestmark = pytest.mark.gpu
 
+
+@pytest.fixture(autouse=True, params=["one call per date", "one call per kernel"])
+def host_path(request, monkeypatch):
+    """Every test of this file runs twice: through the small-image path (kafka_assimilate_date, one
+    C-ABI call per date, what images of up to 2^18 pixels take by default) and through the general
+    path (one call per kernel, what the large shards of the benchmark take)."""
+    import kafka_inferenceengine_b200 as kb_
+    monkeypatch.setattr(kb_.LinearKalman, "SMALL_IMAGE_PATH_DEFAULT", request.param == "one call per date")
+    return request.param
+
 TOL = 1e-6           # north_star: posterior mean and posterior-variance diagonal, relative
 
 
@@ -287,6 +297,24 @@ def test_uniform_first_iteration_shortcut_is_value_neutral():
         assert np.max(gu.rel(r[1], ref[1], floor=1e-3)) < 1e-12
         assert np.allclose(r[2], ref[2], rtol=1e-12, atol=1e-15)
         assert np.allclose(r[4], ref[4], rtol=1e-9)
+    # and the two host paths against each other: one C-ABI call per date (kafka_assimilate_date, no
+    # shared first linearisation) vs one call per kernel
+    both = []
+    for small in (True, False):
+        kf = kb.LinearKalman(obs, syn.MemoryOutput(syn.S2_PARAMETERS), mask, kb.create_prosail_observation_operator,
+                             syn.S2_PARAMETERS, state_propagation=None, prior=None, small_image_path=small)
+        kf.want_forward_modelled = True
+        data = [obs.get_band_data(obs.dates[0], b) for b in range(10)]
+        x, _, A, innov = kf.do_all_bands(obs.dates[0], data, np.tile(syn.SAIL_MEAN, N), None,
+                                         BlockDiag.from_block(inv, N, gu.DEV))
+        both.append((np.asarray(x), A.blocks(), np.asarray(innov), kf.last_iterations[-1], kf.last_norms[-1],
+                     np.asarray(kf.fwd_modelled)))
+    assert both[0][3] == both[1][3] == ref[3]
+    assert np.max(np.abs(both[0][0] - both[1][0]) / np.maximum(np.abs(both[1][0]), 1e-3)) < 1e-12
+    assert np.max(gu.rel(both[0][1], both[1][1], floor=1e-3)) < 1e-12
+    assert np.allclose(both[0][2], both[1][2], rtol=1e-12, atol=1e-15)
+    assert np.allclose(both[0][4], both[1][4], rtol=1e-9)
+    assert np.allclose(both[0][5], both[1][5], rtol=1e-10, atol=1e-13)
     # the detector itself
     v = DeviceVector.from_interleaved(np.tile(syn.SAIL_MEAN, 5000), P, gu.DEV)
     assert np.array_equal(v.uniform_value(), syn.SAIL_MEAN)

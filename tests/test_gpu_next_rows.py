@@ -17,6 +17,16 @@ from oracle.gp import GaussianProcess
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["one call per date", "one call per kernel"])
+def host_path(request, monkeypatch):
+    """Every test of this file runs twice: through the small-image path (kafka_assimilate_date, one
+    C-ABI call per date, what images of up to 2^18 pixels take by default) and through the general
+    path (one call per kernel, what the large shards of the benchmark take)."""
+    import kafka_inferenceengine_b200 as kb_
+    monkeypatch.setattr(kb_.LinearKalman, "SMALL_IMAGE_PATH_DEFAULT", request.param == "one call per date")
+    return request.param
+
+
 # ---------------------------------------------------------------- SAR / WCM
 def test_sar_observation_operator_vs_reference_and_oracle():
     g = gio.load("kat_sar")

@@ -92,18 +92,18 @@ def _call(n, P, bands, x_prev, x_f, pinv_t, flags=0, want_fwd=True):
             fwd[:B, :n].cpu().numpy().ravel(), float(norm2.item()), int(n_bad.item()))
 
 
-@pytest.mark.parametrize("pair", [False, True])
+@pytest.mark.parametrize("pair", [0, _lib.SOLVE_PAIR, _lib.SOLVE_QUAD])
 @pytest.mark.parametrize("P", list(range(1, 17)))
 def test_supplied_jacobian_all_state_sizes(P, pair):
-    """Config 5 sweep axis n_params 1..16 (x bands 1..13); ``pair`` forces the
-    two-lanes-per-pixel kernel (the default at 16 parameters) at every size."""
+    """Config 5 sweep axis n_params 1..16 (x bands 1..13); ``pair`` forces the two-lanes-per-pixel
+    or the four-lanes-per-pixel kernel (the default from 13 parameters) at every size."""
     rng = np.random.default_rng(P)
     B = 1 + (5 * P) % 13
     n = 1500 + 37 * P
     Js, H0s, ws, ys, Pinv, x_f, x_prev = _problem(rng, n, P, B)
     bands = [dict(J=Js[b], H0=H0s[b], y=ys[b], w=ws[b]) for b in range(B)]
     x, A, innov, fwd, norm2, n_bad = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv),
-                                           flags=_lib.SOLVE_PAIR if pair else 0)
+                                           flags=pair)
     xo, Ao, innov_o, fwd_o = kc.solve_dense64(ys, ws, H0s, Js, x_prev, x_f, Pinv)
     assert n_bad == 0
     assert np.max(gu.rel(A, Ao, floor=1e-6)) < RTOL
@@ -113,7 +113,8 @@ def test_supplied_jacobian_all_state_sizes(P, pair):
     assert norm2 == pytest.approx(float(((xo - x_prev) ** 2).sum()), rel=1e-9)
 
 
-@pytest.mark.parametrize("P,flags", [(7, 0), (7, _lib.SOLVE_PAIR), (15, 0)])
+@pytest.mark.parametrize("P,flags", [(7, 0), (7, _lib.SOLVE_PAIR), (15, 0), (6, _lib.SOLVE_QUAD), (16, 0),
+                                     (15, _lib.SOLVE_PAIR)])
 def test_norm_is_deterministic_and_edge_sizes(P, flags):
     rng = np.random.default_rng(99)
     for n in (1, 31, 128, 129, 5000):
@@ -168,6 +169,53 @@ def test_pair_kernel_on_uniform_linear_and_wcm_bands(P):
         assert np.allclose(innov, innov_o, rtol=1e-9, atol=1e-10)
 
 
+@pytest.mark.parametrize("P", [3, 7, 14, 16])
+def test_quad_kernel_on_shared_linearisation_mapped_arrays_and_broadcast_prior(P):
+    """The four-lanes-per-pixel kernel on the band kinds it knows: a shared linearisation
+    (KAFKA_BAND_UNIFORM) on some state slots, per-pixel arrays through a state mapper, per-pixel arrays
+    on every slot; per-pixel prior blocks and one block shared by all pixels.  Same results as the
+    one-thread kernel (same operations in the same order) and as the oracle."""
+    rng = np.random.default_rng(70 + P)
+    n = 1237
+    m = [rng.random(n) < 0.8 for _ in range(3)]
+    ws = [np.where(mm, 200.0, 0.0) for mm in m]
+    ys = [np.where(mm, rng.standard_normal(n), 0.0) for mm in m]
+    D = min(P, 4)
+    map_u, map_a = rng.permutation(P)[:D], np.sort(rng.permutation(P)[:D])
+    uJ, uH0 = rng.standard_normal(D), 0.37
+    Ja = np.where(m[1][:, None], rng.standard_normal((n, D)), 0.0)
+    H0a = np.where(m[1], rng.standard_normal(n), 0.0)
+    Jb = np.where(m[2][:, None], rng.standard_normal((n, P)), 0.0)
+    H0b = np.where(m[2], rng.standard_normal(n), 0.0)
+    x_f = 1.0 + 0.1 * rng.standard_normal(n * P)
+    x_prev = x_f + 0.02 * rng.standard_normal(n * P)
+    bands = [dict(uni_J=uJ, uni_H0=uH0, mapper=map_u, y=ys[0], w=ws[0]),
+             dict(J=Ja, H0=H0a, y=ys[1], w=ws[1], mapper=map_a), dict(J=Jb, H0=H0b, y=ys[2], w=ws[2])]
+    Jf = [np.zeros((n, P)), np.zeros((n, P)), Jb]
+    Jf[0][:, map_u] = uJ
+    Jf[0][~m[0]] = 0.0
+    Jf[1][:, map_a] = Ja
+    H0f = [np.where(m[0], uH0, 0.0), H0a, H0b]
+    Pinv = gu.random_spd(rng, n, P)
+    one = gu.random_spd(rng, 1, P)[0]
+    r, c = np.tril_indices(P)
+    cases = [(gu.pack_blocks(Pinv), Pinv, 0),
+             (torch.from_numpy(np.ascontiguousarray(one[r, c])).to(gu.DEV), np.repeat(one[None], n, axis=0), _lib.PRIOR_BROADCAST)]
+    for packed, blocks, extra in cases:
+        res = [_call(n, P, bands, x_prev, x_f, packed, flags=f | extra) for f in (0, _lib.SOLVE_QUAD)]
+        assert np.allclose(res[0][0], res[1][0], rtol=1e-11, atol=1e-13)
+        assert np.array_equal(res[0][1], res[1][1]) and np.array_equal(res[0][2], res[1][2])
+        assert np.allclose(res[0][3], res[1][3], rtol=1e-11, atol=1e-12)
+        xo, Ao, innov_o, fwd_o = kc.solve_dense64(ys, ws, H0f, Jf, x_prev, x_f, blocks)
+        for x, A, innov, fwd, norm2, n_bad in res:
+            assert n_bad == 0
+            assert np.max(gu.rel(A, Ao, floor=1e-6)) < 1e-8
+            assert np.max(np.abs(x - xo) / np.maximum(np.abs(xo), 1e-3)) < 1e-8
+            assert np.allclose(innov, innov_o, rtol=1e-9, atol=1e-10)
+            assert np.allclose(fwd, fwd_o, rtol=1e-9, atol=1e-10)
+            assert norm2 == pytest.approx(float(((xo - x_prev) ** 2).sum()), rel=1e-9)
+
+
 def test_no_bands_and_empty_image():
     rng = np.random.default_rng(1)
     n, P = 300, 5
@@ -220,7 +268,8 @@ def test_mapper_linear_and_broadcast_prior(pair):
     assert np.allclose(fwd, fwd_o, rtol=1e-9, atol=1e-10)
 
 
-@pytest.mark.parametrize("P,flags", [(4, 0), (4, _lib.SOLVE_PAIR), (13, 0)])
+@pytest.mark.parametrize("P,flags", [(4, 0), (4, _lib.SOLVE_PAIR), (13, 0), (5, _lib.SOLVE_QUAD), (16, 0),
+                                     (13, _lib.SOLVE_PAIR)])
 def test_non_positive_definite_blocks_are_flagged(P, flags):
     rng = np.random.default_rng(8)
     n = 500
