@@ -499,6 +499,8 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
     for (int b = 0; b < n_bands; ++b)
         if (prm.bands[b].kind == KAFKA_BAND_ARRAYS && prm.bands[b].n_planes > n_dim_max) n_dim_max = prm.bands[b].n_planes;
     const size_t ring = (size_t)kAsyncStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
+    // the lane-sharing kernels run 64 pixels per CTA: two CTAs add into one scratch slot
+    const unsigned grid_half = (unsigned)((n_pix + kSolveThreads / 2 - 1) / (kSolveThreads / 2));
     int rc = KAFKA_E_UNSUPPORTED;
     bool quad_kinds = true;                 // the four-lane kernel knows per-pixel arrays and shared linearisations
     for (int b = 0; b < n_bands; ++b)
@@ -508,12 +510,13 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         for (int b = 0; b < n_bands; ++b) all_identity_quad = all_identity_quad && prm.bands[b].identity;
         KAFKA_DISPATCH_P(n_params, {
             auto kern = all_identity_quad ? solve_bands_quad_kernel<kP, true> : solve_bands_quad_kernel<kP, false>;
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring);
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ring / 2));
+            if (e == cudaSuccess) e = cudaMemsetAsync(scratch, 0, 2 * (size_t)grid * sizeof(double), s);
             if (e != cudaSuccess) {
-                set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+                set_error("launch set-up failed: %s", cudaGetErrorString(e));
                 rc = (int)e;
             } else {
-                kern<<<grid, kQuadThreads, ring, s>>>(prm, n_dim_max);
+                kern<<<grid_half, kQuadThreads, ring / 2, s>>>(prm, n_dim_max);
                 rc = launch_status("solve_bands_quad_kernel");
             }
         });
@@ -526,12 +529,13 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         for (int b = 0; b < n_bands; ++b) all_identity_pair = all_identity_pair && prm.bands[b].identity;
         KAFKA_DISPATCH_P(n_params, {
             auto kern = all_identity_pair ? solve_bands_pair_kernel<kP, true> : solve_bands_pair_kernel<kP, false>;
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring);
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ring / 2));
+            if (e == cudaSuccess) e = cudaMemsetAsync(scratch, 0, 2 * (size_t)grid * sizeof(double), s);
             if (e != cudaSuccess) {
-                set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+                set_error("launch set-up failed: %s", cudaGetErrorString(e));
                 rc = (int)e;
             } else {
-                kern<<<grid, kPairThreads, ring, s>>>(prm, n_dim_max);
+                kern<<<grid_half, kPairThreads, ring / 2, s>>>(prm, n_dim_max);
                 rc = launch_status("solve_bands_pair_kernel");
             }
         });

@@ -20,8 +20,8 @@
 //   * forward substitution: y_j broadcast from its owner; backward: each lane sums over its
 //     own rows and one __shfl_xor adds the partner's share.
 // Band values are staged per PIXEL by cp.async (the two lanes copy alternate values) and
-// read by both lanes after __syncwarp.  256 threads = 128 pixels per CTA, so grid size,
-// scratch and the deterministic reduction are exactly those of solve_bands_kernel.
+// read by both lanes after __syncwarp.  128 threads = 64 pixels per CTA (see kPairPix); scratch and the
+// deterministic reduction are those of solve_bands_kernel.
 #pragma once
 
 namespace kafka {
@@ -30,8 +30,13 @@ namespace kafka {
 #define KAFKA_PAIR_FROM_PARAMS 14
 #endif
 constexpr int kPairFromParams = KAFKA_PAIR_FROM_PARAMS;   // state sizes from here on use the pair kernel
-constexpr int kPairThreads = 2 * kSolveThreads;
-constexpr int kPairPix = kSolveThreads;
+// 64 pixels (128 threads) per CTA: at 254 registers that is two CTAs per SM whose load phases (prior block,
+// band rows) and compute phases (factorisation, substitutions) overlap each other; with one 128-pixel CTA
+// per SM every warp waited on memory at the same time and the HBM pipe idled during the factorisation.
+// CTAs 2k and 2k+1 add their partial sums into slot k of the scratch (zeroed by the host before the
+// launch): the sum of two numbers does not depend on their order, so the norm stays bit-reproducible.
+constexpr int kPairPix = kSolveThreads / 2;
+constexpr int kPairThreads = 2 * kPairPix;
 
 template <int P>
 __device__ __forceinline__ double at_or_zero(const double (&v)[P], int idx) {
@@ -42,7 +47,7 @@ __device__ __forceinline__ double pair_bcast(double v, unsigned lane) { return _
 
 // kAllIdentity: every band is a per-pixel array band with the identity mapper (see solve_bands_kernel).
 template <int P, bool kAllIdentity = false>
-__global__ void __launch_bounds__(kPairThreads, 1)
+__global__ void __launch_bounds__(kPairThreads, 2)
 solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     constexpr int K = (P + 1) / 2;
     constexpr int PE = 2 * K;
@@ -317,8 +322,9 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
             s0 += s_part[0][k];
             s1 += s_part[1][k];
         }
-        prm.partials[blockIdx.x] = s0;
-        prm.partials[gridDim.x + blockIdx.x] = s1;
+        const unsigned n_slots = (gridDim.x + 1) / 2;
+        atomicAdd(prm.partials + (blockIdx.x >> 1), s0);
+        atomicAdd(prm.partials + n_slots + (blockIdx.x >> 1), s1);
     }
 }
 

@@ -16,8 +16,8 @@
 //     rows and two __shfl_xor add up the quad.
 // Band values are staged per PIXEL by cp.async (the four lanes copy every fourth value) and read by
 // all four after __syncwarp.  Band kinds: per-pixel arrays and one shared linearisation; an image
-// with LINEAR or WCM bands at these sizes takes the two-lane kernel.  512 threads = 128 pixels per
-// CTA, so grid size, scratch and the deterministic reduction are those of solve_bands_kernel.
+// with LINEAR or WCM bands at these sizes takes the two-lane kernel.  256 threads = 64 pixels per CTA, two
+// CTAs per SM; scratch and the deterministic reduction are those of solve_bands_kernel.
 #pragma once
 
 namespace kafka {
@@ -29,8 +29,8 @@ namespace kafka {
 #endif
 constexpr int kQuadFromParams = KAFKA_QUAD_FROM_PARAMS;
 constexpr int kQuadLanes = 4;
-constexpr int kQuadThreads = kQuadLanes * kSolveThreads;
-constexpr int kQuadPix = kSolveThreads;
+constexpr int kQuadPix = kSolveThreads / 2;                  // 64 pixels = 256 threads per CTA, two CTAs per SM (see kPairPix)
+constexpr int kQuadThreads = kQuadLanes * kQuadPix;
 
 __host__ __device__ constexpr int quad_off(int k) { return 2 * k * (k + 1); }
 
@@ -42,7 +42,7 @@ __device__ __forceinline__ double quad_sum(double v) {
 }
 
 template <int P, bool kAllIdentity = false>
-__global__ void __launch_bounds__(kQuadThreads, 1)
+__global__ void __launch_bounds__(kQuadThreads, 2)
 solve_bands_quad_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     constexpr int G = kQuadLanes;
     constexpr int K = (P + G - 1) / G;
@@ -310,8 +310,9 @@ solve_bands_quad_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
             s0 += s_part[0][k];
             s1 += s_part[1][k];
         }
-        prm.partials[blockIdx.x] = s0;
-        prm.partials[gridDim.x + blockIdx.x] = s1;
+        const unsigned n_slots = (gridDim.x + 1) / 2;
+        atomicAdd(prm.partials + (blockIdx.x >> 1), s0);
+        atomicAdd(prm.partials + n_slots + (blockIdx.x >> 1), s1);
     }
 }
 

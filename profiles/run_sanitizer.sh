@@ -17,4 +17,4 @@ for tool in memcheck racecheck; do
     echo "exit status: ${PIPESTATUS[0]}" >> $log
   done
 done
-tail -40 $OUT/r02_sanitizer_memcheck.txt $OUT/r02_sanitizer_racecheck.txt
+for tool in memcheck racecheck; do echo "== $tool"; tail -40 $OUT/r02_sanitizer_$tool.txt; done

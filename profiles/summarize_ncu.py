@@ -1,6 +1,7 @@
 """Turn an ncu report (ncu --set full ... -o X) into the small summaries committed here.
 
     python profiles/summarize_ncu.py gpurun_out/prof.ncu-rep profiles/r01_ncu_kernels 2196000
+    python profiles/summarize_ncu.py gpurun_out/prof_raw.csv profiles/r02_ncu_kernels 2196000
 
 Writes <out>.json (per kernel: duration, DRAM bytes, pipe/issue/occupancy figures, top stall
 reasons, bytes per pixel) and <out>.txt (the same as a table).  The third argument is the pixel
@@ -31,7 +32,10 @@ SCALE = {"Gbyte": 1.0, "Mbyte": 1e-3, "Kbyte": 1e-6, "byte": 1e-9, "ms": 1.0, "u
 
 
 def main(rep, out, n_pix):
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if rep.endswith(".csv"):          # the raw page as exported on the GPU box (profiles/capture.sh)
+        raw = open(rep).read()
+    else:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
     idx = {h: i for i, h in enumerate(hdr)}
