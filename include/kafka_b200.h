@@ -301,20 +301,20 @@ int kafka_assimilate_iter(int64_t n_pix, int64_t ld, int n_params, const kafka_g
  * stop rule (norm = ||x - x_prev||_2 / len(x) < tol and n_iter >= min_iterations, or the 26th
  * solve; linear_kf.py:293-304), for images so small that per-call overhead is all there is.
  * x_work: [2][n_params*ld] doubles, the iterates ping-pong between the halves and *x_index
- * says which holds the analysis; scalars: 2 doubles on the device; pinned_host16: 16 bytes of
- * page-locked host memory (the per-iteration sum of squares and bad-pixel count land there);
+ * says which holds the analysis; scalars: 2 doubles on the device; pinned_host: 26 x 16 bytes of
+ * page-locked host memory (every solve's sum of squares and bad-pixel count land there);
  * norms_host: >= 26 doubles, one norm per solve; *n_solves = solves taken; *n_bad_last /
  * *n_bad_max = pixels left at the forecast in the last / the worst iteration.  a_out,
  * innovations and fwd (may be NULL) are written by iterations that can be the last one.
  * x_uniform (may be NULL): n_params contiguous doubles on the device -- the state shared by ALL
  * pixels of x_f (e.g. after a prior reset); the first iteration then evaluates the emulators once
  * for that vector, the reference's single-unique-vector branch (kafka/inference/utils.py:72-74).
- * Synchronises `stream` once per iteration. */
+ * Synchronises `stream` once per iteration that can end the loop. */
 int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, const kafka_gp_band* gp_bands_host,
                           int n_bands, const double* y, const double* w, const uint8_t* obs_mask,
                           const double* x_f, const double* pinv_f, double* h0_work, double* jac_work,
                           double* x_work, double* a_out, double* innovations, double* fwd,
-                          double* scalars, void* pinned_host16, double* scratch, double tol,
+                          double* scalars, void* pinned_host, double* scratch, double tol,
                           int min_iterations, uint32_t flags, void* stream, double* norms_host,
                           int* n_solves, int* n_bad_last, int* n_bad_max, int* x_index,
                           const double* x_uniform);

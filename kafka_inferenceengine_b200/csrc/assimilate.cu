@@ -46,26 +46,27 @@ extern "C" int kafka_assimilate_iter(int64_t n_pix, int64_t ld, int n_params, co
 // kafka_test_S2.py:202, kafka_test_Py36.py:241).  The loop and the stop rule are the
 // reference's (linear_kf.py:253-307): relinearise every band at x_prev, solve,
 // norm = ||x - x_prev||_2 / len(x), stop when norm < tol and n_iter >= min_iterations or after
-// the 26th solve; the norm comes back through page-locked memory written by a kernel
-// (kafka_read_small) and the stream is synchronised once per iteration.  The states ping-pong
+// the 26th solve; the norms come back through page-locked memory written by a kernel
+// (kafka_read_small, 16 bytes per solve) and the stream is synchronised once per iteration that
+// can end the loop (iterations below min_iterations are queued back to back).  The states ping-pong
 // between the two halves of x_work; *x_index says which half holds the analysis.  A and the
 // innovations are stored only by iterations that can be the last one.
 extern "C" int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, const kafka_gp_band* gp_bands_host,
                                      int n_bands, const double* y, const double* w, const uint8_t* obs_mask,
                                      const double* x_f, const double* pinv_f, double* h0_work, double* jac_work,
                                      double* x_work, double* a_out, double* innovations, double* fwd,
-                                     double* scalars, void* pinned_host16, double* scratch, double tol,
+                                     double* scalars, void* pinned_host, double* scratch, double tol,
                                      int min_iterations, uint32_t flags, void* stream, double* norms_host,
                                      int* n_solves, int* n_bad_last, int* n_bad_max, int* x_index,
                                      const double* x_uniform) {
-    KAFKA_CHECK_ARG(x_work && scalars && pinned_host16 && norms_host && n_solves && x_index && a_out,
+    KAFKA_CHECK_ARG(x_work && scalars && pinned_host && norms_host && n_solves && x_index && a_out,
                     "kafka_assimilate_date: null workspace or result pointer");
     KAFKA_CHECK_ARG(n_pix >= 1 && n_params >= 1, "kafka_assimilate_date: empty problem");
     KAFKA_CHECK_ARG(n_bands >= 1 && n_bands <= KAFKA_MAX_BANDS && gp_bands_host, "kafka_assimilate_date: n_bands %d", n_bands);
     cudaStream_t s = (cudaStream_t)stream;
     const double* x_prev = x_f;
     const double n_elems = (double)n_pix * (double)n_params;
-    int bad_max = 0, bad = 0, idx = 0;
+    int bad_max = 0, bad = 0, idx = 0, n_read = 0;
     int n_iter = 1;
     for (;; ++n_iter) {
         idx = (n_iter - 1) & 1;
@@ -103,16 +104,23 @@ extern "C" int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, co
                                        reinterpret_cast<int32_t*>(scalars + 1), scratch, flags, stream);
         }
         if (rc != 0) return rc;
-        rc = kafka_read_small(scalars, pinned_host16, 16, stream);
+        // slot n_iter-1 of the page-locked buffer: [sum of squares | bad pixels] of this solve
+        char* slot = static_cast<char*>(pinned_host) + 16 * (n_iter - 1);
+        rc = kafka_read_small(scalars, slot, 16, stream);
         if (rc != 0) return rc;
-        KAFKA_CUDA(cudaStreamSynchronize(s));
-        const volatile double* host = static_cast<const volatile double*>(pinned_host16);
-        const double ssq = host[0];
-        bad = *reinterpret_cast<const volatile int32_t*>(host + 1);
-        bad_max = bad > bad_max ? bad : bad_max;
-        const double norm = sqrt(ssq) / n_elems;                    // linear_kf.py:293
-        norms_host[n_iter - 1] = norm;
         x_prev = x_new;
+        // an iteration below min_iterations cannot end the loop (linear_kf.py:297): its norm is only reported,
+        // so the next iteration is queued right behind it and the host waits once for both
+        if (n_iter < min_iterations && n_iter <= 25) continue;
+        KAFKA_CUDA(cudaStreamSynchronize(s));
+        double norm = 0.0;
+        for (; n_read < n_iter; ++n_read) {
+            const volatile double* host = reinterpret_cast<const volatile double*>(static_cast<char*>(pinned_host) + 16 * n_read);
+            bad = *reinterpret_cast<const volatile int32_t*>(host + 1);
+            bad_max = bad > bad_max ? bad : bad_max;
+            norm = sqrt(host[0]) / n_elems;                         // linear_kf.py:293
+            norms_host[n_read] = norm;
+        }
         if ((norm < tol && n_iter >= min_iterations) || n_iter > 25) break;   // linear_kf.py:297-304
     }
     *n_solves = n_iter;

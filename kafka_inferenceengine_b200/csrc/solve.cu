@@ -535,7 +535,7 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
                 set_error("launch set-up failed: %s", cudaGetErrorString(e));
                 rc = (int)e;
             } else {
-                kern<<<grid_half, kPairThreads, ring / 2, s>>>(prm, n_dim_max);
+                kern<<<(unsigned)((n_pix + kPairPix - 1) / kPairPix), kPairThreads, ring / kPairSplit, s>>>(prm, n_dim_max);
                 rc = launch_status("solve_bands_pair_kernel");
             }
         });

@@ -35,7 +35,11 @@ constexpr int kPairFromParams = KAFKA_PAIR_FROM_PARAMS;   // state sizes from he
 // per SM every warp waited on memory at the same time and the HBM pipe idled during the factorisation.
 // CTAs 2k and 2k+1 add their partial sums into slot k of the scratch (zeroed by the host before the
 // launch): the sum of two numbers does not depend on their order, so the norm stays bit-reproducible.
-constexpr int kPairPix = kSolveThreads / 2;
+#ifndef KAFKA_PAIR_SPLIT
+#define KAFKA_PAIR_SPLIT 2
+#endif
+constexpr int kPairSplit = KAFKA_PAIR_SPLIT;                  // CTAs per 128-pixel tile (experiment knob)
+constexpr int kPairPix = kSolveThreads / kPairSplit;
 constexpr int kPairThreads = 2 * kPairPix;
 
 template <int P>
@@ -47,7 +51,7 @@ __device__ __forceinline__ double pair_bcast(double v, unsigned lane) { return _
 
 // kAllIdentity: every band is a per-pixel array band with the identity mapper (see solve_bands_kernel).
 template <int P, bool kAllIdentity = false>
-__global__ void __launch_bounds__(kPairThreads, 2)
+__global__ void __launch_bounds__(kPairThreads, kPairSplit)
 solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     constexpr int K = (P + 1) / 2;
     constexpr int PE = 2 * K;
@@ -322,9 +326,9 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
             s0 += s_part[0][k];
             s1 += s_part[1][k];
         }
-        const unsigned n_slots = (gridDim.x + 1) / 2;
-        atomicAdd(prm.partials + (blockIdx.x >> 1), s0);
-        atomicAdd(prm.partials + n_slots + (blockIdx.x >> 1), s1);
+        const unsigned n_slots = (gridDim.x + kPairSplit - 1) / kPairSplit;
+        atomicAdd(prm.partials + blockIdx.x / kPairSplit, s0);
+        atomicAdd(prm.partials + n_slots + blockIdx.x / kPairSplit, s1);
     }
 }
 

@@ -175,6 +175,7 @@ class ObservationStager(object):
         self._pool = None
         self._copy_stream = None
         self._pinned_cache = {}              # address -> (byte size, page-locked?)
+        self._band_cache = {}                # ids of a band's three arrays -> (their addresses, the arrays)
 
     def _slot(self, n_bands):
         k = self._next
@@ -255,7 +256,7 @@ class ObservationStager(object):
         # where they are: no staging copy, the host cores do not touch the data at all
         if small:
             # tiny rasters: all in place (addresses, see below) or all through one staging copy
-            direct = self._direct_addresses(holders, n) if not raw and not sources else {}
+            direct = self._direct_addresses(holders, n, current_data) if not raw and not sources else {}
         else:
             direct = self._direct_sources(current_data, holders, raw, sources, n)
         staged_bands = [b for b in range(nb) if b not in sources and b not in direct]
@@ -347,13 +348,20 @@ class ObservationStager(object):
                 slot.copied[b].record(self._copy_stream)
         return StagedDate(slot, nb, raw=raw, sources=sources, keep=direct)
 
-    def _direct_addresses(self, holders, n):
+    def _direct_addresses(self, holders, n, current_data=None):
         """band -> (address of obs, of the inverse variance, of the mask) when ALL bands' rasters are
         page-locked float64 / float64 / bool arrays of n elements, else {}.  Whether an address is page
         locked is remembered (asking the driver costs more than the rest of a small date's staging)."""
         out = {}
         cache = self._pinned_cache
         for b, h in enumerate(holders):
+            # the same three array objects as on an earlier date (a source that keeps its buffers): same addresses
+            d = current_data[b]
+            key = (id(d.observations), id(d.uncertainty), id(d.mask))
+            hit = self._band_cache.get(key)
+            if hit is not None and hit[1] is d.observations and hit[2] is d.uncertainty and hit[3] is d.mask:
+                out[b] = hit[0]
+                continue
             trio = []
             for a, dt_ in ((h.observations, _F64), (h._kafka_inv_var, _F64), (h.mask, _BOOL)):
                 if not isinstance(a, np.ndarray) or a.dtype != dt_ or a.size != n or not a.flags.c_contiguous:
@@ -369,6 +377,9 @@ class ObservationStager(object):
                     return {}
                 trio.append(addr)
             out[b] = tuple(trio)
+            if len(self._band_cache) > 256:
+                self._band_cache.clear()
+            self._band_cache[key] = (out[b], d.observations, d.uncertainty, d.mask)
         return out
 
     @staticmethod

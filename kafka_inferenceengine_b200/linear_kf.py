@@ -446,7 +446,7 @@ class LinearKalman(object):
                   "h0": torch.empty((nb, ld), dtype=torch.float64, device=dev),
                   "jac": torch.empty((nb, D, ld), dtype=torch.float64, device=dev),
                   "scalars": torch.zeros(2, dtype=torch.float64, device=dev),
-                  "pinned": torch.zeros(2, dtype=torch.float64).pin_memory(),
+                  "pinned": torch.zeros(2 * 26, dtype=torch.float64).pin_memory(),      # 16 bytes per solve
                   "scratch": torch.empty(int(lib.kafka_solve_scratch_doubles(n)), dtype=torch.float64, device=dev),
                   "norms": (C.c_double * 32)(), "ints": (C.c_int * 4)(), "arr_key": None, "arr": None}
             st["ints_at"] = C.addressof(st["ints"])

@@ -16,10 +16,15 @@ Contents
 ``kafka_cpu.py``   numpy/scipy restatement of the reference's filter equations:
                    oracle A' (scipy sparse + float32 SuperLU, as the reference
                    does it) and oracle B (fp64, one dense block per pixel).
-``ref_shim.py``    imports the UNMODIFIED reference from ``/root/reference``
-                   behind stub modules (works only where that path exists, i.e.
-                   in the build container, never on the GPU box).
+``ref_shim.py``    imports the UNMODIFIED reference behind stub modules, from
+                   ``/root/reference`` (build container) or from ``baseline/_ref``
+                   (the pip-installed copy that travels to the GPU box).
+``install_ref.py`` the recipe that makes ``baseline/_ref`` (run by
+                   ``__graft_entry__.build()`` where the source tree exists).
+``ref_runner.py``  times the unmodified reference on chunks of the benchmark
+                   workload (``bench.py --impl reference`` / ``cpu_baseline``).
 ``make_golden.py`` runs the unmodified reference under the shim and writes the
                    fixtures committed under ``tests/golden/``.
-``synthetic.py``   seeded synthetic inputs for the BASELINE.json configs.
+``synthetic.py``   the benchmark's seeded workload restated for the CPU legs,
+                   which must not import the product package.
 """
