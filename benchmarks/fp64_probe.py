@@ -20,7 +20,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def main():
     lib = ctypes.CDLL(os.path.join(ROOT, "benchmarks", "libkafka_probe.so"))
-    for name in ("kafka_probe_fp64_tflops", "kafka_probe_dmma_tflops"):
+    for name in ("kafka_probe_fp64_tflops", "kafka_probe_dmma_tflops", "kafka_probe_fp64_fma3_tflops"):
         getattr(lib, name).restype = ctypes.c_double
     lib.kafka_probe_dfma_step_cycles.restype = ctypes.c_double
     lib.kafka_probe_dfma_step_cycles.argtypes = [ctypes.c_int, ctypes.c_int]
@@ -28,6 +28,7 @@ def main():
     smi = subprocess.Popen(["nvidia-smi", "-i", "0", "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
                            stdout=subprocess.PIPE, text=True)
     res = {"dfma_tflops": lib.kafka_probe_fp64_tflops(5), "dmma_m8n8k4_tflops": lib.kafka_probe_dmma_tflops(5)}
+    res["dfma_three_register_operands_tflops"] = lib.kafka_probe_fp64_fma3_tflops(5)
     res["dfma_tflops_again"] = lib.kafka_probe_fp64_tflops(5)
     steps = {}
     for warps in (1, 2, 3, 4):

@@ -26,6 +26,10 @@ VARIANTS = {
     "prehead": ["-DKAFKA_GP_PREFETCH_HEAD=1"],                        # {e2, sgn, zh[0..1]} of the next row fetched a trip early
     "insfirst_prehead": ["-DKAFKA_EXP_INSERT_FIRST=1", "-DKAFKA_GP_PREFETCH_HEAD=1"],
     "ppt3_mb3": ["-DKAFKA_GP_PPT_BIG=3", "-DKAFKA_GP_MINBLOCKS=3"],
+    "t224_mb2": ["-DKAFKA_GP_THREADS=224", "-DKAFKA_GP_MINBLOCKS=2"],     # 14 warps per SM at <= 144 registers
+    "t448_mb1": ["-DKAFKA_GP_THREADS=448", "-DKAFKA_GP_MINBLOCKS=1"],     # the same as one CTA (table staged once per SM)
+    "t192_mb2": ["-DKAFKA_GP_THREADS=192", "-DKAFKA_GP_MINBLOCKS=2"],     # 12 warps as two CTAs, <= 168 registers
+    "t416_mb1": ["-DKAFKA_GP_THREADS=416", "-DKAFKA_GP_MINBLOCKS=1"],     # 13 warps, <= 152 registers
     "tab256": ["-DKAFKA_EXP_LOG2N=8"],
     "repl256": ["-DKAFKA_EXP_LOG2N=8", "-DKAFKA_EXP_REPL=16"],        # conflict-free 2^(k/256) look-ups, degree 4
     "ppt1_mb5": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=5"],  # one pixel per thread, 20 warps per SM

@@ -18,6 +18,29 @@ __global__ void __launch_bounds__(256) fp64_fma_probe(double* out, int iters, do
     if (s == 123.456) out[0] = s;     // never true; keeps the chains alive
 }
 
+// Same, but every FMA reads THREE register operands (the emulator loop's shape: G += w * zh, a += zh * x)
+// instead of one register and two constants: tells whether operand delivery from the register file lowers
+// the reachable rate.  v_k = v_k * p_k + q_k on 8 chains, p/q rotated so that nothing folds into constants.
+__global__ void __launch_bounds__(256) fp64_fma3_probe(double* out, int iters, const double* __restrict__ coef) {
+    double v[8], p[8], q[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        v[k] = threadIdx.x * 1e-9 + k * 1e-3;
+        p[k] = coef[k] - threadIdx.x * 1e-12;            // thread-dependent: must live in vector registers
+        q[k] = coef[8 + k] + threadIdx.x * 1e-15;
+    }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = fma(v[k], p[(k + u) & 7], q[(k + 3 * u) & 7]);
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += v[k];
+    if (s == 123.456) out[0] = s;
+}
+
 // fp64 tensor-core path: mma.sync m8n8k4 (DMMA), 8 independent accumulator chains per warp
 __global__ void __launch_bounds__(256) fp64_dmma_probe(double* out, int iters, double a, double b) {
     double c[8][2];
@@ -158,6 +181,38 @@ double kafka_probe_dmma_tflops(int reps) {
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     cudaFree(out);
+    return best;
+}
+
+// DFMA with three register operands, TFLOP/s, best of `reps`
+double kafka_probe_fp64_fma3_tflops(int reps) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    double *out = nullptr, *coef = nullptr;
+    if (cudaMalloc(&out, 8) != cudaSuccess || cudaMalloc(&coef, 128) != cudaSuccess) return -1.0;
+    double h[16];
+    for (int k = 0; k < 16; ++k) h[k] = k < 8 ? 0.999999 - 1e-9 * k : 1e-7 * (k - 7);
+    cudaMemcpy(coef, h, sizeof(h), cudaMemcpyHostToDevice);
+    const int iters = 4096, threads = 256, blocks = sms * 8;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0.0;
+    for (int r = 0; r < reps + 1; ++r) {
+        cudaEventRecord(e0);
+        fp64_fma3_probe<<<blocks, threads>>>(out, iters, coef);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double tf = 2.0 * 8 * 16 * (double)iters * threads * blocks / (ms * 1e-3) / 1e12;
+        if (r > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    cudaFree(coef);
     return best;
 }
 
