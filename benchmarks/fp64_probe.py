@@ -20,7 +20,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def main():
     lib = ctypes.CDLL(os.path.join(ROOT, "benchmarks", "libkafka_probe.so"))
-    for name in ("kafka_probe_fp64_tflops", "kafka_probe_dmma_tflops", "kafka_probe_fp64_fma3_tflops"):
+    for name in ("kafka_probe_fp64_tflops", "kafka_probe_dmma_tflops", "kafka_probe_fp64_fma3_tflops", "kafka_probe_fp64_loop_shape_tflops"):
         getattr(lib, name).restype = ctypes.c_double
     lib.kafka_probe_dfma_step_cycles.restype = ctypes.c_double
     lib.kafka_probe_dfma_step_cycles.argtypes = [ctypes.c_int, ctypes.c_int]
@@ -29,6 +29,7 @@ def main():
                            stdout=subprocess.PIPE, text=True)
     res = {"dfma_tflops": lib.kafka_probe_fp64_tflops(5), "dmma_m8n8k4_tflops": lib.kafka_probe_dmma_tflops(5)}
     res["dfma_three_register_operands_tflops"] = lib.kafka_probe_fp64_fma3_tflops(5)
+    res["emulator_loop_operand_mix_tflops"] = lib.kafka_probe_fp64_loop_shape_tflops(5)
     res["dfma_tflops_again"] = lib.kafka_probe_fp64_tflops(5)
     steps = {}
     for warps in (1, 2, 3, 4):

@@ -41,6 +41,57 @@ __global__ void __launch_bounds__(256) fp64_fma3_probe(double* out, int iters, c
     if (s == 123.456) out[0] = s;
 }
 
+// The emulator loop's OPERAND MIX without its dependent chain: per row and pair of pixels 20 dot-product FMAs
+// (row value from a broadcast LDS, pixel state and accumulator from registers: the first pixel's FMA reads three
+// registers, the second reuses the row value), 16 two-operand fp64 instructions standing in for the
+// exponential, 20 accumulations (weight reused, row value and sum from registers) and 2 adds; 16 warps per SM,
+// so latency is hidden and what is measured is how fast the register file and the pipe deliver this mix.
+__global__ void __launch_bounds__(128, 4) fp64_loop_shape_probe(double* out, int rows, const double* __restrict__ tab) {
+    __shared__ __align__(16) double s_tab[64 * 12];
+    for (int k = threadIdx.x; k < 64 * 12; k += 128) s_tab[k] = tab[k];
+    __syncthreads();
+    double x0[10], x1[10], g0[10], g1[10], m0 = 0, m1 = 0;
+#pragma unroll
+    for (int d = 0; d < 10; ++d) {
+        x0[d] = 1e-3 * (threadIdx.x + d);
+        x1[d] = 2e-3 * (threadIdx.x + d) + 1e-4;
+        g0[d] = g1[d] = 0;
+    }
+    for (int j = 0; j < rows; ++j) {
+        const double* row = s_tab + (j & 63) * 12;
+        double z[10];
+#pragma unroll
+        for (int d = 0; d < 10; d += 2) {
+            double2 v = *reinterpret_cast<const double2*>(row + d);
+            z[d] = v.x;
+            z[d + 1] = v.y;
+        }
+        double a0 = row[10], a1 = row[10];
+#pragma unroll
+        for (int d = 0; d < 10; ++d) {
+            a0 = fma(z[d], x0[d], a0);
+            a1 = fma(z[d], x1[d], a1);
+        }
+        double p0 = a0, p1 = a1;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {                  // 8 two-operand fp64 instructions per pixel (3 adds, 3 FMAs with
+            p0 = fma(p0, 0.999, 1e-3);                 // constant coefficients, a multiply, an add in the real loop)
+            p1 = fma(p1, 0.999, 1e-3);
+        }
+#pragma unroll
+        for (int d = 0; d < 10; ++d) {
+            g0[d] = fma(p0, z[d], g0[d]);
+            g1[d] = fma(p1, z[d], g1[d]);
+        }
+        m0 += p0;
+        m1 += p1;
+    }
+    double s = m0 + m1;
+#pragma unroll
+    for (int d = 0; d < 10; ++d) s += g0[d] + g1[d];
+    if (s == 123.456) out[0] = s;
+}
+
 // fp64 tensor-core path: mma.sync m8n8k4 (DMMA), 8 independent accumulator chains per warp
 __global__ void __launch_bounds__(256) fp64_dmma_probe(double* out, int iters, double a, double b) {
     double c[8][2];
@@ -181,6 +232,38 @@ double kafka_probe_dmma_tflops(int reps) {
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     cudaFree(out);
+    return best;
+}
+
+// executed TFLOP/s (2 x 58 fp64 instructions per row and pixel pair) of the loop-shaped probe, best of `reps`
+double kafka_probe_fp64_loop_shape_tflops(int reps) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    double *out = nullptr, *tab = nullptr;
+    if (cudaMalloc(&out, 8) != cudaSuccess || cudaMalloc(&tab, 64 * 12 * 8) != cudaSuccess) return -1.0;
+    double h[64 * 12];
+    for (int k = 0; k < 64 * 12; ++k) h[k] = 1e-3 * ((k * 37) % 101) - 0.05;
+    cudaMemcpy(tab, h, sizeof(h), cudaMemcpyHostToDevice);
+    const int rows = 20000, threads = 128, blocks = sms * 16;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0.0;
+    for (int r = 0; r < reps + 1; ++r) {
+        cudaEventRecord(e0);
+        fp64_loop_shape_probe<<<blocks, threads>>>(out, rows, tab);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double tf = 2.0 * 58 * (double)rows * threads * blocks / (ms * 1e-3) / 1e12;
+        if (r > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    cudaFree(tab);
     return best;
 }
 
