@@ -647,6 +647,143 @@ gp_variance_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, co
     if (lane == 0) var[i] = table[2 * DP] - acc;
 }
 
+// ---- predictive variance with fp64 tensor-core tiles --------------------------------------
+// var_i = s_f - k_i^T Q^-1 k_i for a tile of MT points is the one GEMM-shaped piece of the path
+// ((N x T).(T x T), 2 T^2 flops per point): Y = K Q^-1 with K the MT x T kernel matrix of
+// the tile, then var_i = s_f - sum_n K_in Y_in.  An FMA formulation of it reads three registers per
+// instruction and is held to 2/3 of the fp64 pipe by the register file (benchmarks/probe.cu); the
+// tensor path (mma.sync.m8n8k4.f64, DMMA) takes whole fragments per instruction and is not.
+// CTA = 8 warps.  Phase 1: K (exp of the scaled dot products, as in the linearise kernel) into shared
+// memory, zero padded to a multiple of 8 columns, row stride = 8 mod 16 doubles so that the fragment
+// loads of two rows fall on different bank halves.  Phase 2, per 256 columns of Y: warp w owns 32
+// columns and all MT rows (MT/8 x 4 accumulator tiles); the k index of the fragments is permuted so that
+// a lane fetches its operands of two consecutive mma steps as one pair: k = 8 s + 2 (lane % 4) + {0, 1},
+// the A pair from shared memory, the B pair from Q^-1 read through L1/L2 as Q^-1[n][k] (it is
+// symmetric, so the pair is contiguous).  Q^-1 is streamed once per tile: 8 T^2 / MT bytes per point
+// instead of the 8 T^2 of the one-warp-per-point kernel below.
+__device__ __forceinline__ void dmma_m8n8k4(double (&c)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c[0]), "+d"(c[1])
+                 : "d"(a), "d"(b));
+}
+
+constexpr int kVarThreads = 256;
+__host__ __device__ constexpr int var_cols(int T) { return (T + 7) / 8 * 8; }
+__host__ __device__ constexpr int var_stride(int T) { return (var_cols(T) + 15) / 16 * 16 + 8; }
+
+template <int MT>
+__global__ void __launch_bounds__(kVarThreads, 1)
+gp_variance_mma_kernel(const double* __restrict__ xin, int64_t ld, int64_t n_pts, const double* __restrict__ table, int T,
+                       int D, const double* __restrict__ inv_q, double* __restrict__ var) {
+    constexpr int A = MT / 8;                                   // row tiles per warp
+    extern __shared__ __align__(16) double vs[];                // Ks[MT][TS] | xs[MT][16] | sh[MT] | red[8][MT]
+    __shared__ __align__(16) double s_exp[kExpN];
+    const int Tp = var_cols(T), TS = var_stride(T);
+    const int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
+    double* Ks = vs;
+    double* xs = Ks + (size_t)MT * TS;
+    double* shv = xs + MT * 16;
+    double* red = shv + MT;
+    const int64_t p0 = (int64_t)blockIdx.x * MT;
+    for (int k = threadIdx.x; k < kExpN; k += kVarThreads) s_exp[k] = g_exp2_tab[k];
+    for (int k = threadIdx.x; k < MT * 16; k += kVarThreads) {
+        const int i = k >> 4, d = k & 15;
+        const int64_t p = p0 + i;
+        xs[k] = (d < D && p < n_pts) ? xin[(int64_t)d * ld + p] - table[DP + d] : 0.0;   // padding points sit at the centre
+    }
+    __syncthreads();
+    if (threadIdx.x < MT) {
+        double s = 0.0;
+        for (int d = 0; d < D; ++d) s = fma(table[d] * xs[threadIdx.x * 16 + d], xs[threadIdx.x * 16 + d], s);
+        shv[threadIdx.x] = (-0.5 * kL) * s;
+    }
+    __syncthreads();
+    // phase 1: K_ij = s_f exp(-1/2 |x_i - X_j|^2_theta); consecutive threads take consecutive training points
+    for (int idx = threadIdx.x; idx < MT * Tp; idx += kVarThreads) {
+        const int i = idx / Tp, j = idx - i * Tp;
+        double v = 0.0;
+        if (j < T) {
+            const double* row = table + HDR + (size_t)j * RS;
+            double a = row[DP] + shv[i];
+            for (int d = 0; d < D; ++d) a = fma(row[d], xs[i * 16 + d], a);
+            v = exp_scaled(a, s_exp);
+        }
+        Ks[(size_t)i * TS + j] = v;
+    }
+    __syncthreads();
+
+    // phase 2
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int g = lane >> 2, t4 = lane & 3;
+    double acc[A];
+#pragma unroll
+    for (int i = 0; i < A; ++i) acc[i] = 0.0;
+    for (int nc0 = 0; nc0 < Tp; nc0 += 256) {
+        const int n0 = nc0 + 32 * wid;
+        if (n0 >= Tp) break;                                    // warp-uniform
+        double c[A][4][2];
+#pragma unroll
+        for (int i = 0; i < A; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) c[i][j][0] = c[i][j][1] = 0.0;
+        const double* qrow[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int n = n0 + 8 * j + g;
+            qrow[j] = inv_q + (size_t)(n < T ? n : T - 1) * T;  // columns past T: any finite row, their K is zero
+        }
+        for (int k8 = 0; k8 < Tp; k8 += 8) {
+            const int k = k8 + 2 * t4;
+            double b0[4], b1[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                b0[j] = k < T ? __ldg(qrow[j] + k) : 0.0;
+                b1[j] = k + 1 < T ? __ldg(qrow[j] + k + 1) : 0.0;
+            }
+#pragma unroll
+            for (int i = 0; i < A; ++i) {
+                const double2 av = *reinterpret_cast<const double2*>(Ks + (size_t)(8 * i + g) * TS + k);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    dmma_m8n8k4(c[i][j], av.x, b0[j]);
+                    dmma_m8n8k4(c[i][j], av.y, b1[j]);
+                }
+            }
+        }
+        // var partial: Y_in K_in over this warp's columns (K is zero past T)
+#pragma unroll
+        for (int i = 0; i < A; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int col = n0 + 8 * j + 2 * t4;
+                if (col < Tp) {
+                    const double2 kv = *reinterpret_cast<const double2*>(Ks + (size_t)(8 * i + g) * TS + col);
+                    acc[i] = fma(c[i][j][0], kv.x, acc[i]);
+                    acc[i] = fma(c[i][j][1], kv.y, acc[i]);
+                }
+            }
+    }
+#pragma unroll
+    for (int i = 0; i < A; ++i) {
+        double v = acc[i];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        if (t4 == 0) red[wid * MT + 8 * i + g] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < MT && p0 + threadIdx.x < n_pts) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kVarThreads / 32; ++w) s += red[w * MT + threadIdx.x];      // fixed order
+        var[p0 + threadIdx.x] = table[2 * DP] - s;
+    }
+}
+
+template <int MT>
+static size_t variance_mma_smem(int T) {
+    return ((size_t)MT * var_stride(T) + MT * 16 + MT + (kVarThreads / 32) * MT) * sizeof(double);
+}
+
 template <int D, int PPT>
 static int launch_linearize(const GpLinParams& prm, int n_bands, int max_T, cudaStream_t s) {
     // one row more than the table: the rotated loop fetches the next row's operands on its last trip too
@@ -835,6 +972,22 @@ int kafka_gp_predict(const double* xin, int64_t ld, int64_t n_pts, const double*
     for (int d = 0; d < KAFKA_MAX_DIM; ++d) band.mapper[d] = d;
     int rc = kafka_gp_linearize(xin, ld, n_pts, &band, 1, nullptr, mean, jac, 0u, stream);
     if (rc != 0 || !var) return rc;
+    // tensor-core tiles when the tile's kernel matrix fits shared memory (64 points up to T ~ 340, 32 up to ~ 750)
+    if (!getenv("KAFKA_GP_VARIANCE_NAIVE")) {
+        const size_t s64 = variance_mma_smem<64>(n_train), s32 = variance_mma_smem<32>(n_train);
+        if (s64 <= 180 * 1024) {
+            KAFKA_CUDA(cudaFuncSetAttribute(gp_variance_mma_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s64));
+            gp_variance_mma_kernel<64><<<(unsigned)((n_pts + 63) / 64), kVarThreads, s64, (cudaStream_t)stream>>>(
+                xin, ld, n_pts, table, n_train, n_dim, inv_q, var);
+            return launch_status("gp_variance_mma_kernel");
+        }
+        if (s32 <= 200 * 1024) {
+            KAFKA_CUDA(cudaFuncSetAttribute(gp_variance_mma_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s32));
+            gp_variance_mma_kernel<32><<<(unsigned)((n_pts + 31) / 32), kVarThreads, s32, (cudaStream_t)stream>>>(
+                xin, ld, n_pts, table, n_train, n_dim, inv_q, var);
+            return launch_status("gp_variance_mma_kernel");
+        }
+    }
     size_t smem = (size_t)4 * n_train * sizeof(double);
     KAFKA_CUDA(cudaFuncSetAttribute(gp_variance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     gp_variance_kernel<<<(unsigned)((n_pts + 3) / 4), 128, smem, (cudaStream_t)stream>>>(xin, ld, n_pts, table, n_train,

@@ -71,6 +71,31 @@ def test_predict_variance_and_hessian():
         assert np.max(np.abs(h - hess_o) / _scale(hess_o)) < RTOL
 
 
+@pytest.mark.parametrize("D,T,n", [(3, 5, 7), (4, 33, 65), (10, 250, 1000), (7, 251, 129), (4, 500, 300), (2, 340, 64)])
+def test_variance_tensor_core_tiles_vs_oracle(D, T, n):
+    """kafka_gp_predict's variance through the fp64 tensor-core kernel (64-point tiles up to T ~ 340,
+    32-point tiles beyond), odd and padded sizes, partial tiles: s_f - k^T Q^-1 k against the oracle
+    on the scale of s_f, as the one-warp-per-point kernel is checked above."""
+    rng = np.random.default_rng(1000 * D + T)
+    gp, mean, sigma = _gp(rng, D, T)
+    X = mean + sigma * rng.standard_normal((n, D))
+    X[0] = mean + 50.0 * sigma                                   # a point far from the training set: variance = s_f
+    _, var_o, _ = gp.predict(X, do_unc=True)
+    tab = emulator_table(gp, torch.device(gu.DEV))
+    ld = padded(n)
+    xin = gu.planar(X, ld)
+    mu = torch.empty(ld, dtype=torch.float64, device=gu.DEV)
+    var = torch.full((ld,), float("nan"), dtype=torch.float64, device=gu.DEV)
+    _lib.check(_lib.get_lib().kafka_gp_predict(_lib.ptr(xin), ld, n, _lib.ptr(tab.table), T, D, _lib.ptr(tab.inv_q()),
+                                               _lib.ptr(mu), None, _lib.ptr(var), gu.stream()), "predict")
+    v = var[:n].cpu().numpy()
+    s_f = np.exp(gp.theta[D])
+    assert np.isfinite(v).all()
+    assert np.max(np.abs(v - var_o)) < 1e-8 * s_f
+    assert abs(v[0] - s_f) < 1e-9 * s_f
+    assert torch.isnan(var[n:]).all()                            # nothing written past the last point
+
+
 def test_exp_underflow_and_far_points():
     """Inputs far from every training point: kernel values underflow to 0 (not NaN)."""
     rng = np.random.default_rng(12)
