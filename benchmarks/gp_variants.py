@@ -16,31 +16,20 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(ROOT, "kafka_inferenceengine_b200", "csrc")
 OUT = os.path.join(HERE, "variants")
+# Variants whose code is still in csrc/gp.cu.  Round 2 also measured -- and removed from the source, see
+# profiles/r02_gp_variants.txt and the git history -- a fully rotated loop, split dot products, a 16x
+# replicated (conflict-free) exponent table, one pixel per thread at 4-6 CTAs per SM.
 VARIANTS = {
     "default": [],
-    # round 2: what separates 73 % fp64-pipe activity from 100 %?
-    "rot": ["-DKAFKA_GP_ROTATE=1"],                                   # next row's operands fetched behind the G sums
-    "split": ["-DKAFKA_GP_SPLIT_DOT=1"],                              # two half-length dot-product chains per pixel
-    "split_rot": ["-DKAFKA_GP_SPLIT_DOT=1", "-DKAFKA_GP_ROTATE=1"],
-    "insfirst": ["-DKAFKA_EXP_INSERT_FIRST=1"],                       # exponent + sign into the table value, before the multiply
-    "prehead": ["-DKAFKA_GP_PREFETCH_HEAD=1"],                        # {e2, sgn, zh[0..1]} of the next row fetched a trip early
-    "insfirst_prehead": ["-DKAFKA_EXP_INSERT_FIRST=1", "-DKAFKA_GP_PREFETCH_HEAD=1"],
-    "ppt3_mb3": ["-DKAFKA_GP_PPT_BIG=3", "-DKAFKA_GP_MINBLOCKS=3"],
-    "t224_mb2": ["-DKAFKA_GP_THREADS=224", "-DKAFKA_GP_MINBLOCKS=2"],     # 14 warps per SM at <= 144 registers
-    "t448_mb1": ["-DKAFKA_GP_THREADS=448", "-DKAFKA_GP_MINBLOCKS=1"],     # the same as one CTA (table staged once per SM)
-    "t192_mb2": ["-DKAFKA_GP_THREADS=192", "-DKAFKA_GP_MINBLOCKS=2"],     # 12 warps as two CTAs, <= 168 registers
-    "t416_mb1": ["-DKAFKA_GP_THREADS=416", "-DKAFKA_GP_MINBLOCKS=1"],     # 13 warps, <= 152 registers
-    "tab256": ["-DKAFKA_EXP_LOG2N=8"],
-    "repl256": ["-DKAFKA_EXP_LOG2N=8", "-DKAFKA_EXP_REPL=16"],        # conflict-free 2^(k/256) look-ups, degree 4
-    "ppt1_mb5": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=5"],  # one pixel per thread, 20 warps per SM
-    "ppt1_mb5_split": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=5", "-DKAFKA_GP_SPLIT_DOT=1"],
-    "ppt1_mb6": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=6"],
-    "ppt1_mb4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=4"],
-    # round 1 (kept for the record; see DESIGN.md section 3.1 for their results)
+    "no_insfirst": ["-DKAFKA_EXP_INSERT_FIRST=0"],                    # exponent + sign inserted after the multiply
+    "no_prehead": ["-DKAFKA_GP_PREFETCH_HEAD=0"],                     # row head operands fetched at the top of the trip
+    "tab256": ["-DKAFKA_EXP_LOG2N=8"],                                # 256-entry table + degree-4 polynomial
+    "checked": ["-DKAFKA_EXP_CLAMP=0"],
     "u4": ["-DKAFKA_GP_UNROLL=4"],
     "t256": ["-DKAFKA_GP_THREADS=256"],
-    "checked": ["-DKAFKA_EXP_CLAMP=0"],
-    "u1_mb4": ["-DKAFKA_GP_UNROLL=1", "-DKAFKA_GP_MINBLOCKS=4"],
+    "t192_mb2": ["-DKAFKA_GP_THREADS=192", "-DKAFKA_GP_MINBLOCKS=2"],
+    "t224_mb2": ["-DKAFKA_GP_THREADS=224", "-DKAFKA_GP_MINBLOCKS=2"],
+    "ppt1_mb4": ["-DKAFKA_GP_FORCE_PPT=1", "-DKAFKA_GP_MINBLOCKS=4"],
     "ppt3": ["-DKAFKA_GP_PPT_BIG=3"],
     "ppt4": ["-DKAFKA_GP_PPT_BIG=4"],
 }

@@ -67,9 +67,7 @@ extern "C" {
                                    (kafka/inference/utils.py:193-195)                  */
 #define KAFKA_PRIOR_BROADCAST 2u /* pinv_f is ONE packed block shared by all pixels    */
 #define KAFKA_SOLVE_PAIR 4u       /* kafka_solve_bands: use the two-lanes-per-pixel kernel at any size
-                                    (default from 14 parameters when a band is LINEAR or WCM; for tests) */
-#define KAFKA_SOLVE_QUAD 8u       /* kafka_solve_bands: use the four-lanes-per-pixel kernel at any size
-                                    (default from 13 parameters for array / shared-linearisation bands; for tests) */
+                                    (the default from 14 parameters; for tests) */
 
 const char* kafka_last_error(void);
 int kafka_version(void);

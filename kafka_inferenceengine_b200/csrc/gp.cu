@@ -39,15 +39,6 @@ namespace kafka {
 #ifndef KAFKA_EXP_CLAMP
 #define KAFKA_EXP_CLAMP 1
 #endif
-// copies of the 2^(k/N) table in shared memory, interleaved entry-major: lane l reads copy l mod R, so
-// with R = 16 the 16 lanes of a half-warp always hit 16 different bank pairs (no replays whatever the
-// exponents are); R = 1 is the plain table, where 16 random 8-byte reads collide ~3 deep
-#ifndef KAFKA_EXP_REPL
-#define KAFKA_EXP_REPL 1
-#endif
-#ifndef KAFKA_GP_SPLIT_DOT
-#define KAFKA_GP_SPLIT_DOT 0
-#endif
 // both measured on B200 (profiles/r02_gp_variants.txt): 0.45 % and 0.85 %, 1.35 % together
 #ifndef KAFKA_EXP_INSERT_FIRST
 #define KAFKA_EXP_INSERT_FIRST 1
@@ -57,7 +48,6 @@ namespace kafka {
 #endif
 constexpr int kExpLog2N = KAFKA_EXP_LOG2N;
 constexpr int kExpN = 1 << kExpLog2N;
-constexpr int kExpRepl = KAFKA_EXP_REPL;
 // in global memory (not __constant__): every CTA copies it to shared memory, and constant
 // loads at 32 different addresses per warp would serialise
 __device__ __align__(16) const double g_exp2_tab[kExpN] = {
@@ -113,13 +103,12 @@ struct ExpPart {
     int k;          // rint(a)
 };
 
-template <int kRepl = 1>
 __device__ __forceinline__ ExpPart exp_lookup(double a, const double* __restrict__ tab) {
     ExpPart e;
     const double t = a + c_exp_poly[5];              // magic-number add: rint(a) in the low word (F2I/I2F measured slower)
     e.k = __double2loint(t);
     e.r = a - (t - c_exp_poly[5]);
-    e.tv = tab[(e.k & (kExpN - 1)) * kRepl];         // kRepl > 1: tab already points at this lane's copy
+    e.tv = tab[e.k & (kExpN - 1)];
     return e;
 }
 
@@ -163,9 +152,9 @@ __device__ __forceinline__ double exp_finish(const ExpPart& e, double a, int sgn
     }
 }
 
-template <bool kChecked = true, int kRepl = 1>
+template <bool kChecked = true>
 __device__ __forceinline__ double exp_scaled(double a, const double* __restrict__ tab) {
-    return exp_finish<kChecked>(exp_lookup<kRepl>(a, tab), a);
+    return exp_finish<kChecked>(exp_lookup(a, tab), a);
 }
 
 // ---- linearise: mean + Jacobian for every (pixel, band) -------------------------
@@ -241,21 +230,11 @@ __device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, i
 #pragma unroll
         for (int pp = 0; pp < PPT; ++pp) {
             a[pp] = kShiftInside ? ea.x + sh[pp] : ea.x;
-            if constexpr (KAFKA_GP_SPLIT_DOT && D >= 4) {
-                // two half-length chains per pixel (one more add): twice the independent work per warp
-                double a1 = zh[1] * xr[pp][1];
 #pragma unroll
-                for (int d = 0; d < D; d += 2) a[pp] = fma(zh[d], xr[pp][d], a[pp]);
-#pragma unroll
-                for (int d = 3; d < D; d += 2) a1 = fma(zh[d], xr[pp][d], a1);
-                a[pp] += a1;
-            } else {
-#pragma unroll
-                for (int d = 0; d < D; ++d) a[pp] = fma(zh[d], xr[pp][d], a[pp]);
-            }
+            for (int d = 0; d < D; ++d) a[pp] = fma(zh[d], xr[pp][d], a[pp]);
         }
 #pragma unroll
-        for (int pp = 0; pp < PPT; ++pp) ep[pp] = exp_lookup<kExpRepl>(a[pp], tab64);
+        for (int pp = 0; pp < PPT; ++pp) ep[pp] = exp_lookup(a[pp], tab64);
 #pragma unroll
         for (int pp = 0; pp < PPT; ++pp) {
             const double w = exp_finish<kShiftInside || !KAFKA_EXP_CLAMP>(ep[pp], a[pp], sgn);  // = k_j alpha_j / exp(cbar)
@@ -270,72 +249,13 @@ __device__ __forceinline__ void gp_accumulate(const double* __restrict__ rows, i
     }
 }
 
-// Same loop with the NEXT row's operands fetched while the current row's G sums are formed: as
-// soon as the fused multiply-adds that read zh[d], zh[d+1] (of every pixel of the thread) have
-// been issued, those registers take the next row's values, so the shared-memory latency of a row
-// hides behind the ~40 FMAs of the previous row's tail instead of stalling the first FMA of its
-// own dot product -- no register more than the plain loop.  Reads one row past the table on the
-// last trip (the launch allocates that row; its values are never used).
-template <int D, int PPT, bool kShiftInside>
-__device__ __forceinline__ void gp_accumulate_rot(const double* __restrict__ rows, int T, const double (&xr)[PPT][D],
-                                                  const double (&sh)[PPT], double (&mu)[PPT], double (&G)[PPT][D],
-                                                  const double* __restrict__ tab64) {
-    constexpr int DP = dpad(D), RS = tab_row(D);
-    const double* const rows_end = rows + (size_t)T * RS;
-    double zh[DP];
-#pragma unroll
-    for (int d = 0; d < DP; d += 2) {
-        double2 v = *reinterpret_cast<const double2*>(rows + d);
-        zh[d] = v.x;
-        zh[d + 1] = v.y;
-    }
-    double2 ea = *reinterpret_cast<const double2*>(rows + DP + 2);       // {e2, sgn}
-#pragma unroll 1
-    for (const double* row = rows; row != rows_end; row += RS) {
-        const int sgn = __double2loint(ea.y);
-        double a[PPT];
-        ExpPart ep[PPT];
-#pragma unroll
-        for (int pp = 0; pp < PPT; ++pp) {
-            a[pp] = kShiftInside ? ea.x + sh[pp] : ea.x;
-#pragma unroll
-            for (int d = 0; d < D; ++d) a[pp] = fma(zh[d], xr[pp][d], a[pp]);
-        }
-        ea = *reinterpret_cast<const double2*>(row + RS + DP + 2);
-#pragma unroll
-        for (int pp = 0; pp < PPT; ++pp) ep[pp] = exp_lookup<kExpRepl>(a[pp], tab64);
-        double w[PPT];
-#pragma unroll
-        for (int pp = 0; pp < PPT; ++pp) {
-            w[pp] = exp_finish<kShiftInside || !KAFKA_EXP_CLAMP>(ep[pp], a[pp], sgn);
-            mu[pp] += w[pp];
-        }
-#pragma unroll
-        for (int d = 0; d < DP; d += 2) {
-#pragma unroll
-            for (int pp = 0; pp < PPT; ++pp) {
-                if (d < D) G[pp][d] = fma(w[pp], zh[d], G[pp][d]);
-                if (d + 1 < D) G[pp][d + 1] = fma(w[pp], zh[d + 1], G[pp][d + 1]);
-            }
-            double2 v = *reinterpret_cast<const double2*>(row + RS + d);
-            zh[d] = v.x;
-            zh[d + 1] = v.y;
-        }
-    }
-}
-
-#ifndef KAFKA_GP_ROTATE
-#define KAFKA_GP_ROTATE 0
-#endif
-
 template <int D, int PPT>
 __global__ void __launch_bounds__(kGpThreads, (KAFKA_GP_MINBLOCKS == 1 && PPT == 2 && D <= 10 && KAFKA_GP_THREADS == 128) ? 3 : KAFKA_GP_MINBLOCKS)
 gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     constexpr int DP = dpad(D), HDR = tab_hdr(D), RS = tab_row(D);
     extern __shared__ __align__(16) double smem[];
     __shared__ uint64_t bar;
-    __shared__ __align__(16) double s_exp_store[kExpN * kExpRepl];
-    const double* const s_exp = s_exp_store + (kExpRepl > 1 ? (threadIdx.x & (kExpRepl - 1)) : 0);
+    __shared__ __align__(16) double s_exp[kExpN];
 
     // band is the FAST grid index: the CTAs of all bands of one pixel tile run together, so
     // the tile's state is fetched from HBM once and served to the other bands by L2
@@ -348,12 +268,8 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
     if (threadIdx.x == 0) mbar_init(&bar, 1);
     __syncthreads();
     if (threadIdx.x == 0) {
-        if constexpr (kExpRepl == 1) {
-            mbar_expect_tx(&bar, bytes + (uint32_t)sizeof(s_exp_store));
-            tma_bulk_g2s(s_exp_store, g_exp2_tab, (uint32_t)sizeof(s_exp_store), &bar);
-        } else {
-            mbar_expect_tx(&bar, bytes);
-        }
+        mbar_expect_tx(&bar, bytes + (uint32_t)sizeof(s_exp));
+        tma_bulk_g2s(s_exp, g_exp2_tab, (uint32_t)sizeof(s_exp), &bar);
         constexpr uint32_t kChunk = 16384;
         for (uint32_t off = 0; off < bytes; off += kChunk)
             tma_bulk_g2s(reinterpret_cast<char*>(smem) + off, reinterpret_cast<const char*>(band.table) + off,
@@ -377,10 +293,6 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
             xr[pp][d] = in ? prm.x[(int64_t)band.mapper[d] * prm.ld + pix[pp]] : 0.0;
     }
 
-    if constexpr (kExpRepl > 1) {
-        for (int k = threadIdx.x; k < kExpN * kExpRepl; k += kGpThreads) s_exp_store[k] = g_exp2_tab[k / kExpRepl];
-        __syncthreads();
-    }
     mbar_wait(&bar, 0);
 
     const double* theta_e = smem;
@@ -410,10 +322,7 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
         // common case: exp(sh) is applied after the loop; a warp with a far-away pixel keeps
         // sh inside the exponent so that nothing can overflow
         if (!__any_sync(0xffffffffu, far)) {
-            if constexpr (KAFKA_GP_ROTATE)
-                gp_accumulate_rot<D, PPT, false>(rows, T, xr, sh, mu, G, s_exp);
-            else
-                gp_accumulate<D, PPT, false>(rows, T, xr, sh, mu, G, s_exp);
+            gp_accumulate<D, PPT, false>(rows, T, xr, sh, mu, G, s_exp);
             // L * mean ln|alpha|, taken out of every row's exponent (read here, not before the loop: more
             // registers live across it push the polynomial's constants back into the loop)
             const double lcbar = smem[2 * DP + 3];
@@ -424,14 +333,14 @@ gp_linearize_kernel(const __grid_constant__ GpLinParams prm) {
                 double s2 = 0.0;
 #pragma unroll
                 for (int d = 0; d < D; ++d) s2 = fma(theta_e[d] * xr[pp][d], xr[pp][d], s2);
-                const double scale = exp_scaled<true, kExpRepl>((-0.5 * kL) * s2 + lcbar, s_exp);
+                const double scale = exp_scaled((-0.5 * kL) * s2 + lcbar, s_exp);
                 mu[pp] *= scale;
 #pragma unroll
                 for (int d = 0; d < D; ++d) G[pp][d] *= scale;
             }
         } else {
             gp_accumulate<D, PPT, true>(rows, T, xr, sh, mu, G, s_exp);
-            const double scale = exp_scaled<true, kExpRepl>(smem[2 * DP + 3], s_exp);
+            const double scale = exp_scaled(smem[2 * DP + 3], s_exp);
 #pragma unroll
             for (int pp = 0; pp < PPT; ++pp) {
                 mu[pp] *= scale;

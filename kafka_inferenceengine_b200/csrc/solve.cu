@@ -339,7 +339,6 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
 
 }  // namespace kafka
 #include "solve_pair.cuh"
-#include "solve_quad.cuh"
 namespace kafka {
 
 // Fixed-order second stage: same bits every run, whatever the launch order.
@@ -502,28 +501,6 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
     // the lane-sharing kernels run 64 pixels per CTA: two CTAs add into one scratch slot
     const unsigned grid_half = (unsigned)((n_pix + kSolveThreads / 2 - 1) / (kSolveThreads / 2));
     int rc = KAFKA_E_UNSUPPORTED;
-    bool quad_kinds = true;                 // the four-lane kernel knows per-pixel arrays and shared linearisations
-    for (int b = 0; b < n_bands; ++b)
-        quad_kinds = quad_kinds && (prm.bands[b].kind == KAFKA_BAND_ARRAYS || prm.bands[b].kind == KAFKA_BAND_UNIFORM);
-    if (quad_kinds && !(flags & KAFKA_SOLVE_PAIR) && (n_params >= kQuadFromParams || (flags & KAFKA_SOLVE_QUAD))) {
-        bool all_identity_quad = n_bands > 0;
-        for (int b = 0; b < n_bands; ++b) all_identity_quad = all_identity_quad && prm.bands[b].identity;
-        KAFKA_DISPATCH_P(n_params, {
-            auto kern = all_identity_quad ? solve_bands_quad_kernel<kP, true> : solve_bands_quad_kernel<kP, false>;
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ring / 2));
-            if (e == cudaSuccess) e = cudaMemsetAsync(scratch, 0, 2 * (size_t)grid * sizeof(double), s);
-            if (e != cudaSuccess) {
-                set_error("launch set-up failed: %s", cudaGetErrorString(e));
-                rc = (int)e;
-            } else {
-                kern<<<grid_half, kQuadThreads, ring / 2, s>>>(prm, n_dim_max);
-                rc = launch_status("solve_bands_quad_kernel");
-            }
-        });
-        if (rc != 0) return rc;
-        reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
-        return launch_status("reduce_partials_kernel");
-    }
     if (n_params >= kPairFromParams || (flags & KAFKA_SOLVE_PAIR)) {
         bool all_identity_pair = n_bands > 0;
         for (int b = 0; b < n_bands; ++b) all_identity_pair = all_identity_pair && prm.bands[b].identity;

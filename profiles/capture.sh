@@ -2,7 +2,7 @@
 # Profile capture for one round (run on the GPU box through gpurun, one GPU):
 #   bash profiles/capture.sh launches   -> gpurun_out/launches_default.csv (per-launch durations of the DEFAULT bench command)
 #   bash profiles/capture.sh full       -> gpurun_out/prof.ncu-rep   (ncu --set full of the hot kernels, 200-row shard)
-#   bash profiles/capture.sh lanes      -> gpurun_out/lanes.ncu-rep  (the two- and four-lanes-per-pixel solve kernels, P=16)
+#   bash profiles/capture.sh lanes      -> gpurun_out/lanes_4_*.csv  (the two-lanes-per-pixel solve kernel, P=16)
 # Each ncu pass only starts after the identical command has exited 0 without ncu.  The reports are turned into
 # CSV pages on the box (raw metrics + per-instruction source page) and removed: gpurun brings back 64 MiB at most.
 set -e
@@ -19,9 +19,9 @@ if [ "$1" = "launches" ]; then
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_default.csv $CMD > gpurun_out/ncu_launches_default.log 2>&1
 elif [ "$1" = "lanes" ]; then
   export KAFKA_C5_PARAMS=16 KAFKA_C5_PIXELS=1e6
-  for f in 4 8; do
+  for f in 4; do
     KAFKA_C5_FLAGS=$f python bench.py --workload c5 --no-cpu-baseline > gpurun_out/plain_lanes_$f.json
-    KAFKA_C5_FLAGS=$f ncu --set full --clock-control none --import-source on -k regex:'solve_bands_(pair|quad)_kernel' -s 12 -c 1 -f -o gpurun_out/lanes_$f \
+    KAFKA_C5_FLAGS=$f ncu --set full --clock-control none --import-source on -k regex:'solve_bands_pair_kernel' -s 12 -c 1 -f -o gpurun_out/lanes_$f \
       python bench.py --workload c5 --no-cpu-baseline > gpurun_out/ncu_lanes_$f.log 2>&1
     export_rep gpurun_out/lanes_$f
   done

@@ -5,7 +5,7 @@
 # sizes the tools finish in minutes; pytest runs inside the tool, so every kernel the tests launch is checked.
 OUT=${1:-gpurun_out}
 SEL='tests/test_gpu_layout.py tests/test_gpu_advance.py tests/test_gpu_read_small.py tests/test_gpu_assimilate_iter.py tests/test_zz_no_alloc.py'
-SOLVE='tests/test_gpu_solve.py -k "(all_state_sizes and (3- or 10- or 13- or 16-)) or quad_kernel or mapper_linear or non_positive"'
+SOLVE='tests/test_gpu_solve.py -k "(all_state_sizes and (3- or 10- or 13- or 16-)) or pair_kernel or mapper_linear or non_positive"'
 GP='tests/test_gpu_gp.py -k "predict_mean_jacobian and (4-120 or 10-250) or underflow or linearize_bands_mask and (127 or 4095)"'
 for tool in memcheck racecheck; do
   log=$OUT/r02_sanitizer_$tool.txt

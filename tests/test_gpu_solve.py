@@ -92,11 +92,11 @@ def _call(n, P, bands, x_prev, x_f, pinv_t, flags=0, want_fwd=True):
             fwd[:B, :n].cpu().numpy().ravel(), float(norm2.item()), int(n_bad.item()))
 
 
-@pytest.mark.parametrize("pair", [0, _lib.SOLVE_PAIR, _lib.SOLVE_QUAD])
+@pytest.mark.parametrize("pair", [0, _lib.SOLVE_PAIR])
 @pytest.mark.parametrize("P", list(range(1, 17)))
 def test_supplied_jacobian_all_state_sizes(P, pair):
     """Config 5 sweep axis n_params 1..16 (x bands 1..13); ``pair`` forces the two-lanes-per-pixel
-    or the four-lanes-per-pixel kernel (the default from 13 parameters) at every size."""
+    kernel (the default from 14 parameters) at every size."""
     rng = np.random.default_rng(P)
     B = 1 + (5 * P) % 13
     n = 1500 + 37 * P
@@ -113,7 +113,7 @@ def test_supplied_jacobian_all_state_sizes(P, pair):
     assert norm2 == pytest.approx(float(((xo - x_prev) ** 2).sum()), rel=1e-9)
 
 
-@pytest.mark.parametrize("P,flags", [(7, 0), (7, _lib.SOLVE_PAIR), (15, 0), (6, _lib.SOLVE_QUAD), (16, 0),
+@pytest.mark.parametrize("P,flags", [(7, 0), (7, _lib.SOLVE_PAIR), (15, 0), (16, 0),
                                      (15, _lib.SOLVE_PAIR)])
 def test_norm_is_deterministic_and_edge_sizes(P, flags):
     rng = np.random.default_rng(99)
@@ -170,11 +170,11 @@ def test_pair_kernel_on_uniform_linear_and_wcm_bands(P):
 
 
 @pytest.mark.parametrize("P", [3, 7, 14, 16])
-def test_quad_kernel_on_shared_linearisation_mapped_arrays_and_broadcast_prior(P):
-    """The four-lanes-per-pixel kernel on the band kinds it knows: a shared linearisation
-    (KAFKA_BAND_UNIFORM) on some state slots, per-pixel arrays through a state mapper, per-pixel arrays
-    on every slot; per-pixel prior blocks and one block shared by all pixels.  Same results as the
-    one-thread kernel (same operations in the same order) and as the oracle."""
+def test_pair_kernel_on_shared_linearisation_mapped_arrays_and_broadcast_prior(P):
+    """The two-lanes-per-pixel kernel on a shared linearisation (KAFKA_BAND_UNIFORM) on some state slots,
+    per-pixel arrays through a state mapper and per-pixel arrays on every slot, with per-pixel prior
+    blocks and with one block shared by all pixels.  Same results as the one-thread kernel (same
+    operations in the same order) and as the oracle."""
     rng = np.random.default_rng(70 + P)
     n = 1237
     m = [rng.random(n) < 0.8 for _ in range(3)]
@@ -202,7 +202,7 @@ def test_quad_kernel_on_shared_linearisation_mapped_arrays_and_broadcast_prior(P
     cases = [(gu.pack_blocks(Pinv), Pinv, 0),
              (torch.from_numpy(np.ascontiguousarray(one[r, c])).to(gu.DEV), np.repeat(one[None], n, axis=0), _lib.PRIOR_BROADCAST)]
     for packed, blocks, extra in cases:
-        res = [_call(n, P, bands, x_prev, x_f, packed, flags=f | extra) for f in (0, _lib.SOLVE_QUAD)]
+        res = [_call(n, P, bands, x_prev, x_f, packed, flags=f | extra) for f in (0, _lib.SOLVE_PAIR)]
         assert np.allclose(res[0][0], res[1][0], rtol=1e-11, atol=1e-13)
         assert np.array_equal(res[0][1], res[1][1]) and np.array_equal(res[0][2], res[1][2])
         assert np.allclose(res[0][3], res[1][3], rtol=1e-11, atol=1e-12)
@@ -268,7 +268,7 @@ def test_mapper_linear_and_broadcast_prior(pair):
     assert np.allclose(fwd, fwd_o, rtol=1e-9, atol=1e-10)
 
 
-@pytest.mark.parametrize("P,flags", [(4, 0), (4, _lib.SOLVE_PAIR), (13, 0), (5, _lib.SOLVE_QUAD), (16, 0),
+@pytest.mark.parametrize("P,flags", [(4, 0), (4, _lib.SOLVE_PAIR), (13, 0), (16, 0),
                                      (13, _lib.SOLVE_PAIR)])
 def test_non_positive_definite_blocks_are_flagged(P, flags):
     rng = np.random.default_rng(8)
