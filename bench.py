@@ -54,6 +54,8 @@ def parse():
                     help="side of the square chunks the CPU legs hand to the reference (<= 256, its drivers' practice)")
     ap.add_argument("--port-sample", type=int, default=65536, help="pixels the numpy port is timed on (cpu_baseline.port)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true",
+                    help="leave configs2_modis_c3 / configs4_sweep_c5 out of the default line")
     ap.add_argument("--host-sources", default="pinned", choices=["pinned", "pageable"],
                     help="memory the e2e legs' host rasters live in (see e2e.api)")
     ap.add_argument("--comm", default="native", choices=["native", "torch"],
@@ -499,7 +501,7 @@ def _hbm_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def run_c3(args):
+def run_c3(args, ctx=None):
     """BASELINE configs[2]: MODIS tile 2400 x 2400 (5.76 M px) per GPU, 7-parameter TIP state, 2 broadbands
     through per-band state mappers (D=4, T=500), --c3-days daily steps (365) with an observation every 8th
     day, propagate_information_filter_LAI with Q[6::7] = 0.04 (kafka_test.py:156-217,
@@ -512,7 +514,7 @@ def run_c3(args):
     from kafka_inferenceengine_b200.device import DeviceVector
     from kafka_inferenceengine_b200.inference.utils import emulator_table, linearize_bands
     from kafka_inferenceengine_b200.output import RasterOutput
-    world, rank, local, device, comm, barrier, max_over_ranks = _dist_setup(args)
+    world, rank, local, device, comm, barrier, max_over_ranks = ctx or _dist_setup(args)
     base = dt.datetime(2017, 1, 1)
     ny = nx = args.c3_side
     N = ny * nx
@@ -593,11 +595,10 @@ def run_c3(args):
         assert ex < 1e-6 and ed < 1e-6, (ex, ed)
         parity = {"pixels": ns, "date": 0, "solves": iters[0], "max_rel_err_x": ex, "max_rel_err_diag": ed,
                   "against": "oracle B (fp64), same number of solves"}
-    if rank == 0:
-        adv_bytes = N * (24 + 8 * 7 + 4 * 7 * 8)
-        hbm, _ = _hbm_peak()
-        emit(json.dumps({
-            "workload": "c3: MODIS tile %dx%d (%.2f M px) per GPU, TIP P=7, B=2 (D=4, T=500), %d daily steps, "
+    if rank != 0:
+        return None
+    adv_bytes = N * (24 + 8 * 7 + 4 * 7 * 8)
+    return {"workload": "c3: MODIS tile %dx%d (%.2f M px) per GPU, TIP P=7, B=2 (D=4, T=500), %d daily steps, "
                         "observations every 8th day (%d dates), LAI propagator with Q[6::7]=0.04; one "
                         "LinearKalman.run(): host rasters in on observation days (%s), float32 mean/uncertainty "
                         "rasters read back EVERY day" % (ny, nx, N / 1e6, n_steps, len(dates), args.host_sources),
@@ -606,10 +607,7 @@ def run_c3(args):
             "pixel_dates_per_s": world * N * len(dates) / (ms * 1e-3), "iterations": iters,
             "h2d_bytes_per_run": kf._stager.h2d_bytes - h2d0, "d2h_bytes_per_run": out.d2h_bytes - d2h0,
             "d2h_gbs_per_rank": (out.d2h_bytes - d2h0) / (ms * 1e-3) / 1e9,
-            "advance_algorithmic_bytes_per_step": adv_bytes, "clocks": clocks, "parity": parity}))
-    if world > 1:
-        import torch.distributed as dist
-        dist.destroy_process_group()
+            "advance_algorithmic_bytes_per_step": adv_bytes, "clocks": clocks, "parity": parity}
 
 
 C5_BANDS = (1, 4, 10, 13)
@@ -644,7 +642,7 @@ def _c5_cpu_chunk(args):
     return ref_runner.time_supplied_jacobian_solve(Pn, Bn, side, seed)
 
 
-def run_c5(args):
+def run_c5(args, ctx=None, params=None, sizes=None, bands=None, cpu_arm=True):
     """BASELINE configs[4]: batched update with SUPPLIED Jacobians (the solve kernels alone), n_params 2-16 x
     bands {1,4,10,13} x pixels 1e4..1e8 (or what fits in memory) per GPU; with --gpus N every rank solves its
     own pixel range and the convergence norm is all-reduced after every launch, as do_all_bands does."""
@@ -652,11 +650,12 @@ def run_c5(args):
     import torch.distributed as dist
     from kafka_inferenceengine_b200 import _lib
     from kafka_inferenceengine_b200.device import padded, tri_count
-    world, rank, local, device, comm, barrier, max_over_ranks = _dist_setup(args)
+    world, rank, local, device, comm, barrier, max_over_ranks = ctx or _dist_setup(args)
     lib = _lib.get_lib()
     hbm, peak_src = _hbm_peak()
-    params = [int(v) for v in os.environ.get("KAFKA_C5_PARAMS", ",".join(str(k) for k in range(2, 17))).split(",")]
-    sizes = [int(float(v)) for v in os.environ.get("KAFKA_C5_PIXELS", "1e4,1e5,1e6,1e7,1e8").split(",")]
+    params = params or [int(v) for v in os.environ.get("KAFKA_C5_PARAMS", ",".join(str(k) for k in range(2, 17))).split(",")]
+    sizes = sizes or [int(float(v)) for v in os.environ.get("KAFKA_C5_PIXELS", "1e4,1e5,1e6,1e7,1e8").split(",")]
+    bands = bands or C5_BANDS
     # KAFKA_C5_FLAGS: kafka_solve_bands flags, e.g. 4 / 8 to force the two- / four-lanes-per-pixel kernel
     c5_flags = int(os.environ.get("KAFKA_C5_FLAGS", "0")) | (_lib.SOLVE_PAIR if os.environ.get("KAFKA_C5_PAIR") else 0)
     budget = float(os.environ.get("KAFKA_C5_MEM_GB", "120")) * 1e9
@@ -676,7 +675,7 @@ def run_c5(args):
     for n_req in sizes:
         for Pn in params:
             Lp = tri_count(Pn)
-            for Bn in C5_BANDS:
+            for Bn in bands:
                 bytes_pp = 16 * Pn + 8 * Pn * (Pn + 1) + 8 * Pn + Bn * 8 * (3 + Pn)   # x_f,x_prev,x ; Pinv in + A out ; bands
                 n = int(min(n_req, budget // bytes_pp // 1024 * 1024))
                 if n < n_req and any(r["n_params"] == Pn and r["n_bands"] == Bn and r["pixels"] == n for r in rows):
@@ -746,35 +745,38 @@ def run_c5(args):
                 del J, h0, y, w, xp, xf, pinv, xo, ao, scratch
         torch.cuda.empty_cache()
     clocks = sampler.stop() if sampler else None
-    if rank == 0:
-        line = {"workload": "c5: batched update with supplied Jacobians, per-pixel prior blocks: n_params %s x bands %s x "
-                            "pixels %s per GPU (capped at what fits %d GB)" % (params, list(C5_BANDS), sizes, budget / 1e9),
-                "metric": "pixels/sec", "n_gpus": world, "scaling": "weak", "hbm_peak": hbm, "peak_source": peak_src,
-                "algorithmic_bytes_per_pixel": "16P + 8P(P+1) + 8P + B*8*(3+P)", "rows": rows, "clocks": clocks,
-                "parity": {"checked": "first 512 pixels of every (n_params, bands) at the smallest size vs oracle B",
-                           "max_rel_err_x": parity_worst}}
-        if world == 1 and not args.no_cpu_baseline:
-            cores = os.cpu_count() or 1
-            cpu_params = [int(v) for v in os.environ.get("KAFKA_C5_CPU_PARAMS", "2,7,10,16").split(",")]
-            line["cpu_arm"] = {"what": "unmodified reference variational_kalman_multiband (scipy sparse build + float32 "
-                                       "SuperLU, kafka/inference/solvers.py:100-145), supplied Jacobians, chunks of 128x128 px; "
-                                       "rates per pixel, EXTRAPOLATED linearly to the sweep's pixel counts (SuperLU runs "
-                                       "out of memory at 1e6 px in one piece, SURVEY section 6)",
-                               "kind": "reference" if _reference_installed() else "unavailable",
-                               "rows": _c5_cpu_arm(cpu_params, C5_BANDS, min(cores, 64)) if _reference_installed() else []}
-        emit(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    if rank != 0:
+        return None
+    line = {"workload": "c5: batched update with supplied Jacobians, per-pixel prior blocks: n_params %s x bands %s x "
+                        "pixels %s per GPU (capped at what fits %d GB)" % (params, list(bands), sizes, budget / 1e9),
+            "metric": "pixels/sec", "n_gpus": world, "scaling": "weak", "hbm_peak": hbm, "peak_source": peak_src,
+            "algorithmic_bytes_per_pixel": "16P + 8P(P+1) + 8P + B*8*(3+P)", "rows": rows, "clocks": clocks,
+            "parity": {"checked": "first 512 pixels of every (n_params, bands) at the smallest size vs oracle B",
+                       "max_rel_err_x": parity_worst}}
+    if world == 1 and cpu_arm and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        cpu_params = [int(v) for v in os.environ.get("KAFKA_C5_CPU_PARAMS", "2,7,10,16").split(",")]
+        line["cpu_arm"] = {"what": "unmodified reference variational_kalman_multiband (scipy sparse build + float32 "
+                                   "SuperLU, kafka/inference/solvers.py:100-145), supplied Jacobians, chunks of 128x128 px; "
+                                   "rates per pixel, EXTRAPOLATED linearly to the sweep's pixel counts (SuperLU runs "
+                                   "out of memory at 1e6 px in one piece, SURVEY section 6)",
+                           "kind": "reference" if _reference_installed() else "unavailable",
+                           "rows": _c5_cpu_arm(cpu_params, bands, min(cores, 64)) if _reference_installed() else []}
+    return line
 
 
 def run_other_workload(args):
-    if args.workload == "c3":
-        return run_c3(args)
-    if args.workload == "c5":
-        return run_c5(args)
     import torch
-    torch.cuda.set_device(0)
-    emit(json.dumps(measure_c2(torch.device("cuda", 0), args.steps)))
+    if args.workload == "c2":
+        torch.cuda.set_device(0)
+        emit(json.dumps(measure_c2(torch.device("cuda", 0), args.steps)))
+        return
+    line = run_c3(args) if args.workload == "c3" else run_c5(args)
+    if line is not None:
+        emit(json.dumps(line))
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
 
 
 class HostObservationsGeneric(object):
@@ -991,6 +993,20 @@ def main():
                           "(Sentinel2_Observations.py:166-179) runs on the device fused with the compaction gather; "
                           "%s; same float32 output rasters read back every date" % src_note)
 
+    # ---------------- the other BASELINE configs, inside the same line ------
+    # configs[2] (MODIS year, every rank one tile) and a reduced configs[4] sweep, so that they are measured by
+    # whoever runs the default command, at every N; the full versions are `--workload c3|c5`
+    c3_line = c5_line = None
+    if args.rows == SHARD_ROWS and not args.no_e2e and not args.no_other_configs:
+        del obs_dev, kf, prior, x0, Pinv0, data, rho, inv, mask
+        torch.cuda.empty_cache()
+        ctx = (world, rank, local, device, comm, barrier, max_over_ranks)
+        c3_line = run_c3(args, ctx)
+        torch.cuda.empty_cache()
+        c5_line = run_c5(args, ctx, params=[2, 7, 10, 13, 16], sizes=[10000, 1000000, 10000000], bands=(1, 10),
+                         cpu_arm=False)
+        torch.cuda.empty_cache()
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -1096,6 +1112,9 @@ def main():
         # BASELINE configs[1] (the Barrax mask on one GPU) beside the headline workload: a parity-test size
         # at which a B200 is launch-bound, reported for completeness, measured after the timed region
         line["configs1_barrax"] = measure_c2(device, 3)
+    if c3_line is not None:
+        line["configs2_modis_c3"] = c3_line
+        line["configs4_sweep_c5"] = c5_line
     emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
