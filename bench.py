@@ -1079,7 +1079,7 @@ def main():
                 "note": "for the record: this kernel is bound by the fp64 pipe, not by HBM "
                         "(SURVEY 8d: ~195 kflop vs ~1 kB per pixel-iteration)"},
         "solve_kernel": {"kernel": "solve_bands_kernel<10> (normal equations + Cholesky + partial norm; per-pixel "
-                                   "operators, i.e. the launches of iteration >= 2) + reduce_partials_kernel",
+                                   "operators, i.e. the launches of iteration >= 2) + finish_solve_kernel",
                          "bound": "hbm", "achieved": sv_bytes / (sv_ms * 1e-3) / 1e9, "peak": hbm_peak,
                          "unit": "GB/s", "frac": sv_bytes / (sv_ms * 1e-3) / 1e9 / hbm_peak,
                          "algorithmic_bytes_per_launch": sv_bytes, "ms_per_launch": sv_ms,

@@ -68,6 +68,8 @@ extern "C" {
 #define KAFKA_PRIOR_BROADCAST 2u /* pinv_f is ONE packed block shared by all pixels    */
 #define KAFKA_SOLVE_PAIR 4u       /* kafka_solve_bands: use the two-lanes-per-pixel kernel at any size
                                     (the default from 14 parameters; for tests) */
+#define KAFKA_SOLVE_COUNT_LU 8u  /* kafka_solve_bands: n_bad points at TWO int32: [0] pixels left at the
+                                    forecast, [1] pixels solved by pivoted elimination */
 
 const char* kafka_last_error(void);
 int kafka_version(void);
@@ -264,15 +266,19 @@ int64_t kafka_solve_scratch_doubles(int64_t n_pix);
  *     y'_b = y_b + J_b.x_prev - H0_b
  *     A    = sum_b w_b J_b J_b^T + Pinv_f          (packed, written to a_out)
  *     rhs  = sum_b w_b y'_b J_b + Pinv_f x_f
- *     x    = A^-1 rhs   (fp64 Cholesky per pixel)   (written to x_out)
+ *     x    = A^-1 rhs   (fp64 Cholesky per pixel; a block that is not positive
+ *            definite is solved by Gaussian elimination with partial pivoting,
+ *            as the reference's sparse LU solves it, solvers.py:133-134)
+ *                                                  (written to x_out)
  *     *norm2 = sum_i sum_p (x - x_prev)^2           (deterministic two-stage sum)
  * Optional outputs (may be NULL): a_out (an iteration that cannot be the last
  * one needs no A), innovations[b*ld+i] = y_b - H0_b
  * (solvers.py:142), fwd[b*ld+i] = J_b.(x - x_f) + H0_b (solvers.py:137),
- * n_bad = number of pixels whose block was not positive definite (their x is
- * left at x_f).  `scratch` holds kafka_solve_scratch_doubles(n_pix) doubles.
+ * n_bad = number of pixels left at x_f: their block is singular or holds a NaN,
+ * or a Water-Cloud band was asked for a state outside the model's domain.
+ * `scratch` holds kafka_solve_scratch_doubles(n_pix) doubles.
  * flags: KAFKA_PRIOR_BROADCAST; KAFKA_ROUND_F32 (applies to WCM bands, whose
- * operator the reference also stores in float32). */
+ * operator the reference also stores in float32); KAFKA_SOLVE_COUNT_LU. */
 int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve_band* bands_host,
                       int n_bands, const double* x_prev, const double* x_f, const double* pinv_f,
                       double* x_out, double* a_out, double* innovations, double* fwd,
@@ -331,7 +337,7 @@ int kafka_upload_rasters(int n, const void* const* src_host, void* const* dst_de
  * latency-bound loop that must not hit the device-wide synchronisation of
  * cudaMalloc/cudaFree; a thin FFI stub that owns nothing but the input and
  * output arrays it was handed.  The scratch is a fixed array inside the library
- * (KAFKA_STATIC_SCRATCH_DOUBLES doubles = 2 MiB of device memory on every GPU
+ * (KAFKA_STATIC_SCRATCH_DOUBLES doubles = 4 MiB of device memory on every GPU
  * that loads the library, until the process exits), so:
  *   - at most KAFKA_STATIC_MAX_PIXELS pixels per call, else KAFKA_E_TOOLARGE;
  *   - the call neither allocates nor frees anything (no cudaMalloc/cudaFree, no
@@ -344,8 +350,8 @@ int kafka_upload_rasters(int n, const void* const* src_host, void* const* dst_de
  *   - the first call on each device looks up the array's device address (one-off
  *     set-up); issue it before any stream capture starts.
  * Arguments and results are exactly those of kafka_solve_bands minus `scratch`. */
-#define KAFKA_STATIC_SCRATCH_DOUBLES 262144
-#define KAFKA_STATIC_MAX_PIXELS 16777088 /* (262144 - 2) / 2 thread blocks of 128 pixels */
+#define KAFKA_STATIC_SCRATCH_DOUBLES 524288
+#define KAFKA_STATIC_MAX_PIXELS 16758144 /* (524288 - 596) / 4 tiles of 128 pixels */
 int kafka_solve_bands_static(int64_t n_pix, int64_t ld, int n_params, const kafka_solve_band* bands_host,
                              int n_bands, const double* x_prev, const double* x_f, const double* pinv_f,
                              double* x_out, double* a_out, double* innovations, double* fwd,

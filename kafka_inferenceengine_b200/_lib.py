@@ -22,9 +22,10 @@ RAW_I16, RAW_U16, RAW_F32, RAW_F64 = 0, 1, 2, 3
 ROUND_F32 = 1
 PRIOR_BROADCAST = 2
 SOLVE_PAIR = 4
+SOLVE_COUNT_LU = 8
 COMM_ID_BYTES = 128
-STATIC_SCRATCH_DOUBLES = 262144
-STATIC_MAX_PIXELS = 16777088
+STATIC_SCRATCH_DOUBLES = 524288
+STATIC_MAX_PIXELS = 16758144
 
 
 class KafkaCudaError(RuntimeError):

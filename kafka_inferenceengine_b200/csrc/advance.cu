@@ -2,6 +2,7 @@
 // planar state and packed precision blocks (sm_100a, HBM-bound).  Replace the
 // propagators of kafka/inference/kf_tools.py:174-353.
 #include "chol.cuh"
+#include "lu.cuh"
 
 namespace kafka {
 
@@ -66,14 +67,19 @@ advance_standard_kernel(const double* __restrict__ x_a, const double* __restrict
 // propagate_information_filter_SLOW (kf_tools.py:208-245):
 //   (I + Pinv Q)^-1 Pinv  =  Pinv - (S Pinv)^T (I + S Pinv S)^-1 (S Pinv),  S = sqrt(Q)
 // The inner matrix is symmetric positive definite whenever Pinv is, so one
-// Cholesky per pixel replaces the reference's global sparse LU.
+// Cholesky per pixel replaces the reference's global sparse LU.  When it is not
+// (a block the second-order correction left indefinite), the warp solves the
+// reference's own system (I + Pinv Q) X = Pinv for that pixel by elimination with
+// partial pivoting (lu.cuh); only a singular block is handed on unchanged and counted.
 template <int P>
 __global__ void __launch_bounds__(128)
 advance_exact_kernel(const double* __restrict__ a, const double* __restrict__ q, int64_t ld, int64_t n_pix,
                      double* __restrict__ pinv_f, int32_t* __restrict__ n_bad) {
     constexpr int L = tri_count(P);
+    __shared__ LuWork<KAFKA_MAX_PARAMS> s_work[4];
     const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
     int bad = 0;
+    bool failed = false;
     if (i < n_pix) {
         double A[L], M[L], s[P], invd[P];
 #pragma unroll
@@ -85,7 +91,7 @@ advance_exact_kernel(const double* __restrict__ a, const double* __restrict__ q,
 #pragma unroll
             for (int c = 0; c <= r; ++c) M[tri(r, c)] = s[r] * A[tri(r, c)] * s[c] + (r == c ? 1.0 : 0.0);
         const bool ok = chol_factor<P>(M, invd);
-        bad = ok ? 0 : 1;
+        failed = !ok;
         // column by column: w = L^-1 (S Pinv e_col); out -= w w^T accumulated over columns
         double out[L];
 #pragma unroll
@@ -112,7 +118,31 @@ advance_exact_kernel(const double* __restrict__ a, const double* __restrict__ q,
                 stg_stream(pinv_f + (int64_t)tri(r, c) * ld + i, ok ? v : A[tri(r, c)]);
             }
     }
-    bad = __reduce_add_sync(0xffffffffu, bad);
+    unsigned todo = __ballot_sync(0xffffffffu, failed);
+    if (todo) {
+        const int lane = threadIdx.x & 31;
+        LuWork<KAFKA_MAX_PARAMS>& W = s_work[threadIdx.x >> 5];
+        const int64_t i0 = (int64_t)blockIdx.x * 128 + (threadIdx.x & ~31);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t j = i0 + src;
+            if (lane < P) {                                         // row r of [I + Pinv Q | Pinv]
+                const int r = lane;
+                for (int c = 0; c < P; ++c) {
+                    const double v = a[(int64_t)(r >= c ? tri(r, c) : tri(c, r)) * ld + j];
+                    W.m[r][c] = fma(v, q[(int64_t)c * ld + j], r == c ? 1.0 : 0.0);
+                    W.m[r][P + c] = v;
+                }
+            }
+            __syncwarp();
+            const bool ok = warp_gepp(W, P, P, lane);
+            if (ok && lane < P)
+                for (int r = lane; r < P; ++r) pinv_f[(int64_t)tri(r, lane) * ld + j] = W.m[r][P + lane];   // lower triangle of X
+            bad += ok ? 0 : 1;
+            __syncwarp();
+        }
+    }
     if ((threadIdx.x & 31) == 0 && bad != 0 && n_bad) atomicAdd(n_bad, bad);
 }
 

@@ -2,7 +2,7 @@
 // that cannot hand over a scratch buffer because they cannot allocate one.
 //
 // Who that is.  kafka_solve_bands needs a few kilobytes to a couple of megabytes
-// of device scratch (one partial sum and one bad-pixel count per thread block)
+// of device scratch (partial sums, counts and one failure bit per pixel)
 // and leaves it to the caller to provide it.  Some callers have nowhere to get
 // it from:
 //   * a plug-in running inside a host application whose own memory manager
@@ -19,7 +19,7 @@
 // and held until the process exits.
 //
 // Rules that follow from sharing one array:
-//   * size limit: KAFKA_STATIC_SCRATCH_DOUBLES doubles (2 MiB), enough for
+//   * size limit: KAFKA_STATIC_SCRATCH_DOUBLES doubles (4 MiB), enough for
 //     KAFKA_STATIC_MAX_PIXELS pixels per call; larger calls are refused with
 //     KAFKA_E_TOOLARGE and must use kafka_solve_bands with their own scratch;
 //   * the array keeps whatever the previous call left in it.  Nothing in it has

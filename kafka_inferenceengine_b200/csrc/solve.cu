@@ -38,7 +38,9 @@ struct SolveParams {
     double* a_out;
     double* innovations;
     double* fwd;
-    double* partials;     // [2][gridDim.x]: sum of squares, bad-pixel count
+    double* partials;     // [2][tiles]: sum of squares, pixels left at the forecast (tile = 128 pixels)
+    uint32_t* fail_bits;  // one bit per pixel: Cholesky met a non-positive pivot (finish_solve_kernel takes over)
+    int32_t* n_lu;        // [0] pixels solved by elimination, [1] arrival ticket of finish_solve_kernel
     int64_t n_pix;
     int64_t ld;
     int32_t n_bands;
@@ -245,7 +247,7 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
     double rhs[P], xp[P];
     const bool bcast = (prm.flags & KAFKA_PRIOR_BROADCAST) != 0;
     const bool round32 = (prm.flags & KAFKA_ROUND_F32) != 0;
-    bool domain_bad = false;
+    bool domain_bad = false, indefinite = false;
 #pragma unroll
     for (int c = 0; c < L; ++c) A.set(c, bcast ? prm.pinv_f[c] : ldg_stream(prm.pinv_f + (int64_t)c * ld + il));
 #pragma unroll
@@ -293,7 +295,9 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
             for (int c = 0; c < L; ++c) stg_stream(prm.a_out + (int64_t)c * ld + i, A.get(c));
         }
         double invd[P];
-        const bool ok = chol_factor_blk<P>(A, invd) && !domain_bad;
+        const bool spd = chol_factor_blk<P>(A, invd);
+        const bool ok = spd && !domain_bad;
+        indefinite = !spd && !domain_bad;
         chol_solve_blk<P>(A, invd, rhs);
 #pragma unroll
         for (int p = 0; p < P; ++p) {
@@ -320,9 +324,11 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
 
     ssq = warp_sum(ssq);
     bad = warp_sum(bad);
+    const unsigned fail = __ballot_sync(0xffffffffu, indefinite);
     if ((threadIdx.x & 31) == 0) {
         s_part[0][threadIdx.x >> 5] = ssq;
         s_part[1][threadIdx.x >> 5] = bad;
+        prm.fail_bits[blockIdx.x * (kSolveThreads / 32) + (threadIdx.x >> 5)] = fail;   // word w = pixels 32w .. 32w+31
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -334,40 +340,19 @@ solve_bands_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) {
         }
         prm.partials[blockIdx.x] = s0;
         prm.partials[gridDim.x + blockIdx.x] = s1;
+        if (blockIdx.x == 0) prm.n_lu[0] = prm.n_lu[1] = 0;           // counter and ticket of the second stage
     }
 }
 
 }  // namespace kafka
 #include "solve_pair.cuh"
+#include "solve_lu.cuh"
 namespace kafka {
 
-// Fixed-order second stage: same bits every run, whatever the launch order.
-__global__ void __launch_bounds__(256)
-reduce_partials_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ norm2,
-                       int32_t* __restrict__ n_bad) {
-    __shared__ double s0[256], s1[256];
-    double a = 0.0, b = 0.0;
-    for (int k = threadIdx.x; k < n_blocks; k += 256) {
-        a += partials[k];
-        b += partials[n_blocks + k];
-    }
-    s0[threadIdx.x] = a;
-    s1[threadIdx.x] = b;
-    __syncthreads();
-    for (int o = 128; o > 0; o >>= 1) {
-        if ((int)threadIdx.x < o) {
-            s0[threadIdx.x] += s0[threadIdx.x + o];
-            s1[threadIdx.x] += s1[threadIdx.x + o];
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        if (norm2) *norm2 = s0[0];
-        if (n_bad) *n_bad = (int32_t)s1[0];
-    }
-}
-
-// blend_prior (kf_tools.py:75-96): C = Pf + Cp, b = Pf mu_p + Cp x_f, x = C^-1 b
+// blend_prior (kf_tools.py:75-96): C = Pf + Cp, b = Pf mu_p + Cp x_f, x = C^-1 b.  The reference solves with a
+// sparse LU (kf_tools.py:93-94); a pixel whose C is not positive definite -- a forecast block the second-order
+// correction left indefinite -- is therefore solved by elimination with partial pivoting (warp_gepp): the warp
+// takes its failed pixels one at a time through shared memory, lane r rebuilding row r of [C | b].
 template <int P>
 __global__ void __launch_bounds__(kSolveThreads)
 blend_prior_kernel(const double* __restrict__ prior_mean, const double* __restrict__ prior_inv,
@@ -375,10 +360,11 @@ blend_prior_kernel(const double* __restrict__ prior_mean, const double* __restri
                    double* __restrict__ x_out, double* __restrict__ c_out, int32_t* __restrict__ n_bad,
                    uint32_t flags) {
     constexpr int L = tri_count(P);
+    __shared__ LuWork<1> s_work[kSolveThreads / 32];
     const int64_t i = (int64_t)blockIdx.x * kSolveThreads + threadIdx.x;
-    int bad = 0;
+    const bool bcast = (flags & KAFKA_PRIOR_BROADCAST) != 0;
+    bool failed = false;
     if (i < n_pix) {
-        const bool bcast = (flags & KAFKA_PRIOR_BROADCAST) != 0;
         double Pf[L], Cp[L], mu[P], xf[P], b1[P], b2[P];
 #pragma unroll
         for (int c = 0; c < L; ++c) {
@@ -404,10 +390,44 @@ blend_prior_kernel(const double* __restrict__ prior_mean, const double* __restri
         chol_solve<P>(Pf, invd, b1);
 #pragma unroll
         for (int p = 0; p < P; ++p) stg_stream(x_out + (int64_t)p * ld + i, ok ? b1[p] : xf[p]);
-        bad = ok ? 0 : 1;
+        failed = !ok;
     }
-    bad = __reduce_add_sync(0xffffffffu, bad);        // integer count: order-independent
-    if ((threadIdx.x & 31) == 0 && bad != 0 && n_bad) atomicAdd(n_bad, bad);
+    unsigned todo = __ballot_sync(0xffffffffu, failed);
+    int bad = 0;
+    if (todo) {
+        const int lane = threadIdx.x & 31;
+        LuWork<1>& W = s_work[threadIdx.x >> 5];
+        const int64_t i0 = (int64_t)blockIdx.x * kSolveThreads + (threadIdx.x & ~31);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t j = i0 + src;
+            if (lane < P) {
+                const int r = lane;
+                double b = 0.0;
+                for (int q = 0; q < P; ++q) {                       // row r of Pf and Cp, b_r as symv adds it up
+                    const int c = r >= q ? tri(r, q) : tri(q, r);
+                    const double pf = pinv_f[(int64_t)c * ld + j];
+                    b = fma(pf, bcast ? prior_mean[q] : prior_mean[(int64_t)q * ld + j], b);
+                    W.m[r][q] = pf;
+                }
+                double b2 = 0.0;
+                for (int q = 0; q < P; ++q) {
+                    const int c = r >= q ? tri(r, q) : tri(q, r);
+                    const double cp = bcast ? prior_inv[c] : prior_inv[(int64_t)c * ld + j];
+                    b2 = fma(cp, x_f[(int64_t)q * ld + j], b2);
+                    W.m[r][q] += cp;
+                }
+                W.m[r][P] = b + b2;
+            }
+            __syncwarp();
+            const bool ok = warp_gepp(W, P, 1, lane);
+            if (ok && lane < P) x_out[(int64_t)lane * ld + j] = W.m[lane][P];
+            bad += ok ? 0 : 1;
+            __syncwarp();
+        }
+    }
+    if ((threadIdx.x & 31) == 0 && bad != 0 && n_bad) atomicAdd(n_bad, bad);   // integer count: order-independent
 }
 
 }  // namespace kafka
@@ -416,9 +436,12 @@ using namespace kafka;
 
 extern "C" {
 
+// scratch, T = tiles of 128 pixels: [0, T) partial sums of squares | [T, 2T) pixels left at the forecast |
+// [2T, 4T) one bit per pixel "Cholesky failed" (4 words per tile) | [4T] pixels solved by the pivoted
+// elimination (int32) and the second stage's arrival ticket (uint32) | 3 spare | 2 kFinishCtas per-CTA sums
 int64_t kafka_solve_scratch_doubles(int64_t n_pix) {
     if (n_pix < 0) return -1;
-    return 2 * ((n_pix + kSolveThreads - 1) / kSolveThreads) + 2;
+    return 4 * ((n_pix + kSolveThreads - 1) / kSolveThreads) + 4 + 2 * kFinishCtas;
 }
 
 int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve_band* bands, int n_bands,
@@ -433,9 +456,10 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
                     KAFKA_MAX_BANDS);
     KAFKA_CHECK_ARG(n_bands == 0 || bands, "kafka_solve_bands: bands is null");
     cudaStream_t s = (cudaStream_t)stream;
+    const bool report_lu = (flags & KAFKA_SOLVE_COUNT_LU) != 0;
     if (n_pix == 0) {
         if (norm2) KAFKA_CUDA(cudaMemsetAsync(norm2, 0, sizeof(double), s));
-        if (n_bad) KAFKA_CUDA(cudaMemsetAsync(n_bad, 0, sizeof(int32_t), s));
+        if (n_bad) KAFKA_CUDA(cudaMemsetAsync(n_bad, 0, (report_lu ? 2 : 1) * sizeof(int32_t), s));
         return 0;
     }
     KAFKA_CHECK_ARG(x_prev && x_f && pinv_f && x_out && scratch, "kafka_solve_bands: null pointer");
@@ -489,17 +513,27 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
     prm.innovations = innovations;
     prm.fwd = fwd;
     prm.partials = scratch;
+    const unsigned grid = (unsigned)((n_pix + kSolveThreads - 1) / kSolveThreads);
+    prm.fail_bits = reinterpret_cast<uint32_t*>(scratch + 2 * (size_t)grid);
+    prm.n_lu = reinterpret_cast<int32_t*>(scratch + 4 * (size_t)grid);
     prm.n_pix = n_pix;
     prm.ld = ld;
     prm.n_bands = n_bands;
     prm.flags = flags;
-    const unsigned grid = (unsigned)((n_pix + kSolveThreads - 1) / kSolveThreads);
     int n_dim_max = 0;
     for (int b = 0; b < n_bands; ++b)
         if (prm.bands[b].kind == KAFKA_BAND_ARRAYS && prm.bands[b].n_planes > n_dim_max) n_dim_max = prm.bands[b].n_planes;
     const size_t ring = (size_t)kAsyncStages * (3 + n_dim_max) * kSolveThreads * sizeof(double);
-    // the lane-sharing kernels run 64 pixels per CTA: two CTAs add into one scratch slot
-    const unsigned grid_half = (unsigned)((n_pix + kSolveThreads / 2 - 1) / (kSolveThreads / 2));
+    // second stage (solve_lu.cuh): pixels whose Cholesky failed are solved by pivoted elimination, then the
+    // partial sums are added up in a fixed order
+    auto finish = [&]() -> int {
+        unsigned ctas = (grid + kFinishWarps * 32 - 1) / (kFinishWarps * 32);
+        ctas = ctas < (unsigned)kFinishCtas ? ctas : (unsigned)kFinishCtas;
+        finish_solve_kernel<<<ctas, kFinishWarps * 32, 0, s>>>(prm, n_params, grid, scratch + 4 * (size_t)grid + 4,
+                                                               reinterpret_cast<unsigned*>(prm.n_lu + 1), norm2, n_bad,
+                                                               report_lu);
+        return launch_status("finish_solve_kernel");
+    };
     int rc = KAFKA_E_UNSUPPORTED;
     if (n_params >= kPairFromParams || (flags & KAFKA_SOLVE_PAIR)) {
         bool all_identity_pair = n_bands > 0;
@@ -507,7 +541,8 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         KAFKA_DISPATCH_P(n_params, {
             auto kern = all_identity_pair ? solve_bands_pair_kernel<kP, true> : solve_bands_pair_kernel<kP, false>;
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ring / 2));
-            if (e == cudaSuccess) e = cudaMemsetAsync(scratch, 0, 2 * (size_t)grid * sizeof(double), s);
+            // the two CTAs of a tile add into one scratch slot, failure bits are only ever set: all start at zero
+            if (e == cudaSuccess) e = cudaMemsetAsync(scratch, 0, (4 * (size_t)grid + 1) * sizeof(double), s);
             if (e != cudaSuccess) {
                 set_error("launch set-up failed: %s", cudaGetErrorString(e));
                 rc = (int)e;
@@ -517,8 +552,7 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
             }
         });
         if (rc != 0) return rc;
-        reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
-        return launch_status("reduce_partials_kernel");
+        return finish();
     }
     bool all_identity = n_bands > 0, all_uniform = n_bands > 0;
     for (int b = 0; b < n_bands; ++b) {
@@ -538,8 +572,7 @@ int kafka_solve_bands(int64_t n_pix, int64_t ld, int n_params, const kafka_solve
         }
     });
     if (rc != 0) return rc;
-    reduce_partials_kernel<<<1, 256, 0, s>>>(scratch, (int)grid, norm2, n_bad);
-    return launch_status("reduce_partials_kernel");
+    return finish();
 }
 
 int kafka_wcm_forward(const double* x, int64_t ld, int64_t n, const double* params_host, double* sigma0, double* grad,

@@ -248,6 +248,7 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
                     if (q > j) a[k * (k + 1) + q] = fma(-a[k * (k + 1) + j], col[q], a[k * (k + 1) + q]);
             }
     }
+    const bool indefinite = live && !ok && !domain_bad;             // solve_indefinite_kernel takes this pixel over
     ok = ok && !domain_bad;
 
     // ---- forward substitution: y_j broadcast from its owner ----
@@ -314,6 +315,18 @@ solve_bands_pair_kernel(const __grid_constant__ SolveParams prm, int n_dim_max) 
 
     ssq = warp_sum(ssq);
     bad = warp_sum(bad);
+    {   // one bit per pixel: the even lanes' verdicts, packed into the half word of this warp's 16 pixels
+        // (the words were zeroed by the host before the launch, so only a failure writes)
+        unsigned m = __ballot_sync(0xffffffffu, indefinite && g == 0);
+        if (m != 0 && (threadIdx.x & 31) == 0) {
+            m = (m | (m >> 1)) & 0x33333333u;
+            m = (m | (m >> 2)) & 0x0f0f0f0fu;
+            m = (m | (m >> 4)) & 0x00ff00ffu;
+            m = (m | (m >> 8)) & 0x0000ffffu;
+            const int64_t first = tile0 + (threadIdx.x >> 5) * 16;  // first pixel of this warp
+            atomicOr(prm.fail_bits + (first >> 5), m << (first & 31));
+        }
+    }
     if ((threadIdx.x & 31) == 0) {
         s_part[0][threadIdx.x >> 5] = ssq;
         s_part[1][threadIdx.x >> 5] = bad;

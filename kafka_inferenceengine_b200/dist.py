@@ -122,39 +122,51 @@ class NativeComm(object):
 def global_norm(sum_sq_local, n_elems_local, comm=None, n_bad_local=None):
     """``(sqrt(sum of squares over all ranks) / total element count)`` and the
     total count.  ``sum_sq_local`` may be a python float or a 0-d/1-element
-    tensor on any device.  With ``n_bad_local`` (same kinds) the bad-pixel count
-    of the solve rides in the same all-reduce and its total is returned as a
-    third value."""
+    tensor on any device.  With ``n_bad_local`` (same kinds; a tensor may hold
+    several counters, e.g. [pixels left at the forecast, pixels solved by pivoted
+    elimination]) the counts of the solve ride in the same all-reduce and their
+    totals are returned as a third value (an int, or a tuple of ints)."""
     import torch.distributed as dist
+
+    def counts_on(dev):
+        if n_bad_local is None:
+            return []
+        if isinstance(n_bad_local, torch.Tensor):
+            return [n_bad_local.reshape(-1).to(device=dev, dtype=torch.float64)]
+        return [torch.tensor([float(n_bad_local)], dtype=torch.float64, device=dev)]
+
+    def result(tot):
+        res = (float(np.sqrt(tot[0]) / tot[1]), float(tot[1]))
+        if n_bad_local is None:
+            return res
+        counts = tuple(int(round(float(v))) for v in tot[2:])
+        return res + (counts[0] if len(counts) == 1 else counts,)
+
     if isinstance(comm, NativeComm):
         from . import _lib
         dev = comm.device
-        parts = [sum_sq_local.reshape(-1)[0].to(device=dev, dtype=torch.float64)
-                 if isinstance(sum_sq_local, torch.Tensor) else torch.tensor(float(sum_sq_local), dtype=torch.float64, device=dev),
-                 torch.tensor(float(n_elems_local), dtype=torch.float64, device=dev)]
-        if n_bad_local is not None:
-            parts.append(n_bad_local.reshape(-1)[0].to(device=dev, dtype=torch.float64) if isinstance(n_bad_local, torch.Tensor)
-                         else torch.tensor(float(n_bad_local), dtype=torch.float64, device=dev))
-        buf = comm.all_reduce_sums(torch.stack(parts))
+        head = [sum_sq_local.reshape(-1)[0:1].to(device=dev, dtype=torch.float64)
+                if isinstance(sum_sq_local, torch.Tensor) else torch.tensor([float(sum_sq_local)], dtype=torch.float64, device=dev),
+                torch.tensor([float(n_elems_local)], dtype=torch.float64, device=dev)]
+        buf = comm.all_reduce_sums(torch.cat(head + counts_on(dev)))
         with torch.cuda.device(dev):
             tot = _lib.read_small(buf)
-        res = (float(np.sqrt(tot[0]) / tot[1]), float(tot[1]))
-        return res if n_bad_local is None else res + (int(round(float(tot[2]))),)
+        return result(tot)
     if comm is None and not (dist.is_available() and dist.is_initialized()):
         s = float(sum_sq_local)
         res = (np.sqrt(s) / float(n_elems_local), float(n_elems_local))
-        return res if n_bad_local is None else res + (int(n_bad_local),)
+        if n_bad_local is None:
+            return res
+        if isinstance(n_bad_local, torch.Tensor) and n_bad_local.numel() > 1:
+            return res + (tuple(int(v) for v in n_bad_local.reshape(-1).tolist()),)
+        return res + (int(n_bad_local),)
     if isinstance(sum_sq_local, torch.Tensor):
         dev = sum_sq_local.device
-        parts = [sum_sq_local.reshape(-1)[0].to(torch.float64),
-                 torch.tensor(float(n_elems_local), dtype=torch.float64, device=dev)]
-        if n_bad_local is not None:
-            parts.append(n_bad_local.reshape(-1)[0].to(torch.float64) if isinstance(n_bad_local, torch.Tensor)
-                         else torch.tensor(float(n_bad_local), dtype=torch.float64, device=dev))
-        buf = torch.stack(parts)
+        buf = torch.cat([sum_sq_local.reshape(-1)[0:1].to(torch.float64),
+                         torch.tensor([float(n_elems_local)], dtype=torch.float64, device=dev)] + counts_on(dev))
     else:
-        buf = torch.tensor([float(sum_sq_local), float(n_elems_local)]
-                           + ([] if n_bad_local is None else [float(n_bad_local)]), dtype=torch.float64)
+        buf = torch.cat([torch.tensor([float(sum_sq_local), float(n_elems_local)], dtype=torch.float64)]
+                        + counts_on(torch.device("cpu")))
     backend = dist.get_backend(comm)
     if backend == "gloo" and buf.is_cuda:
         buf = buf.cpu()
@@ -165,8 +177,7 @@ def global_norm(sum_sq_local, n_elems_local, comm=None, n_bad_local=None):
             tot = _lib.read_small(buf)           # no device->host memcpy: see kafka_read_small
     else:
         tot = buf.numpy()
-    res = (float(np.sqrt(tot[0]) / tot[1]), float(tot[1]))
-    return res if n_bad_local is None else res + (int(round(float(tot[2]))),)
+    return result(tot)
 
 
 def gather_interleaved(x_local, comm=None, dst=None):

@@ -518,17 +518,20 @@ class SolveWorkspace(object):
         self.ld = ld
         self.innov = torch.zeros((max(n_bands, 1), ld), dtype=torch.float64, device=device)
         self.fwd = torch.zeros((max(n_bands, 1), ld), dtype=torch.float64, device=device) if want_fwd else None
-        # the two scalars every solve leaves behind, side by side so that one kafka_read_small
-        # brings both to the host: [sum of squares (f64) | bad-pixel count (i32) + padding]
+        # the scalars every solve leaves behind, side by side so that one kafka_read_small brings them
+        # to the host: [sum of squares (f64) | pixels left at the forecast (i32) | pixels solved by
+        # pivoted elimination (i32)]
         self.scalars = torch.zeros(2, dtype=torch.float64, device=device)
         self.norm2 = self.scalars[0:1]
-        self.n_bad = self.scalars[1:2].view(torch.int32)[0:1]
+        self.n_bad = self.scalars[1:2].view(torch.int32)[0:2]
         self.scratch = torch.empty(int(lib.kafka_solve_scratch_doubles(n_pix)), dtype=torch.float64, device=device)
 
     def read_scalars(self):
-        """(sum of squares, bad-pixel count) of the last solve, waiting for it."""
+        """(sum of squares, pixels left at the forecast, pixels solved by pivoted elimination) of
+        the last solve, waiting for it."""
         host = _lib.read_small(self.scalars)
-        return float(host[0]), int(host[1:2].view(np.int32)[0])
+        counts = host[1:2].view(np.int32)
+        return float(host[0]), int(counts[0]), int(counts[1])
 
 
 def make_solve_bands(descs, bufs):
@@ -572,7 +575,8 @@ def solve_bands(ws, descs, bufs, x_prev, x_f, pinv_f, x_out, a_out, want_fwd=Fal
     A, innovations and forward-modelled values nobody will read: none is stored."""
     lib = _lib.get_lib()
     arr = make_solve_bands(descs, bufs)
-    flags = (_lib.PRIOR_BROADCAST if pinv_f.is_broadcast else 0) | (_lib.ROUND_F32 if round_f32 else 0)
+    flags = (_lib.PRIOR_BROADCAST if pinv_f.is_broadcast else 0) | (_lib.ROUND_F32 if round_f32 else 0) | \
+        _lib.SOLVE_COUNT_LU
     with torch.cuda.device(ws.device):
         _lib.check(lib.kafka_solve_bands(ws.n_pix, ws.ld, ws.n_params, arr, len(descs), _lib.ptr(x_prev.data),
                                          _lib.ptr(x_f.data), _lib.ptr(pinv_f.data), _lib.ptr(x_out.data),

@@ -266,14 +266,15 @@ def blend_prior(prior_mean, prior_cov_inverse, x_forecast, P_forecast_inverse):
         _lib.check(lib.kafka_blend_prior(_lib.ptr(mu_t), _lib.ptr(cp_t), _lib.ptr(xf.data), _lib.ptr(Pf.data),
                                          Pf.ld, n, P, _lib.ptr(x_out.data), _lib.ptr(c_out.data),
                                          _lib.ptr(n_bad), flags, _lib.stream_ptr()), "kafka_blend_prior")
-        _warn_bad(n_bad, "blend_prior: %d pixels have a combined inverse covariance that is not positive definite; "
+        _warn_bad(n_bad, "blend_prior: %d pixels have a singular combined inverse covariance; "
                          "their mean is left at the forecast")
     return x_out, c_out
 
 
 def _warn_bad(n_bad, message):
     """Read a kernel's failed-pixel counter back (kafka_read_small: no device->host memcpy) and
-    log it the way do_all_bands does; the reference's LU never notices such blocks."""
+    log it the way do_all_bands does.  Blocks that are merely not positive definite are solved by
+    elimination with partial pivoting, as the reference's LU solves them, and are not counted."""
     n = int(_lib.read_small(n_bad)[0])
     if n:
         LOG.warning(message, n)
@@ -330,8 +331,8 @@ def propagate_information_filter_SLOW(x_analysis, P_analysis, P_analysis_inverse
     with torch.cuda.device(dev):
         _lib.check(lib.kafka_advance_exact(_lib.ptr(Pi.data), _lib.ptr(q.data), Pi.ld, n, P, _lib.ptr(out.data),
                                            _lib.ptr(n_bad), _lib.stream_ptr()), "kafka_advance_exact")
-        _warn_bad(n_bad, "propagate_information_filter_SLOW: %d pixels have an inflated block that is not positive "
-                         "definite; their inverse covariance is carried over unchanged")
+        _warn_bad(n_bad, "propagate_information_filter_SLOW: %d pixels have a singular inflated block; "
+                         "their inverse covariance is carried over unchanged")
     return x_f, None, out
 
 

@@ -285,11 +285,23 @@ class LinearKalman(object):
         """Convergence norm over ALL pixels (all ranks): linear_kf.py:293."""
         n_elems = self.n_state_elems * self.n_params
         if self.comm is None:
-            ssq, self._n_bad_last = ws.read_scalars()
+            ssq, self._n_bad_last, self._n_lu_last = ws.read_scalars()
             return float(np.sqrt(ssq) / float(n_elems)), float(n_elems)
         from .dist import global_norm
-        norm, count, self._n_bad_last = global_norm(ws.norm2, n_elems, self.comm, n_bad_local=ws.n_bad)
+        norm, count, (self._n_bad_last, self._n_lu_last) = global_norm(ws.norm2, n_elems, self.comm,
+                                                                       n_bad_local=ws.n_bad)
         return norm, count
+
+    @staticmethod
+    def _warn_counts(n_bad, n_bad_max, n_lu, n_lu_max):
+        """The counts of the last solve; an earlier linearisation point may have met more."""
+        if n_lu_max:
+            LOG.warning("%d pixels had an information matrix that is not positive definite; solved by elimination "
+                        "with partial pivoting, as the reference's sparse LU solves them%s", n_lu,
+                        "" if n_lu == n_lu_max else " (%d in an earlier iteration)" % n_lu_max)
+        if n_bad_max:
+            LOG.warning("%d pixels had a singular (or non-finite) information matrix; left at the forecast"
+                        "%s", n_bad, "" if n_bad == n_bad_max else " (%d in an earlier iteration)" % n_bad_max)
 
     def do_all_bands(self, timestep, current_data, x_forecast, P_forecast,
                      P_forecast_inverse, convergence_tolerance=1e-3,
@@ -336,6 +348,7 @@ class LinearKalman(object):
         x_prev = x_forecast
         n_iter = 1
         n_bad = n_bad_max = 0                 # pixels the solve left at the forecast: last iteration / worst
+        n_lu = n_lu_max = 0                   # pixels solved by pivoted elimination (block not positive definite)
         is_wcm = self._create_observation_operator.kind == "wcm"
         norms = []
         not_converged = True
@@ -373,13 +386,13 @@ class LinearKalman(object):
                     # a full emulator pass is now queued: use the wait to stage the next date
                     self._prefetch_next()
                 convergence_norm, count = self._global_norm(ws)   # linear_kf.py:293
-                n_bad = self._n_bad_last
-                n_bad_max = max(n_bad_max, n_bad)
+                n_bad, n_lu = self._n_bad_last, self._n_lu_last
+                n_bad_max, n_lu_max = max(n_bad_max, n_bad), max(n_lu_max, n_lu)
                 if n_bad and is_wcm:
                     # the reference's forward model refuses such a linearisation point in the iteration
                     # that meets it (sar_forward_model.py:66-71)
                     raise ValueError("%d pixels left the Water-Cloud model's domain (LAI <= 0 or SM <= 0) or have "
-                                     "a non positive-definite information matrix (iteration %d)" % (n_bad, n_iter))
+                                     "a singular information matrix (iteration %d)" % (n_bad, n_iter))
                 x_analysis = x_new
                 x_analysis._uniform = False      # a solved state: skip the shared-vector test next iteration
             else:
@@ -399,10 +412,7 @@ class LinearKalman(object):
             x_prev = x_analysis
             n_iter += 1
 
-        if n_bad_max:
-            # the count of the last solve; an earlier linearisation point may have lost more
-            LOG.warning("%d pixels had a non positive-definite information matrix; left at the forecast"
-                        "%s", n_bad, "" if n_bad == n_bad_max else " (%d in an earlier iteration)" % n_bad_max)
+        self._warn_counts(n_bad, n_bad_max, n_lu, n_lu_max)
         if (self.hessian_correction or getattr(self, "_force_hessian", False)) and groups:
             # P_analysis_inverse - P_correction (linear_kf.py:319,416), evaluated at x_analysis
             for group in groups:
@@ -468,7 +478,7 @@ class LinearKalman(object):
         innov = torch.empty((nb, ld), dtype=torch.float64, device=dev)
         fwd = torch.empty((nb, ld), dtype=torch.float64, device=dev) if self.want_forward_modelled else None
         flags = (_lib.PRIOR_BROADCAST if P_forecast_inverse.is_broadcast else 0) | \
-            (_lib.ROUND_F32 if self.round_operator_f32 else 0)
+            (_lib.ROUND_F32 if self.round_operator_f32 else 0) | _lib.SOLVE_COUNT_LU
         ints = st["ints"]
         x_uni = None
         if self.dedup_uniform_state and isinstance(x_forecast._uniform, np.ndarray):
@@ -486,16 +496,17 @@ class LinearKalman(object):
                 st["ints_at"] + 12, _lib.ptr(x_uni)),
                 "kafka_assimilate_date")
         n_solves, n_bad, n_bad_max, idx = ints[0], ints[1], ints[2], ints[3]
-        _lib.launch_count += 4 * n_solves                # kernels of the call: (linearise, solve, reduce, read) per solve
+        _lib.launch_count += 4 * n_solves     # kernels of the call: (linearise, solve, second stage, read) per solve
+        # slot k of the page-locked buffer: [sum of squares f64 | left at the forecast i32 | solved by elimination i32]
+        lu = st["pinned"].numpy().view(np.int32)[3:4 * n_solves:4]
+        n_lu, n_lu_max = int(lu[-1]), int(lu.max())
         norms = [st["norms"][k] for k in range(n_solves)]
         if LOG.isEnabledFor(logging.INFO):
             for k, v in enumerate(norms):
                 LOG.info("Band {:d}, Iteration # {:d}, convergence norm: {:g}".format(nb - 1, k + 1, v))
         if n_solves > 25:
             LOG.warning("Bailing out after 25 iterations!!!!!!")
-        if n_bad_max:
-            LOG.warning("%d pixels had a non positive-definite information matrix; left at the forecast"
-                        "%s", n_bad, "" if n_bad == n_bad_max else " (%d in an earlier iteration)" % n_bad_max)
+        self._warn_counts(n_bad, n_bad_max, n_lu, n_lu_max)
         x_analysis = DeviceVector(x_work[idx], n, P)
         x_analysis._uniform = False
         self.last_iterations.append(n_solves)

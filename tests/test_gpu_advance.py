@@ -150,3 +150,57 @@ def test_lai_advance_large_modis_tile_properties():
     assert torch.equal(x1.data[6, :n], x.data[6, :n])
     mean, _, _ = kb.tip_prior()
     assert torch.all(x1.data[0, :n] == mean[0])
+
+
+def _make_indefinite(rng, blocks, which):
+    """Flip the sign of one eigen-direction of the chosen SPD blocks."""
+    out = blocks.copy()
+    for i in which:
+        w, V = np.linalg.eigh(out[i])
+        k = int(rng.integers(0, len(w)))
+        w[k] = -w[k]
+        out[i] = (V * w) @ V.T
+        out[i] = 0.5 * (out[i] + out[i].T)
+    return out
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 7, 10, 13, 16])
+def test_indefinite_blocks_are_solved_like_the_reference_lu(P):
+    """The reference's exact propagator and prior blend solve with a sparse LU (kf_tools.py:236-243,
+    :93-94), so a block that is not positive definite still gets the solution of its equations.
+    Here such pixels leave the Cholesky path and are solved by elimination with partial pivoting;
+    a singular block is handed on unchanged / left at the forecast."""
+    rng = np.random.default_rng(40 + P)
+    n = 700
+    Pinv = gu.random_spd(rng, n, P)
+    which = np.array(sorted(set([0, 31, 32, 127, 128, n - 1]) | set(rng.integers(0, n, 30).tolist())))
+    Pinv = _make_indefinite(rng, Pinv, which)
+    x_a = rng.standard_normal(n * P)
+    # inflation large enough for I + S Pinv S to lose positive definiteness on the flipped direction
+    q = rng.uniform(2.0, 3.0, n * P) / np.repeat(np.abs(np.linalg.eigvalsh(Pinv)).min(axis=1), P)
+    A = BlockDiag.from_blocks(Pinv, gu.DEV)
+    Q = kb.DiagonalMatrix(q, P, gu.DEV)
+    _, _, p = kb.propagate_information_filter_SLOW(x_a, None, A, None, Q)
+    _, want = kc.propagate_information_filter_exact(x_a, Pinv, q)
+    inner = np.eye(P)[None] + np.sqrt(q).reshape(n, P, 1) * Pinv * np.sqrt(q).reshape(n, 1, P)
+    assert (np.linalg.eigvalsh(inner)[which].min(axis=1) < 0).all()          # these pixels did take the other path
+    got = p.blocks()
+    lower = np.tril(np.ones((P, P), dtype=bool))
+    scale = np.abs(want).max(axis=(1, 2), keepdims=True)
+    assert np.max(np.abs(got - want)[:, lower] / np.broadcast_to(scale, want.shape)[:, lower]) < 1e-8
+    keep = np.ones(n, dtype=bool)
+    keep[which] = False
+    assert np.allclose(got[keep], want[keep], rtol=1e-10, atol=1e-11)
+
+    # prior blend: C = Pinv + prior_inv indefinite on the same pixels
+    prior_inv = 1e-3 * gu.random_spd(rng, n, P)
+    prior_mean = rng.standard_normal(n * P)
+    xc, C = kb.blend_prior(prior_mean, BlockDiag.from_blocks(prior_inv, gu.DEV), x_a, A)
+    xo, Co = kc.blend_prior(prior_mean, prior_inv, x_a, Pinv)
+    ev = np.linalg.eigvalsh(Co)
+    assert (ev[which].min(axis=1) < 0).all()
+    assert np.allclose(C.blocks(), Co, rtol=1e-14)
+    err = np.abs(np.asarray(xc) - xo).reshape(n, P).max(axis=1) / np.abs(xo).reshape(n, P).max(axis=1)
+    cond = np.abs(ev).max(axis=1) / np.abs(ev).min(axis=1)
+    assert (err < 1e-13 * np.maximum(cond, 10.0)).all()
+    assert (err[keep] < 1e-10).all()

