@@ -125,6 +125,17 @@ int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, in
                          int n_params, const int32_t* idx, int64_t n_raster, float* mean_raster,
                          float* unc_raster, void* stream);
 
+/* The whole output stage of one date in one call (KafkaOutput.dump_data,
+ * kafka/input_output/observations.py:360-399, up to the point where it hands the rasters to GDAL):
+ * optionally zero the device rasters, scatter as kafka_scatter_output, then read the rasters back
+ * into host_dst (page-locked: the copy is then asynchronous) -- all queued on `stream`.  The two
+ * rasters must be one allocation: unc_raster == mean_raster + n_params * n_raster (or NULL), and
+ * host_dst receives them in that order.  zero_first may be 0 when the buffer was zero-filled once
+ * and is only ever written through the same idx. */
+int kafka_output_rasters(const double* x, const double* a_packed, int64_t ld, int64_t n_pix,
+                         int n_params, const int32_t* idx, int64_t n_raster, float* mean_raster,
+                         float* unc_raster, int zero_first, void* host_dst, void* stream);
+
 /* Observation ingest of the MODIS broadband-albedo reader fused with the gather,
  * replacing the arithmetic of BHRObservations.get_band_data
  * (kafka/input_output/observations.py:288-310).  kernels: the band's three BRDF
@@ -313,7 +324,12 @@ int kafka_assimilate_iter(int64_t n_pix, int64_t ld, int n_params, const kafka_g
  * x_uniform (may be NULL): n_params contiguous doubles on the device -- the state shared by ALL
  * pixels of x_f (e.g. after a prior reset); the first iteration then evaluates the emulators once
  * for that vector, the reference's single-unique-vector branch (kafka/inference/utils.py:72-74).
- * Synchronises `stream` once per iteration that can end the loop. */
+ * Synchronises `stream` once per iteration that can end the loop.
+ * while_queued (may be NULL): called once, with while_queued_arg, after the first iterations have been
+ * queued and before the first wait -- host work the caller wants done while the GPU is busy (the
+ * reference's loop has no such slot; here it is where the next date's rasters are read and sent,
+ * kafka/linear_kf.py:225-227).  It must not touch `stream`'s pending work or the buffers of this call. */
+typedef void (*kafka_host_hook)(void* arg);
 int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, const kafka_gp_band* gp_bands_host,
                           int n_bands, const double* y, const double* w, const uint8_t* obs_mask,
                           const double* x_f, const double* pinv_f, double* h0_work, double* jac_work,
@@ -321,7 +337,7 @@ int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, const kafka_g
                           double* scalars, void* pinned_host, double* scratch, double tol,
                           int min_iterations, uint32_t flags, void* stream, double* norms_host,
                           int* n_solves, int* n_bad_last, int* n_bad_max, int* x_index,
-                          const double* x_uniform);
+                          const double* x_uniform, kafka_host_hook while_queued, void* while_queued_arg);
 
 /* n host->device copies queued on `stream` by one call: the upload of one date's rasters
  * (observations.get_band_data, kafka/linear_kf.py:225-227, hands over three rasters per band) for

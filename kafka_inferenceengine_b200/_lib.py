@@ -57,6 +57,7 @@ SIGNATURES = {
     "kafka_gather_backscatter_band": (C.c_int, [_p, _i32, _p, _i64, C.c_double, C.c_double, _p, _p, _p, _p]),
     "kafka_gather_scaled_band": (C.c_int, [_p, _i32, _p, _p, _i64, C.c_double, C.c_double, _p, _p, _p, _p]),
     "kafka_scatter_output": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p, _p, _p]),
+    "kafka_output_rasters": (C.c_int, [_p, _p, _i64, _i64, _i32, _p, _i64, _p, _p, _i32, _p, _p]),
     "kafka_state_uniform": (C.c_int, [_p, _i64, _i64, _i32, _p, _p]),
     "kafka_read_small": (C.c_int, [_p, _p, _i64, _p]),
     "kafka_interleaved_to_planar": (C.c_int, [_p, _i64, _i32, _p, _i64, _p]),
@@ -78,7 +79,7 @@ SIGNATURES = {
     "kafka_assimilate_iter": (C.c_int, [_i64, _i64, _i32, C.POINTER(GpBand), _i32, _p, _p, _p, _p, _p, _p, _p, _p,
                                         _p, _p, _p, _p, _p, _p, _p, _u32, _p]),
     "kafka_assimilate_date": (C.c_int, [_i64, _i64, _i32, C.POINTER(GpBand), _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p,
-                                        _p, _p, _p, _p, C.c_double, _i32, _u32, _p, _p, _p, _p, _p, _p, _p]),
+                                        _p, _p, _p, _p, C.c_double, _i32, _u32, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "kafka_upload_rasters": (C.c_int, [_i32, _p, _p, _p, _p]),
     "kafka_wcm_forward": (C.c_int, [_p, _i64, _i64, _p, _p, _p, _p]),
     "kafka_advance_carry_slot": (C.c_int, [_p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _p, _p, _p]),
@@ -147,9 +148,16 @@ def np_ptr(a):
     return C.c_void_p(a.ctypes.data)
 
 
+HOST_HOOK = C.CFUNCTYPE(None, C.c_void_p)      # kafka_host_hook
+
+
 def stream_ptr():
+    """The current CUDA stream of the current device as a void*."""
     import torch
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    try:
+        return C.c_void_p(torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice()))
+    except AttributeError:                      # a torch without these helpers
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
 _small = {}          # device index -> (pinned uint8 tensor, event)

@@ -48,7 +48,8 @@ extern "C" int kafka_assimilate_iter(int64_t n_pix, int64_t ld, int n_params, co
 // norm = ||x - x_prev||_2 / len(x), stop when norm < tol and n_iter >= min_iterations or after
 // the 26th solve; the norms come back through page-locked memory written by a kernel
 // (kafka_read_small, 16 bytes per solve) and the stream is synchronised once per iteration that
-// can end the loop (iterations below min_iterations are queued back to back).  The states ping-pong
+// can end the loop (iterations below min_iterations are queued back to back; before the first wait the
+// caller's while_queued hook runs, so its host work hides behind the queued kernels).  The states ping-pong
 // between the two halves of x_work; *x_index says which half holds the analysis.  A and the
 // innovations are stored only by iterations that can be the last one.
 extern "C" int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, const kafka_gp_band* gp_bands_host,
@@ -58,7 +59,8 @@ extern "C" int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, co
                                      double* scalars, void* pinned_host, double* scratch, double tol,
                                      int min_iterations, uint32_t flags, void* stream, double* norms_host,
                                      int* n_solves, int* n_bad_last, int* n_bad_max, int* x_index,
-                                     const double* x_uniform) {
+                                     const double* x_uniform, kafka_host_hook while_queued,
+                                     void* while_queued_arg) {
     KAFKA_CHECK_ARG(x_work && scalars && pinned_host && norms_host && n_solves && x_index && a_out,
                     "kafka_assimilate_date: null workspace or result pointer");
     KAFKA_CHECK_ARG(n_pix >= 1 && n_params >= 1, "kafka_assimilate_date: empty problem");
@@ -112,6 +114,10 @@ extern "C" int kafka_assimilate_date(int64_t n_pix, int64_t ld, int n_params, co
         // an iteration below min_iterations cannot end the loop (linear_kf.py:297): its norm is only reported,
         // so the next iteration is queued right behind it and the host waits once for both
         if (n_iter < min_iterations && n_iter <= 25) continue;
+        if (while_queued) {                                         // the caller's host work, behind the queued iterations
+            while_queued(while_queued_arg);
+            while_queued = nullptr;
+        }
         KAFKA_CUDA(cudaStreamSynchronize(s));
         double norm = 0.0;
         for (; n_read < n_iter; ++n_read) {

@@ -462,6 +462,22 @@ int kafka_scatter_output(const double* x, const double* a_packed, int64_t ld, in
     return launch_status("scatter_output");
 }
 
+int kafka_output_rasters(const double* x, const double* a_packed, int64_t ld, int64_t n_pix, int n_params,
+                         const int32_t* idx, int64_t n_raster, float* mean_raster, float* unc_raster, int zero_first,
+                         void* host_dst, void* stream) {
+    KAFKA_CHECK_ARG(mean_raster && n_raster >= 0, "kafka_output_rasters: null raster");
+    KAFKA_CHECK_ARG(n_params >= 1 && n_params <= KAFKA_MAX_PARAMS, "kafka_output_rasters: n_params=%d", n_params);
+    KAFKA_CHECK_ARG(!unc_raster || unc_raster == mean_raster + (int64_t)n_params * n_raster,
+                    "kafka_output_rasters: the two rasters must be one allocation, mean first");
+    const size_t bytes = (size_t)(unc_raster ? 2 : 1) * n_params * n_raster * sizeof(float);
+    if (zero_first && bytes) KAFKA_CUDA(cudaMemsetAsync(mean_raster, 0, bytes, (cudaStream_t)stream));
+    int rc = kafka_scatter_output(x, a_packed, ld, n_pix, n_params, idx, n_raster, mean_raster, unc_raster, stream);
+    if (rc != 0) return rc;
+    if (host_dst && bytes)
+        KAFKA_CUDA(cudaMemcpyAsync(host_dst, mean_raster, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    return 0;
+}
+
 int kafka_state_uniform(const double* x, int64_t ld, int64_t n_pix, int n_params, int32_t* n_diff, void* stream) {
     KAFKA_CHECK_ARG(n_pix >= 0 && ld >= n_pix, "kafka_state_uniform: need 0 <= n_pix <= ld");
     KAFKA_CHECK_ARG(n_params >= 1 && n_params <= KAFKA_MAX_PARAMS, "kafka_state_uniform: n_params=%d", n_params);

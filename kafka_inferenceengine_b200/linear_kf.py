@@ -443,6 +443,22 @@ class LinearKalman(object):
                 and 0 < self.n_state_elems <= self.SMALL_IMAGE_PIXELS
                 and not self.hessian_correction and not getattr(self, "_force_hessian", False))
 
+    def _while_queued_hook(self):
+        """kafka_host_hook of kafka_assimilate_date: the next date's rasters are read and sent once
+        this date's first iterations are queued, so that host work hides behind the kernels.  An
+        exception cannot cross the C frame: it is kept and raised when the call returns."""
+        hook = getattr(self, "_hook", None)
+        if hook is None:
+            self._hook_error = None
+
+            def run(_arg, self=self):
+                try:
+                    self._prefetch_next()
+                except BaseException as e:          # noqa: B036 -- re-raised by the caller of the C function
+                    self._hook_error = e
+            hook = self._hook = _lib.HOST_HOOK(run)
+        return hook
+
     def _do_all_bands_small(self, current_data, group, token, x_forecast, P_forecast_inverse, tol, min_iterations):
         import ctypes as C
         lib = _lib.get_lib()
@@ -471,7 +487,6 @@ class LinearKalman(object):
                     arr[b].mapper[d] = int(mp[d])
             st["arr"], st["arr_key"] = arr, key
         bufs = self._stager.finish(token if token is not None else self._stager.stage(current_data), out=st["bufs"])
-        self._prefetch_next()                 # the next date's rasters travel while this date is solved
         # handed to the caller: fresh per date (the output stage may still be reading the previous ones)
         x_work = torch.empty((2, P, ld), dtype=torch.float64, device=dev)
         a_out = BlockDiag.empty(n, P, dev)
@@ -493,8 +508,11 @@ class LinearKalman(object):
                 _lib.ptr(a_out.data), _lib.ptr(innov), _lib.ptr(fwd), _lib.ptr(st["scalars"]),
                 C.c_void_p(st["pinned"].data_ptr()), _lib.ptr(st["scratch"]), float(tol), int(min_iterations), flags,
                 _lib.stream_ptr(), C.addressof(st["norms"]), st["ints_at"], st["ints_at"] + 4, st["ints_at"] + 8,
-                st["ints_at"] + 12, _lib.ptr(x_uni)),
+                st["ints_at"] + 12, _lib.ptr(x_uni), self._while_queued_hook(), None),
                 "kafka_assimilate_date")
+        if self._hook_error is not None:
+            err, self._hook_error = self._hook_error, None
+            raise err
         n_solves, n_bad, n_bad_max, idx = ints[0], ints[1], ints[2], ints[3]
         _lib.launch_count += 4 * n_solves     # kernels of the call: (linearise, solve, second stage, read) per solve
         # slot k of the page-locked buffer: [sum of squares f64 | left at the forecast i32 | solved by elimination i32]

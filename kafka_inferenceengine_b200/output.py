@@ -8,9 +8,12 @@ rasters on the host and writes GeoTIFFs with GDAL.  Here the scatter, the
 the rasters come back through pinned buffers; what is done with them (GeoTIFF,
 NetCDF, nothing) is the ``sink``'s business -- GDAL itself is out of scope.
 """
+import ctypes as C
+
 import numpy as np
 import torch
 
+from . import _lib
 from .device import BlockDiag, DeviceVector, PixelIndex
 
 
@@ -76,6 +79,8 @@ class RasterOutput(object):
         self._deliver()
 
     def _host_pair(self, shape):
+        """A free buffer set of the ring: [host mean, host unc, host both (pinned), device both,
+        event, the pixel index the device rasters were last written through]."""
         while True:
             while self._free:
                 pair = self._free.pop()
@@ -85,7 +90,7 @@ class RasterOutput(object):
             if self._n_alloc < self.n_buffers or not self._pending:      # (no date in flight: the pair self.last holds)
                 self._n_alloc += 1
                 both = torch.empty((2,) + tuple(shape), dtype=torch.float32).pin_memory()
-                return (both[0], both[1], both)
+                return [both[0], both[1], both, None, torch.cuda.Event(), None]
             # every pair is in flight: wait for the oldest date
             timestep, event, host, keep = self._pending[0]
             event.synchronize()
@@ -98,24 +103,37 @@ class RasterOutput(object):
         P_analysis_inv = BlockDiag.coerce(P_analysis_inv, n_params, x_analysis.n_pix, device).materialise()
         pix = getattr(self, "pixels", None) or self._pixel_index(state_mask, device)
         self._deliver(block=False)                       # whatever has arrived in the meantime
-        main = torch.cuda.current_stream(device)
         if self._stream is None:
             self._stream = torch.cuda.Stream(device=device)
-        side = self._stream if self.overlap else main
-        side.wait_stream(main)
-        with torch.cuda.stream(side):
-            mean_r, unc_r = pix.scatter_output(x_analysis, P_analysis_inv, n_params)
-            host = self._host_pair(mean_r.shape)
-            base = mean_r._base
-            if base is not None and base is unc_r._base and base.is_contiguous() and base.numel() == host[2].numel():
-                host[2].view(base.shape).copy_(base, non_blocking=True)  # both rasters in one copy
+            self._main_done = torch.cuda.Event()
+        shape = (n_params,) + tuple(pix.shape)
+        pair = self._host_pair(shape)
+        # the device rasters belong to the buffer set: filled with zeros once, afterwards only the
+        # state pixels are rewritten (through the same index), so no fill and no allocation per date
+        zero_first = 0
+        if pair[3] is None or pair[3].device != device:
+            pair[3] = torch.empty((2, n_params, pix.n_raster), dtype=torch.float32, device=device)
+            pair[5] = None
+        if pair[5] is not pix:
+            zero_first, pair[5] = 1, pix
+        dev = pair[3]
+        with torch.cuda.device(device):
+            if self.overlap:
+                self._main_done.record()                 # current stream: the analysis is complete there
+                self._stream.wait_event(self._main_done)
+                stream = C.c_void_p(self._stream.cuda_stream)
             else:
-                host[0].copy_(mean_r, non_blocking=True)
-                host[1].copy_(unc_r, non_blocking=True)
-            event = torch.cuda.Event()
-            event.record(side)
-        # keep the device tensors alive until the copy has been consumed
-        self._pending.append((timestep, event, host, (mean_r, unc_r, x_analysis, P_analysis_inv)))
-        self.d2h_bytes += 2 * mean_r.numel() * 4
+                stream = _lib.stream_ptr()
+            _lib.check(_lib.get_lib().kafka_output_rasters(
+                _lib.ptr(x_analysis.data), _lib.ptr(P_analysis_inv.data), x_analysis.ld, pix.n_pix, n_params,
+                _lib.ptr(pix.idx), pix.n_raster, C.c_void_p(dev.data_ptr()), C.c_void_p(dev[1].data_ptr()), zero_first,
+                C.c_void_p(pair[2].data_ptr()), stream), "kafka_output_rasters")
+            if self.overlap:
+                pair[4].record(self._stream)
+            else:
+                pair[4].record()
+        # keep the inputs alive until the copy has been consumed
+        self._pending.append((timestep, pair[4], pair, (x_analysis, P_analysis_inv)))
+        self.d2h_bytes += 2 * n_params * pix.n_raster * 4
         if not self.overlap:
             self._deliver()
