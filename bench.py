@@ -1103,7 +1103,7 @@ def main():
                                "and shared (reference: run_emulator single-unique-vector branch, utils.py:72-74); "
                                "later iterations evaluate every pixel",
             "value_without_shared_first_linearisation": world * n_pix / (ms_nodedup * 1e-3),
-            "collective": None if world == 1 else ("2-3 double NCCL all-reduce per solver iteration through %s"
+            "collective": None if world == 1 else ("4-double NCCL all-reduce (sum of squares, element count, two pixel counters) per solver iteration through %s"
                                                    % ("the library's communicator (kafka_allreduce_norm)"
                                                       if args.comm == "native" else "torch.distributed")),
             "clocks": clocks, "e2e": e2e, "e2e_raw_ingest": e2e_raw, "gpu_launches": launches, "roofline": roofline,
