@@ -28,6 +28,6 @@ elif [ "$1" = "lanes" ]; then
 else
   CMD="python bench.py --steps 2 --warmup 3 --rows 200 --no-cpu-baseline --no-e2e"
   $CMD > gpurun_out/plain.json
-  ncu --set full --clock-control none --import-source on -k regex:'gp_linearize_kernel|solve_bands_kernel' -s 4 -c 3 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
+  ncu --set full --clock-control none --import-source on -k regex:'gp_linearize_kernel|solve_bands_kernel|finish_solve_kernel' -s 6 -c 6 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
   export_rep gpurun_out/prof
 fi
