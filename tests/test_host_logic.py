@@ -91,6 +91,11 @@ norm, count = kdist.global_norm(local, i1 - i0)
 want = np.linalg.norm(d) / 1000.0           # linear_kf.py:293 on the unsharded vector
 assert count == 1000.0, count
 assert abs(norm - want) <= 1e-15 * want, (norm, want)
+# the two pixel counters of a solve (left at the forecast, solved by elimination) ride in the same all-reduce
+norm2, count2, counts = kdist.global_norm(local, i1 - i0, n_bad_local=torch.tensor([rank + 1, 10 * rank], dtype=torch.int32))
+assert (norm2, count2) == (norm, count) and counts == (3, 10), counts
+norm3, _, one = kdist.global_norm(float(local), i1 - i0, n_bad_local=2)
+assert norm3 == norm and one == 4, one
 g = kdist.gather_interleaved(torch.from_numpy(d[i0:i1].copy()))
 assert np.array_equal(g.numpy(), d)
 # ranks take the same stop decision
