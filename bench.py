@@ -938,6 +938,9 @@ def main():
                 return RasterOutput.dump_data(self, *a, **k)
 
         def run_e2e(obs):
+            import gc
+            gc.collect()                                   # what the previous leg left behind (page-locked rasters: freeing
+            torch.cuda.synchronize()                       # them synchronises the device) goes now, not inside the timed run
             out = TimedRasterOutput(syn.S2_PARAMETERS)     # float32 mean + 1/sqrt(diag) rasters, read back to the host
             kf2, prior2 = make_filter(obs, out)
             out.pixels = kf2.pixels

@@ -449,13 +449,20 @@ class LinearKalman(object):
         exception cannot cross the C frame: it is kept and raised when the call returns."""
         hook = getattr(self, "_hook", None)
         if hook is None:
+            import weakref
             self._hook_error = None
+            me = weakref.ref(self)                  # no reference cycle: the filter (and the page-locked rasters its
+                                                    # caches hold) must go away when the caller drops it, not at some
+                                                    # later collection in the middle of another run
 
-            def run(_arg, self=self):
+            def run(_arg):
+                kf = me()
+                if kf is None:
+                    return
                 try:
-                    self._prefetch_next()
+                    kf._prefetch_next()
                 except BaseException as e:          # noqa: B036 -- re-raised by the caller of the C function
-                    self._hook_error = e
+                    kf._hook_error = e
             hook = self._hook = _lib.HOST_HOOK(run)
         return hook
 
