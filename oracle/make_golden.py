@@ -22,6 +22,9 @@ run_linear.npz       LinearKalman.run, 1 linear band in (H0,H) tuple form
 kat_sar.npz          sar_observation_operator, VV and VH
                      (observation_operators/sar_forward_model.py:13-113)
 kat_hessian.npz      hessian_correction(_multiband) on the TIP layout (kf_tools.py:26-72)
+solve_indefinite.npz variational_kalman_multiband and blend_prior on forecast blocks that are NOT
+                     positive definite (what the Hessian correction can hand on): the sparse LU
+                     returns the solution of the equations (solvers.py:133-134, kf_tools.py:93-94)
 """
 import datetime as dt
 import hashlib
@@ -558,6 +561,65 @@ def kat_output_stage(kafka):
     np.savez_compressed(os.path.join(OUT, "kat_output_stage.npz"), **res)
 
 
+def solve_indefinite(kafka):
+    """The unmodified solver and prior blend on a forecast whose inverse-covariance blocks are
+    indefinite for every third pixel (one eigenvalue flipped); two bands with supplied
+    linearisations in the (H0, dH) tuple form, some pixels unobserved."""
+    rng = np.random.default_rng(4242)
+    P, B = 7, 2
+    mask = _small_mask(rng, 9, 11)
+    N = int(mask.sum())
+    ku = kafka.inference.utils
+    blocks = np.zeros((N, P, P))
+    for i in range(N):
+        M = rng.standard_normal((P, P))
+        S = M @ M.T / P + np.eye(P)
+        if i % 3 == 0:                                   # flip the middle eigenvalue: indefinite, well conditioned
+            w, V = np.linalg.eigh(S)
+            w[P // 2] = -w[P // 2]
+            S = (V * w) @ V.T
+        blocks[i] = 0.5 * (S + S.T)
+    blocks = blocks.astype(np.float32).astype(np.float64)
+    Pinv = sp.block_diag([b for b in blocks], format="csr")
+    x_f = rng.standard_normal(N * P)
+    x_lin = x_f + 0.1 * rng.standard_normal(N * P)
+    n_raster = mask.size
+    Hs, obs_r, unc, masks, Jd, H0d = [], [], [], [], [], []
+    rows = np.repeat(np.arange(N), P)
+    cols = np.arange(N * P)
+    for b in range(B):
+        m = np.zeros(mask.shape, dtype=bool)
+        m[mask] = rng.random(N) < 0.8
+        J = rng.standard_normal((N, P)).astype(np.float32)
+        J[~m[mask]] = 0.0                               # unobserved pixels carry an empty row (utils.py:199-215)
+        H0 = (rng.standard_normal(N) * m[mask]).astype(np.float32)
+        dH = sp.csr_matrix((J.ravel(), (rows, cols)), shape=(N, N * P), dtype=np.float32)
+        y = np.zeros(mask.shape)
+        y[mask] = rng.standard_normal(N)
+        r = np.zeros(n_raster)
+        r[m.ravel()] = 1.0 / (0.05 + 0.1 * rng.random(int(m.sum()))) ** 2
+        Hs.append((H0, dH))
+        obs_r.append(y)
+        unc.append(sp.diags(r, format="csr"))
+        masks.append(m)
+        Jd.append(J)
+        H0d.append(H0)
+    x, _, A, innov, fwd = kafka.inference.solvers.variational_kalman_multiband(
+        obs_r, masks, mask, unc, Hs, P, x_lin, x_f, None, Pinv, None)
+    # prior blend with the same forecast blocks (kf_tools.py:75-96)
+    prior_inv_blocks = (1e-2 * np.eye(P)[None] * (1.0 + rng.random((N, 1, 1)))).astype(np.float32).astype(np.float64)
+    prior_mean = rng.standard_normal(N * P)
+    xb, Cb = kafka.inference.kf_tools.blend_prior(prior_mean, sp.block_diag([b for b in prior_inv_blocks], format="csr"),
+                                                  x_f, Pinv)
+    res = {"mask": mask, "blocks": blocks, "x_f": x_f, "x_lin": x_lin,
+           "J": np.array(Jd), "H0": np.array(H0d), "obs": np.array(obs_r), "inv_var": np.array([u.diagonal() for u in unc]),
+           "obs_mask": np.array(masks), "ref_x": np.asarray(x), "ref_A_diag": A.diagonal(),
+           "ref_innovations": innov, "ref_fwd": fwd,
+           "prior_inv_blocks": prior_inv_blocks, "prior_mean": prior_mean, "ref_blend_x": np.asarray(xb),
+           "ref_blend_C_diag": Cb.diagonal()}
+    np.savez_compressed(os.path.join(OUT, "solve_indefinite.npz"), **res)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     kafka = ref_shim.load()
@@ -572,6 +634,7 @@ def main():
     solve_and_run_s2(kafka)
     run_tip(kafka)
     run_linear(kafka)
+    solve_indefinite(kafka)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

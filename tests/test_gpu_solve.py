@@ -452,3 +452,53 @@ def test_large_image_properties():
         rhs += 400.0 * yp[:, None] * Jb
     res = np.einsum("npq,nq->np", Ab, xs_) - rhs
     assert np.max(np.abs(res)) < 1e-9 * np.max(np.abs(rhs))
+
+
+@pytest.mark.parametrize("pair", [0, _lib.SOLVE_PAIR])
+def test_indefinite_blocks_vs_unmodified_reference(pair):
+    """tests/golden/solve_indefinite.npz: the UNMODIFIED reference's variational_kalman_multiband
+    (solvers.py:100-145) and blend_prior (kf_tools.py:75-96) on forecast blocks that are not positive
+    definite for every third pixel.  Its sparse LU returns the solution of those systems; the
+    library reaches the same numbers through the pivoted elimination of its second stage (to the
+    float32 accuracy of the reference's LU) and agrees with oracle B to 1e-9."""
+    from kafka_inferenceengine_b200.device import BlockDiag
+    g = gio.load("solve_indefinite")
+    P = 7
+    blocks = g["blocks"]
+    n = blocks.shape[0]
+    mask = g["mask"]
+    bands, ys, ws, H0s, Js = [], [], [], [], []
+    for b in range(g["obs"].shape[0]):
+        y, r, m = kc.gather_band(g["obs"][b], g["inv_var"][b], g["obs_mask"][b], mask)
+        w = kc.gate_inverse_variance(r, m)
+        J, H0 = g["J"][b].astype(np.float64), g["H0"][b].astype(np.float64)
+        bands.append(dict(J=J, H0=H0, y=y, w=w))
+        ys.append(y)
+        ws.append(w)
+        H0s.append(H0)
+        Js.append(J)
+    x, A, innov, fwd, norm2, n_bad, n_lu = _call(n, P, bands, g["x_lin"], g["x_f"], gu.pack_blocks(blocks), flags=pair,
+                                                 count_lu=True)
+    xo, Ao, innov_o, fwd_o = kc.solve_dense64(ys, ws, H0s, Js, g["x_lin"], g["x_f"], blocks)
+    ev = np.linalg.eigvalsh(Ao)
+    assert n_bad == 0 and n_lu == int((ev.min(axis=1) < 0).sum()) and n_lu >= 12
+    assert np.max(np.abs(x - xo) / np.maximum(np.abs(xo), 1e-3)) < RTOL
+    assert norm2 == pytest.approx(float(((xo - g["x_lin"]) ** 2).sum()), rel=1e-9)
+    assert np.allclose(fwd, fwd_o, rtol=1e-8, atol=1e-9)
+    # against the reference's float32 LU: errors of the order of cond(A) * 6e-8
+    cond = np.abs(ev).max(axis=1) / np.abs(ev).min(axis=1)
+    err = np.abs(x - g["ref_x"]).reshape(n, P).max(axis=1) / np.abs(g["ref_x"]).reshape(n, P).max(axis=1)
+    assert (err < 2e-6 * np.maximum(cond, 10.0)).all(), (err / cond).max()
+    idx = np.arange(P)
+    assert np.allclose(A[:, idx, idx].ravel(), g["ref_A_diag"], rtol=3e-6, atol=1e-5)
+    if not pair:
+        xb, Cb = kb.blend_prior(g["prior_mean"], BlockDiag.from_blocks(g["prior_inv_blocks"], gu.DEV), g["x_f"],
+                                BlockDiag.from_blocks(blocks, gu.DEV))
+        xbo, Cbo = kc.blend_prior(g["prior_mean"], g["prior_inv_blocks"], g["x_f"], blocks)
+        assert np.max(np.abs(np.asarray(xb) - xbo) / np.maximum(np.abs(xbo), 1e-3)) < 1e-9
+        evc = np.linalg.eigvalsh(Cbo)
+        condc = np.abs(evc).max(axis=1) / np.abs(evc).min(axis=1)
+        errb = np.abs(np.asarray(xb) - g["ref_blend_x"]).reshape(n, P).max(axis=1) / \
+            np.abs(g["ref_blend_x"]).reshape(n, P).max(axis=1)
+        assert (errb < 2e-6 * np.maximum(condc, 10.0)).all(), (errb / condc).max()
+        assert np.allclose(Cb.blocks()[:, idx, idx].ravel(), g["ref_blend_C_diag"], rtol=1e-6)

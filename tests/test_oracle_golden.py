@@ -352,3 +352,53 @@ def test_output_scatter_matches_the_unmodified_writer():
     for ii in range(P):
         assert np.array_equal(kc.scatter_param(g["x"], ii, P, g["mask"]), g["mean_%d" % ii])
         assert np.array_equal(kc.scatter_unc(diag, ii, P, g["mask"]), g["unc_%d" % ii])
+
+
+def _indefinite_inputs(g):
+    """Compacted per-band rows of the solve_indefinite fixture as the oracle takes them."""
+    mask = g["mask"]
+    ys, ws, ms = [], [], []
+    for b in range(g["obs"].shape[0]):
+        y, r, m = kc.gather_band(g["obs"][b], g["inv_var"][b], g["obs_mask"][b], mask)
+        ys.append(y)
+        ws.append(kc.gate_inverse_variance(r, m))
+        ms.append(m)
+    return ys, ws, [g["H0"][b].astype(np.float64) for b in range(len(ys))], \
+        [g["J"][b].astype(np.float64) for b in range(len(ys))]
+
+
+def test_indefinite_blocks_vs_reference():
+    """Forecast blocks that are not positive definite (every third pixel): the unmodified reference's
+    sparse LU returns the solution of the equations for them like for any other pixel
+    (solvers.py:133-134, kf_tools.py:93-94), and so do both oracles -- the rule the CUDA path is held
+    to (tests/test_gpu_solve.py, test_gpu_advance.py)."""
+    g = gio.load("solve_indefinite")
+    P = 7
+    blocks = g["blocks"]
+    N = blocks.shape[0]
+    ev = np.linalg.eigvalsh(blocks)
+    indef = ev.min(axis=1) < 0
+    assert indef.sum() == len(range(0, N, 3)) and (np.abs(ev).max(axis=1) / np.abs(ev).min(axis=1)).max() < 1e3
+    ys, ws, H0s, Js = _indefinite_inputs(g)
+    xd, Ad, innov_d, fwd_d = kc.solve_dense64(ys, ws, H0s, Js, g["x_lin"], g["x_f"], blocks)
+    xs, As, _, _ = kc.solve_sparse32(ys, ws, H0s, Js, g["x_lin"], g["x_f"], kc.blocks_to_sparse(blocks))
+    # most of those systems are still indefinite after the observations have been added
+    still = np.linalg.eigvalsh(Ad).min(axis=1) < 0
+    assert still.sum() >= 12 and not still[~indef].any()
+    idx = np.arange(P)
+    assert np.allclose(Ad[:, idx, idx].ravel(), g["ref_A_diag"], rtol=3e-6, atol=1e-5)
+    # float32 LU of the reference: errors of the order of cond(A) * 6e-8
+    cond = np.abs(np.linalg.eigvalsh(Ad)).max(axis=1) / np.abs(np.linalg.eigvalsh(Ad)).min(axis=1)
+    err = np.abs(xd - g["ref_x"]).reshape(N, P).max(axis=1) / np.abs(g["ref_x"]).reshape(N, P).max(axis=1)
+    assert (err < 2e-6 * np.maximum(cond, 10.0)).all(), (err / cond).max()
+    assert np.allclose(xs, g["ref_x"], rtol=2e-3, atol=1e-4)
+    assert np.allclose(innov_d, g["ref_innovations"], rtol=1e-6, atol=1e-6)
+    assert np.allclose(fwd_d, g["ref_fwd"], rtol=2e-3, atol=2e-3)
+    # prior blend on the same forecast blocks
+    xb, Cb = kc.blend_prior(g["prior_mean"], g["prior_inv_blocks"], g["x_f"], blocks)
+    assert np.allclose(Cb[:, idx, idx].ravel(), g["ref_blend_C_diag"], rtol=1e-6)
+    evc = np.linalg.eigvalsh(Cb)
+    assert (evc[indef].min(axis=1) < 0).all()
+    condc = np.abs(evc).max(axis=1) / np.abs(evc).min(axis=1)
+    errb = np.abs(xb - g["ref_blend_x"]).reshape(N, P).max(axis=1) / np.abs(g["ref_blend_x"]).reshape(N, P).max(axis=1)
+    assert (errb < 2e-6 * np.maximum(condc, 10.0)).all(), (errb / condc).max()
