@@ -107,3 +107,37 @@ def test_gp_pack_host_matches_numpy():
     assert rows[0, 4] == -2.0 ** 29 and rows[0, 5].view(np.uint64) == 0 and rows[2, 5].view(np.uint64) == 0x80000000
     with pytest.raises(_lib.KafkaCudaError):
         _lib.gp_pack(np.zeros((3, 2)), np.zeros(4), np.array([1.0, np.nan, 1.0]))
+
+
+def test_header_constants_match_the_python_binding():
+    """The numbers a binder copies out of include/kafka_b200.h are the ones _lib.py uses, and the
+    built-in scratch of kafka_solve_bands_static is exactly as large as its pixel limit needs."""
+    text = open(HEADER).read()
+
+    def const(name):
+        m = re.search(r"#define\s+%s\s+\(?(-?\d+)u?\)?" % name, text)
+        assert m, name
+        return int(m.group(1))
+    assert const("KAFKA_MAX_PARAMS") == _lib.MAX_PARAMS and const("KAFKA_MAX_DIM") == _lib.MAX_DIM
+    assert const("KAFKA_ROUND_F32") == _lib.ROUND_F32 and const("KAFKA_PRIOR_BROADCAST") == _lib.PRIOR_BROADCAST
+    assert const("KAFKA_SOLVE_PAIR") == _lib.SOLVE_PAIR and const("KAFKA_SOLVE_COUNT_LU") == _lib.SOLVE_COUNT_LU
+    assert const("KAFKA_STATIC_SCRATCH_DOUBLES") == _lib.STATIC_SCRATCH_DOUBLES
+    assert const("KAFKA_STATIC_MAX_PIXELS") == _lib.STATIC_MAX_PIXELS
+    assert const("KAFKA_COMM_ID_BYTES") == _lib.COMM_ID_BYTES
+    lib = _lib.get_lib()
+    assert lib.kafka_solve_scratch_doubles(_lib.STATIC_MAX_PIXELS) == _lib.STATIC_SCRATCH_DOUBLES
+    assert lib.kafka_solve_scratch_doubles(_lib.STATIC_MAX_PIXELS + 1) > _lib.STATIC_SCRATCH_DOUBLES
+    assert lib.kafka_solve_scratch_doubles(0) > 0            # the second stage's own slots
+
+
+def test_new_entry_points_reject_bad_arguments_without_a_gpu():
+    lib = _lib.get_lib()
+    st = lib.kafka_output_rasters(None, None, 32, 10, 4, None, 100, None, None, 0, None, None)
+    assert st == -1 and b"raster" in lib.kafka_last_error()
+    st = lib.kafka_output_rasters(None, None, 32, 10, 17, None, 100, C.c_void_p(256), None, 0, None, None)
+    assert st == -1 and b"n_params" in lib.kafka_last_error()
+    # the two rasters have to be one allocation, mean first
+    st = lib.kafka_output_rasters(None, None, 32, 10, 4, None, 100, C.c_void_p(4096), C.c_void_p(4096 + 8), 0, None, None)
+    assert st == -1 and b"one allocation" in lib.kafka_last_error()
+    st = lib.kafka_upload_rasters(3, None, None, None, None)
+    assert st == -1
