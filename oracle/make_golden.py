@@ -611,7 +611,14 @@ def solve_indefinite(kafka):
     prior_mean = rng.standard_normal(N * P)
     xb, Cb = kafka.inference.kf_tools.blend_prior(prior_mean, sp.block_diag([b for b in prior_inv_blocks], format="csr"),
                                                   x_f, Pinv)
-    res = {"mask": mask, "blocks": blocks, "x_f": x_f, "x_lin": x_lin,
+    # exact propagator on the same blocks (kf_tools.py:208-245: spsolve of (I + P^-1 Q) X = P^-1), with an
+    # inflation large enough for the flipped direction to matter
+    q = rng.uniform(0.5, 1.5, N * P) / np.repeat(np.abs(np.linalg.eigvalsh(blocks)).min(axis=1), P)
+    _, _, Pf = kafka.inference.kf_tools.propagate_information_filter_SLOW(
+        x_f, None, Pinv, sp.eye(N * P, format="csr"), sp.diags(q, format="csr"))
+    Pf = sp.csr_matrix(Pf).toarray()
+    res = {"q": q, "ref_exact_blocks": np.array([Pf[i * P:(i + 1) * P, i * P:(i + 1) * P] for i in range(N)]),
+           "mask": mask, "blocks": blocks, "x_f": x_f, "x_lin": x_lin,
            "J": np.array(Jd), "H0": np.array(H0d), "obs": np.array(obs_r), "inv_var": np.array([u.diagonal() for u in unc]),
            "obs_mask": np.array(masks), "ref_x": np.asarray(x), "ref_A_diag": A.diagonal(),
            "ref_innovations": innov, "ref_fwd": fwd,

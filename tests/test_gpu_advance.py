@@ -204,3 +204,22 @@ def test_indefinite_blocks_are_solved_like_the_reference_lu(P):
     cond = np.abs(ev).max(axis=1) / np.abs(ev).min(axis=1)
     assert (err < 1e-13 * np.maximum(cond, 10.0)).all()
     assert (err[keep] < 1e-10).all()
+
+
+def test_exact_propagator_on_indefinite_blocks_vs_unmodified_reference():
+    """tests/golden/solve_indefinite.npz: the unmodified propagate_information_filter_SLOW
+    (kf_tools.py:208-245, a float64 spsolve) on analysis blocks that are not positive definite for
+    every third pixel; for 19 of the 55 pixels I + S P^-1 S is not positive definite either, so the
+    kernel's Cholesky route fails and its pivoted elimination has to give the reference's answer."""
+    g = gio.load("solve_indefinite")
+    P = 7
+    blocks, q = g["blocks"], g["q"]
+    n = blocks.shape[0]
+    inner = np.eye(P)[None] + np.sqrt(q).reshape(n, P, 1) * blocks * np.sqrt(q).reshape(n, 1, P)
+    assert int((np.linalg.eigvalsh(inner).min(axis=1) < 0).sum()) == 19
+    _, _, p = kb.propagate_information_filter_SLOW(g["x_f"], None, BlockDiag.from_blocks(blocks, gu.DEV), None,
+                                                   kb.DiagonalMatrix(q, P, gu.DEV))
+    got = p.blocks()
+    lower = np.tril(np.ones((P, P), dtype=bool))
+    scale = np.broadcast_to(np.abs(g["ref_exact_blocks"]).max(axis=(1, 2), keepdims=True), got.shape)
+    assert np.max((np.abs(got - g["ref_exact_blocks"]) / scale)[:, lower]) < 1e-10

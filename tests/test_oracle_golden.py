@@ -402,3 +402,7 @@ def test_indefinite_blocks_vs_reference():
     condc = np.abs(evc).max(axis=1) / np.abs(evc).min(axis=1)
     errb = np.abs(xb - g["ref_blend_x"]).reshape(N, P).max(axis=1) / np.abs(g["ref_blend_x"]).reshape(N, P).max(axis=1)
     assert (errb < 2e-6 * np.maximum(condc, 10.0)).all(), (errb / condc).max()
+    # exact propagator on the same blocks (kf_tools.py:208-245: a float64 spsolve)
+    _, want = kc.propagate_information_filter_exact(g["x_f"], blocks, g["q"])
+    scale = np.abs(g["ref_exact_blocks"]).max(axis=(1, 2), keepdims=True)
+    assert np.max(np.abs(want - g["ref_exact_blocks"]) / scale) < 1e-12
